@@ -1,0 +1,290 @@
+"""
+oracle.py -- TEST INFRASTRUCTURE ONLY (checker for the CUDA product path).
+
+Two CPU restatements of the reference's frame-recurrent 4x EnhanceNet inference path:
+
+* backend "c":     ctypes binding of oracle/isr_oracle.c (plain C, fp32, explicit op order).
+* backend "torch": the same functions restated with torch CPU ops (F.conv2d, F.interpolate,
+                   F.grid_sample) -- the third-party arithmetic the reference itself calls
+                   (PyTorch ATen, torch 2.11.0; not vendored under /root/reference).  Used for
+                   sizes the scalar C code would take too long on, and as the timed CPU baseline.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  Nothing here reads /root/reference at run time.
+
+Each function cites the reference file:line it follows (relative to
+/root/reference/SuperresolutionNetwork).  Parity is pinned against tests/golden/*.npz, produced
+from the live reference by oracle/gen_golden.py (the reference ships no golden vectors of its
+own: "parity unpinned by the reference's tests").
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+STATE_DICT_KEYS = (
+    ["preblock.0.weight", "preblock.0.bias"]
+    + [f"blocks.{i}.{j}.{k}" for i in range(10) for j in (0, 2) for k in ("weight", "bias")]
+    + [f"postblock.{j}.{k}" for j in (1, 4, 6, 8) for k in ("weight", "bias")]
+)
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "libisr_oracle.so")
+    src = os.path.join(_HERE, "isr_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = ctypes.CDLL(build())
+        _LIB.orc_initial_image.restype = ctypes.c_int
+        _LIB.orc_enhancenet_forward.restype = ctypes.c_int
+    return _LIB
+
+
+def _f32(a):
+    if isinstance(a, torch.Tensor):
+        a = a.detach().cpu().numpy()
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+# ---------------------------------------------------------------------------------------------
+# models/videotools.py:8-25
+def flatten_high(image_high, upscale_factor, backend="c"):
+    x = _f32(image_high)
+    B, C, H, W = x.shape
+    r = upscale_factor
+    if backend == "torch":
+        return F.pixel_unshuffle(torch.from_numpy(x), r).numpy()
+    out = np.empty((B, C * r * r, H // r, W // r), np.float32)
+    lib().orc_flatten_high(_p(x), _p(out), B, C, H, W, r)
+    return out
+
+
+# models/videotools.py:49-87
+def warp_upscale(image_high, flow_low, upscale_factor, special_mask=False, backend="c"):
+    img, flow = _f32(image_high), _f32(flow_low)
+    B, C, H, W = img.shape
+    _, two, h, w = flow.shape
+    assert two == 2 and H == h * upscale_factor and W == w * upscale_factor
+    if backend == "torch":
+        ti, tf = torch.from_numpy(img), torch.from_numpy(flow)
+        f2 = torch.cat((tf[:, 0:1] * -2.0, tf[:, 1:2] * 2.0), dim=1)
+        fh = F.interpolate(f2, scale_factor=upscale_factor, mode="bilinear").permute(0, 2, 3, 1)
+        gh = torch.linspace(-1, 1, H).unsqueeze(1)
+        gw = torch.linspace(-1, 1, W).unsqueeze(0)
+        offs = torch.stack(torch.broadcast_tensors(gw, gh), dim=2).unsqueeze(0)
+        grid = offs + fh
+        if special_mask:
+            ti = torch.cat([ti[:, 0:1] * 0.5 + 0.5, ti[:, 1:]], dim=1)
+        o = F.grid_sample(ti, grid, mode="bilinear", padding_mode="zeros", align_corners=False)
+        if special_mask:
+            o = torch.cat([o[:, 0:1] * 2 - 1, o[:, 1:]], dim=1)
+        return o.numpy()
+    out = np.empty_like(img)
+    lib().orc_warp_upscale(_p(img), _p(flow), _p(out), B, C, h, w, upscale_factor, int(bool(special_mask)))
+    return out
+
+
+_MODES = {"zero": 0, "unshaded": 1, "input": 2}
+
+
+# utils/initial_image.py:5-54
+def initial_image(current_input, channels, mode, ao_inverted, upscaling=4):
+    x = _f32(current_input)
+    B, Cin, h, w = x.shape
+    if mode not in _MODES:
+        raise ValueError("unknown input mode: " + mode)
+    out = np.empty((B, channels, h * upscaling, w * upscaling), np.float32)
+    rc = lib().orc_initial_image(_p(x), _p(out), B, Cin, h, w, channels, _MODES[mode], int(bool(ao_inverted)), upscaling)
+    if rc != 0:
+        raise ValueError("for mode='unshaded', channels is expected to be 5 or 6")
+    return out
+
+
+def upsample(x, s, mode, backend="c"):
+    x = _f32(x)
+    B, C, h, w = x.shape
+    if backend == "torch":
+        return F.interpolate(torch.from_numpy(x), scale_factor=s, mode=mode).numpy()
+    out = np.empty((B, C, h * s, w * s), np.float32)
+    (lib().orc_upsample_bilinear if mode == "bilinear" else lib().orc_upsample_nearest)(_p(x), _p(out), B, C, h, w, s)
+    return out
+
+
+def conv3x3(x, weight, bias, relu=False):
+    x, weight, bias = _f32(x), _f32(weight), _f32(bias)
+    B, Cin, H, W = x.shape
+    Cout = weight.shape[0]
+    out = np.empty((B, Cout, H, W), np.float32)
+    lib().orc_conv3x3(_p(x), _p(weight), _p(bias), _p(out), B, Cin, Cout, H, W, int(relu))
+    return out
+
+
+# models/enhancenet.py:136-145 + :51-90
+def enhancenet_forward(state_dict, inputs, upsample_mode="bilinear", recon_type="residual", n_mask=5,
+                       backend="c"):
+    """Returns (recon, raw) like EnhanceNet.forward.  state_dict: name -> array/tensor (useBN=False)."""
+    x = _f32(inputs)
+    B, Cin, h, w = x.shape
+    params = [_f32(state_dict[k]) for k in STATE_DICT_KEYS]
+    Cout = params[-1].shape[0]
+    assert params[0].shape[1] == Cin
+    if upsample_mode not in ("nearest", "bilinear"):
+        raise ValueError("oracle supports nearest|bilinear")
+    if backend == "torch":
+        with torch.no_grad():
+            t = [torch.from_numpy(p) for p in params]
+            xin = torch.from_numpy(x)
+            f = F.relu(F.conv2d(xin, t[0], t[1], padding=1))
+            pi = 2
+            for _ in range(10):
+                u = F.relu(F.conv2d(f, t[pi], t[pi + 1], padding=1))
+                u = F.conv2d(u, t[pi + 2], t[pi + 3], padding=1)
+                f = f + u
+                pi += 4
+            f = F.interpolate(f, scale_factor=2, mode=upsample_mode)
+            f = F.relu(F.conv2d(f, t[pi], t[pi + 1], padding=1)); pi += 2
+            f = F.interpolate(f, scale_factor=2, mode=upsample_mode)
+            f = F.relu(F.conv2d(f, t[pi], t[pi + 1], padding=1)); pi += 2
+            f = F.relu(F.conv2d(f, t[pi], t[pi + 1], padding=1)); pi += 2
+            raw = F.conv2d(f, t[pi], t[pi + 1], padding=1)
+            if recon_type == "residual":
+                if n_mask > Cout:
+                    raise ValueError("number of output channels must be at least the number of masked input channels")
+                sk = F.interpolate(xin[:, 0:n_mask], size=[raw.shape[2], raw.shape[3]], mode=upsample_mode)
+                recon = torch.cat([sk + raw[:, 0:n_mask], raw[:, n_mask:]], dim=1)
+            else:
+                recon = raw
+            return recon.numpy(), raw.numpy()
+    recon = np.empty((B, Cout, 4 * h, 4 * w), np.float32)
+    raw = np.empty_like(recon)
+    arr = (ctypes.c_void_p * len(params))(*[p.ctypes.data for p in params])
+    rc = lib().orc_enhancenet_forward(_p(x), arr, _p(recon), _p(raw), B, Cin, Cout, h, w,
+                                      1 if upsample_mode == "bilinear" else 0,
+                                      1 if recon_type == "residual" else 0, n_mask)
+    if rc != 0:
+        raise ValueError("number of output channels must be at least the number of masked input channels")
+    return recon, raw
+
+
+# mainVideoUnshaded.py:460-465 / mainGUI.py:594-598 / mainVideo.py:416
+def postprocess(pred, unshaded=True):
+    x = _f32(pred)
+    B, C, H, W = x.shape
+    out = np.empty_like(x)
+    lib().orc_postprocess(_p(x), _p(out), B, C, H, W, int(bool(unshaded)))
+    return out
+
+
+def shading_params(ambient=(0.1, 0.1, 0.1), diffuse=(1.0, 1.0, 1.0), specular=(0.2, 0.2, 0.2),
+                   light=(0.1, 0.1, 1.0), material=(1.0, 0.3, 0.0), background=(0.0, 0.0, 0.0),
+                   ao_strength=1.0, exponent=16, enable_specular=True, inverse_ao=False):
+    """Packs the 22-float parameter block (same layout as include/isr.h isr_shade)."""
+    light = np.asarray(light, np.float64)
+    light = light / np.linalg.norm(light)   # shading.py:77 normalises in float64 then casts
+    p = np.zeros(22, np.float32)
+    p[0:3], p[3:6], p[6:9] = ambient, diffuse, specular
+    p[9:12] = light.astype(np.float32)
+    p[12:15], p[15:18] = material, background
+    p[18], p[19], p[20], p[21] = ao_strength, float(int(exponent)), float(enable_specular), float(inverse_ao)
+    return p
+
+
+# utils/shading.py:148-191
+def shade(gbuffer, params):
+    x = _f32(gbuffer)
+    B, C, H, W = x.shape
+    assert C >= 5
+    prm = _f32(params)
+    out = np.empty((B, 3, H, W), np.float32)
+    lib().orc_shade(_p(x), _p(prm), _p(out), B, C, H, W)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# Frame recurrence (mainVideoUnshaded.py:417-465 / loadedmodel.py:70-121), used as the e2e checker
+# and as the timed CPU baseline.
+def unshaded_sequence(state_dict, low, flow, upsample_mode="bilinear", initial="input", backend="torch",
+                      shade_params=None):
+    """low: B x T x 5 x h x w, flow: B x T x 2 x h x w -> list of T predictions (B x 6 x 4h x 4w)
+    (and shaded RGB frames when shade_params is given)."""
+    low, flow = _f32(low), _f32(flow)
+    B, T = low.shape[:2]
+    preds, rgbs = [], []
+    prev = None
+    for j in range(T):
+        inp = low[:, j]
+        if j == 0:
+            warped = initial_image(inp, 6, initial, False, 4)
+        else:
+            warped = warp_upscale(prev, flow[:, j - 1], 4, special_mask=True, backend=backend)
+        single = np.concatenate([inp, flatten_high(warped, 4, backend=backend)], axis=1)
+        recon, _ = enhancenet_forward(state_dict, single, upsample_mode, "residual", 5, backend=backend)
+        preds.append(recon)
+        prev = postprocess(recon, unshaded=True)
+        if shade_params is not None:
+            rgbs.append(shade(prev, shade_params))
+    return preds, rgbs
+
+
+# ---------------------------------------------------------------------------------------------
+# Synthetic inputs.  Pure numpy so that GPU tests, bench and oracle agree bit for bit.
+def synthetic_gbuffer(B, h, w, seed, T=1):
+    """Analytic scene of random spheres -> low-res G-buffer sequence.
+    Returns low (B,T,5,h,w): mask in [-1,1] (soft edge), unit normals inside, depth in [0.4,0.9];
+    flow (B,T,2,h,w) smooth, |flow| <= 0.02; ao (B,T,1,h,w) in [0.3,1]."""
+    rng = np.random.RandomState(seed)
+    yy, xx = np.meshgrid(np.linspace(-1, 1, h, dtype=np.float32), np.linspace(-1, 1, w, dtype=np.float32), indexing="ij")
+    low = np.zeros((B, T, 5, h, w), np.float32)
+    flow = np.zeros((B, T, 2, h, w), np.float32)
+    ao = np.ones((B, T, 1, h, w), np.float32)
+    for b in range(B):
+        n_s = rng.randint(3, 6)
+        cx, cy = rng.uniform(-0.7, 0.7, n_s), rng.uniform(-0.7, 0.7, n_s)
+        rad = rng.uniform(0.15, 0.45, n_s)
+        vel = rng.uniform(-0.01, 0.01, (n_s, 2))
+        ph = rng.uniform(0, 2 * np.pi, 4)
+        for t in range(T):
+            mask = np.full((h, w), -1.0, np.float32)
+            nrm = np.zeros((3, h, w), np.float32)
+            dep = np.zeros((h, w), np.float32)
+            zbest = np.full((h, w), -1e9, np.float32)
+            for s in range(n_s):
+                dx = (xx - (cx[s] + vel[s, 0] * t)) / rad[s]
+                dy = (yy - (cy[s] + vel[s, 1] * t)) / rad[s]
+                rr = dx * dx + dy * dy
+                inside = rr < 1.0
+                z = np.sqrt(np.clip(1.0 - rr, 0, None)).astype(np.float32)
+                zz = z * rad[s] + 0.1 * s
+                upd = inside & (zz > zbest)
+                zbest = np.where(upd, zz, zbest)
+                edge = np.clip((1.0 - np.sqrt(rr)) * rad[s] * min(h, w) * 0.5, 0, 1).astype(np.float32)
+                mask = np.where(upd, edge * 2 - 1, mask)
+                nrm = np.where(upd[None], np.stack([dx, -dy, z]).astype(np.float32), nrm)
+                dep = np.where(upd, (0.9 - 0.5 * z).astype(np.float32), dep)
+            low[b, t, 0], low[b, t, 1:4], low[b, t, 4] = mask, nrm, dep
+            flow[b, t, 0] = 0.012 * np.sin(2.1 * xx + ph[0] + 0.3 * t) * np.cos(1.3 * yy + ph[1]) + rng.uniform(-0.004, 0.004, (h, w))
+            flow[b, t, 1] = 0.012 * np.cos(1.7 * xx + ph[2]) * np.sin(2.3 * yy + ph[3] + 0.2 * t) + rng.uniform(-0.004, 0.004, (h, w))
+            ao[b, t, 0] = np.clip(0.65 + 0.35 * np.sin(5 * xx + ph[0]) * np.cos(4 * yy + ph[2]), 0.3, 1.0)
+    return low, flow.astype(np.float32), ao
+
+
+def psnr(a, b, epsilon=1e-7):
+    """utils/psnr.py:10-15 (unmasked branch): 10*log10(1/(eps + mean((a-b)^2))), peak = 1."""
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(10.0 * np.log10(1.0 / (epsilon + np.mean((a - b) ** 2))))
