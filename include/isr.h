@@ -1,0 +1,151 @@
+/*
+ * isr.h -- C ABI of libisr.so: the B200 (sm_100a) implementation of the frame-recurrent 4x
+ * EnhanceNet inference path of shamanDevel/IsosurfaceSuperresolution.
+ *
+ * Conventions (modelled on the reference's own FFI, SuperresolutionNetwork/inference/renderer.py:78-117
+ * and GPURendererDirect/GPURendererDirect.cpp:228-246,393-446: plain C functions, int status, the CALLER
+ * allocates every tensor and passes raw device pointers, like `render(CUdeviceptr)` there):
+ *   - every function returns 0 on success and a negative value on error; isr_last_error() returns the
+ *     message of the last error on the calling thread;
+ *   - all tensor pointers are CUDA device pointers unless the name ends in _host; fp32 tensors are NCHW
+ *     contiguous exactly as the reference's torch tensors;
+ *   - launches are asynchronous on `stream` (a cudaStream_t passed as void*; NULL = legacy default stream);
+ *     nothing synchronises unless documented; no function allocates device memory except isr_net_create /
+ *     isr_net_load_weights (packed weights, a few MB) -- activations live in the caller's workspace;
+ *   - there is no CPU path: with no CUDA device every compute entry point fails with ISR_ERR_CUDA.
+ *
+ * Reference paths are relative to /root/reference/SuperresolutionNetwork.
+ */
+#ifndef ISR_H_
+#define ISR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ISR_OK 0
+#define ISR_ERR_ARG (-1)      /* invalid argument (the reference raises AssertionError / ValueError) */
+#define ISR_ERR_CUDA (-2)     /* CUDA runtime / driver error, or no device */
+#define ISR_ERR_WORKSPACE (-3)/* workspace too small */
+#define ISR_ERR_UNSUPPORTED (-4)
+
+/* upsample modes of EnhanceNet (opt.upsample, models/enhancenet.py:40-48) */
+#define ISR_UPSAMPLE_NEAREST 0
+#define ISR_UPSAMPLE_BILINEAR 1
+
+/* initialImage modes (utils/initial_image.py:24-54) */
+#define ISR_INITIAL_ZERO 0
+#define ISR_INITIAL_UNSHADED 1
+#define ISR_INITIAL_INPUT 2
+
+/* Tensor-core operand schemes of the convolution stack (accumulation is always fp32 in TMEM).
+ * "x3" = split operands: A=Ahi+Alo, W=Whi+Wlo, three MMAs (hi*hi + hi*lo + lo*hi) per k-step. */
+#define ISR_PREC_BF16 0        /* single-pass bf16 everywhere (fast; misses 1e-2 with random-init weights) */
+#define ISR_PREC_BF16X3 1      /* split-bf16 everywhere (safe) */
+#define ISR_PREC_MIXED 2       /* DEFAULT: split-bf16 in the low-res trunk, single-pass fp16 in the high-res tail */
+#define ISR_PREC_FP16 3        /* single-pass fp16 everywhere */
+#define ISR_PREC_FP16X3 4      /* split-fp16 everywhere */
+#define ISR_PREC_MIXED2 5      /* split-bf16 trunk, fp16 tail with split activations (2 MMAs per k-step) */
+
+int isr_version(void);
+const char *isr_last_error(void);
+/* number of kernels launched by this library on the calling process since load (bench.py's gpu_launches) */
+uint64_t isr_launch_count(void);
+
+/* ---- memory-bound passes (fp32 NCHW) ------------------------------------------------------------------ */
+
+/* VideoTools.flatten_high (models/videotools.py:8-25): out[b, c*r*r+dy*r+dx, y, x] = in[b, c, y*r+dy, x*r+dx].
+ * in: B x C x H x W, out: B x C*r*r x H/r x W/r.  Bit-exact. */
+int isr_flatten_high(const float *in, float *out, int B, int C, int H, int W, int r, void *stream);
+
+/* VideoTools.warp_upscale (models/videotools.py:49-87): flow*(-2,+2), bilinear x r, + linspace grid,
+ * grid_sample(bilinear, zeros).  align_corners=0 reproduces the installed-torch default (the parity oracle);
+ * 1 = the torch-1.0.1 behaviour the reference was written for.  prev/out: B x C x h*r x w*r, flow: B x 2 x h x w. */
+int isr_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
+                     int special_mask, int align_corners, void *stream);
+
+/* initialImage (utils/initial_image.py:5-54).  in: B x Cin x h x w, out: B x channels x h*r x w*r. */
+int isr_initial_image(const float *in, float *out, int B, int Cin, int h, int w, int channels, int mode,
+                      int ao_inverted, int r, void *stream);
+
+/* inter-frame post-processing (mainVideoUnshaded.py:460-465, mainGUI.py:594-598; mainVideo.py:416):
+ * unshaded: clamp(mask,-1,1), normal/max(|normal|,1e-7), clamp(depth,0,1), clamp(ao,0,1); shaded: clamp(x,0,1). */
+int isr_postprocess(const float *in, float *out, int B, int C, int H, int W, int unshaded, void *stream);
+
+/* ScreenSpaceShading.forward (utils/shading.py:148-191).  params_host: 22 floats on the HOST:
+ * [0..2] ambient, [3..5] diffuse, [6..8] specular, [9..11] light direction (normalised), [12..14] material,
+ * [15..17] background, [18] ao strength, [19] specular exponent, [20] enable_specular, [21] inverse_ao.
+ * gbuf: B x C x H x W (C>=5: mask,nx,ny,nz,depth[,ao]), rgb: B x 3 x H x W. */
+int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, int C, int H, int W, void *stream);
+
+/* ---- EnhanceNet generator (models/enhancenet.py:8-26,92-145) ------------------------------------------- */
+
+typedef struct isr_net isr_net;
+
+/* Mirrors EnhanceNet(upscale_factor=4, input_channels, channel_mask, output_channels, opt): n_mask =
+ * len(channel_mask) (the skip uses inputs[:, 0:n_mask], enhancenet.py:64-66), upsample = opt.upsample,
+ * recon_residual = (opt.reconType == 'residual').  useBN is not supported (fold it first). */
+int isr_net_create(isr_net **net, int input_channels, int output_channels, int n_mask, int upsample,
+                   int recon_residual);
+void isr_net_destroy(isr_net *net);
+
+/* params: 50 DEVICE pointers to fp32 tensors in state_dict order: preblock.0.{weight,bias},
+ * blocks.{0..9}.{0,2}.{weight,bias}, postblock.{1,4,6,8}.{weight,bias} (OIHW).  Packs them into the tensor-core
+ * layouts ([part][tap][Cout][Cin] bf16/fp16 hi+lo).  Synchronises `stream` before returning. */
+int isr_net_load_weights(isr_net *net, const float *const *params, int n_params, void *stream);
+
+/* bytes of caller-provided device workspace needed by isr_net_forward* for a batch of B low-res frames h x w */
+int isr_net_workspace_bytes(const isr_net *net, int B, int h, int w, int precision, size_t *bytes);
+
+/* EnhanceNet.forward(inputs) -> (recon, raw)  (models/enhancenet.py:136-145).
+ * inputs: B x input_channels x h x w.  out_recon / out_raw: B x output_channels x 4h x 4w (either may be NULL).
+ * out_state (optional): post-processed recon (isr_postprocess; unshaded iff output_channels==6 semantics flag). */
+int isr_net_forward(isr_net *net, const float *inputs, float *out_recon, float *out_raw, float *out_state,
+                    int state_unshaded, int B, int h, int w, int precision, void *workspace, size_t workspace_bytes,
+                    void *stream);
+
+/* One frame of the recurrence (mainVideoUnshaded.py:419-465 / inference/loadedmodel.py:70-121) with the previous-frame
+ * path fused: network input = cat(low, flatten_high(warp_upscale(prev, flow, 4, special_mask), 4)) is produced
+ * directly in the convolution's NHWC 16-bit layout, never materialised in fp32.
+ * low: B x c_low x h x w; prev: B x c_prev x 4h x 4w (already the warped/initial image if flow==NULL);
+ * flow: B x 2 x h x w or NULL (= prev is used as is).  c_low + 16*c_prev must equal input_channels. */
+int isr_net_forward_recurrent(isr_net *net, const float *low, const float *prev, const float *flow, int c_low,
+                              int c_prev, int special_mask, int align_corners, float *out_recon, float *out_raw,
+                              float *out_state, int state_unshaded, int B, int h, int w, int precision,
+                              void *workspace, size_t workspace_bytes, void *stream);
+
+/* Same as isr_net_forward_recurrent but low_host / flow_host are (pinned) HOST buffers copied to the device inside
+ * the call, and recon_host (B x Cout x 4h x 4w, HOST) receives the prediction; the recurrent state stays on the
+ * device in state_dev (read as `prev` when has_prev != 0, then overwritten).  Synchronises `stream` before returning.
+ * staging_dev must hold B*(c_low+2)*h*w + B*Cout*16*h*w floats. */
+int isr_net_forward_recurrent_host(isr_net *net, const float *low_host, const float *flow_host, float *state_dev,
+                                   int has_prev, int initial_mode, int c_low, int c_prev, int special_mask,
+                                   float *recon_host, int B, int h, int w, int precision, void *workspace,
+                                   size_t workspace_bytes, float *staging_dev, void *stream);
+
+/* ---- test / bench hooks --------------------------------------------------------------------------------- */
+
+/* One conv3x3(pad 1) 64->cout (cout in {64, <=16}) through the tensor-core kernel, fp32 NCHW in and out, for unit tests:
+ * x: B x 64 x H x W, weight: cout x 64 x 3 x 3, bias: cout, addend: B x 64 x H x W or NULL (only cout==64),
+ * out: B x cout x H x W.  fmt: 0 bf16, 1 fp16; n_act_parts / n_w_parts in {1,2}.  workspace: isr_debug_conv_workspace_bytes. */
+int isr_debug_conv3x3(const float *x, const float *weight, const float *bias, const float *addend, float *out, int B,
+                      int H, int W, int cout, int relu, int fmt, int n_act_parts, int n_w_parts, void *workspace,
+                      size_t workspace_bytes, void *stream);
+int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
+
+/* Tunables of the convolution kernel's shared-memory operand addressing (see DESIGN.md "UMMA descriptors"):
+ * key "halo_pitch" (10 | 16), "base_offset_mode" (0 | 1), "max_ctas" (0 = #SMs).  Returns previous value. */
+int isr_set_tunable(const char *key, int value);
+
+/* Times `iters` back-to-back launches of the network's dominant kernel (the 64->64 conv at 4h x 4w) with CUDA events
+ * on `stream`; returns the average milliseconds per launch in *ms (bench.py's roofline leg). */
+int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scale, void *workspace,
+                      size_t workspace_bytes, int iters, float *ms, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ISR_H_ */

@@ -1,0 +1,330 @@
+// isr_conv.cuh -- conv3x3 (pad 1, Cin = 64 per launch) as an implicit GEMM on tcgen05 tensor cores.
+//
+// Replaces the cuDNN convolutions behind nn.Conv2d in the reference's EnhanceNet
+// (/root/reference/SuperresolutionNetwork/models/enhancenet.py:93-125): preblock, 20 residual-block convs, 4 postblock convs.
+//
+// GEMM view per launch: D[M = pixels, N = Cout] = sum over 9 taps of A_tap[M, K = 64] * W_tap[N, K]^T.
+//   * Activations are NHWC 16-bit (bf16 or fp16), channel dim = 64 * n_parts (hi | lo planes for split precision).
+//   * One CTA tile = 8 px wide x 16 rows = 128 GEMM rows.  Its (8+2) x (16+2) halo is fetched ONCE by a 4-D TMA box
+//     (out-of-bounds = zero fill = the conv's zero padding) into 128B-swizzled shared memory (one pixel = one 128-byte row);
+//     the nine taps are nine UMMA shared-memory descriptors into that same halo tile (start address shifted by
+//     (ky*pitch + kx) rows, 8-row-group stride = pitch*128 B) -- no im2col copy, no re-read.
+//   * All nine taps' weights ([part][tap][Cout][64], K-major, 128B swizzle) stay resident in shared memory for the whole
+//     persistent CTA; accumulators live in TMEM (double buffered: epilogue of tile i overlaps the MMAs of tile i+1).
+//   * Warp roles: warps 0-3 epilogue (TMEM lanes 32w..32w+31), warp 4 TMA producer, warp 5 MMA issuer + TMEM owner.
+//   * Split precision ("x3"): passes (Ahi,Whi), (Ahi,Wlo), (Alo,Whi) accumulate into the same TMEM tile.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "isr_ptx.cuh"
+
+namespace isr {
+
+constexpr int kTileW = 8;
+constexpr int kTileH = 16;
+constexpr int kHaloH = kTileH + 2;
+constexpr int kConvThreads = 192;
+
+enum { EPI_STORE16 = 0, EPI_FINAL = 1 };
+
+struct ConvParams {
+  int B, H, W;
+  int tiles_x, tiles_y, num_tiles;
+  int pitch;             // halo pitch in pixels (10 = exact halo, 16 = 1024B-aligned 8-row groups)
+  int base_offset_mode;  // 1: descriptor base_offset = (start >> 7) & 7
+  int n_act_parts;       // 1 | 2 (input channel dim = 64 * n_act_parts)
+  int n_w_parts;         // 1 | 2
+  int is_bf16;
+  int w_row0;            // first row of this launch's weights inside the weight tensor map
+  int w_row_stride;      // rows between consecutive (part, tap) blocks
+  int num_stages, stage_bytes;
+  int relu;
+  const float *bias;     // N floats (zero padded), or nullptr
+  const uint16_t *addend;  // [B,H,W,64*add_parts] or nullptr
+  int add_parts;
+  uint16_t *out16;       // [B,H,W,64*out_parts]
+  int out_parts;
+  // EPI_FINAL
+  float *out_raw, *out_recon, *out_state;  // B x cout x H x W fp32 NCHW (any may be null)
+  int cout, n_mask, upsample, recon_residual, state_unshaded;
+  const float *skip_src;  // low-res fp32 NCHW input, first n_mask channels used
+  long long skip_bstride;  // floats between batches of skip_src
+  int h_low, w_low;
+};
+
+__device__ __forceinline__ uint32_t pack2(float a, float b, int is_bf16) {
+  if (is_bf16) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+  }
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&v);
+}
+__device__ __forceinline__ float2 unpack2(uint32_t u, int is_bf16) {
+  if (is_bf16) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162 *>(&u));
+  return __half22float2(*reinterpret_cast<__half2 *>(&u));
+}
+
+// torch upsample_bilinear2d(align_corners=False) source index / weights for an integer scale
+__device__ __forceinline__ void bil_src(int dst, int n_in, float inv_scale, int &i0, int &i1, float &l0, float &l1) {
+  float src = inv_scale * (static_cast<float>(dst) + 0.5f) - 0.5f;
+  src = src < 0.f ? 0.f : src;
+  int a = static_cast<int>(src);
+  a = a > n_in - 1 ? n_in - 1 : a;
+  i0 = a;
+  i1 = a < n_in - 1 ? a + 1 : a;
+  float t = src - static_cast<float>(a);
+  t = fminf(fmaxf(t, 0.f), 1.f);
+  l1 = t;
+  l0 = 1.f - t;
+}
+
+template <int N, int EPI>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                    const ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  constexpr uint32_t kWTapBytes = N * 128;               // one (part, tap) weight tile
+  const uint32_t w_bytes = p.n_w_parts * 9 * kWTapBytes;
+  const uint32_t s_w = smem_base;
+  const uint32_t s_stage0 = s_w + ((w_bytes + 1023u) & ~1023u);
+  const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
+  // barrier block: full[8], empty[8], wbar, tmem_full[2], tmem_empty[2], tmem_ptr
+  const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
+                 b_tempty = s_bar + 152, s_tptr = s_bar + 168;
+  __shared__ float s_bias[64];
+
+  if (threadIdx.x < 64) s_bias[threadIdx.x] = (p.bias != nullptr && threadIdx.x < N) ? p.bias[threadIdx.x] : 0.f;
+
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(b_full + 8 * s, 1);
+      mbar_init(b_empty + 8 * s, 1);
+    }
+    mbar_init(b_w, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(b_tfull + 8 * a, 1);
+      mbar_init(b_tempty + 8 * a, 4);
+    }
+    fence_barrier_init();
+  }
+  constexpr uint32_t kTmemCols = (2 * N < 32) ? 32 : 2 * N;
+  if (warp == 5) tmem_alloc(s_tptr, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(s_tptr));
+
+  const int my_tiles = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                       static_cast<int>(gridDim.x);
+
+  if (warp == 4) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(b_w, w_bytes);
+      for (int wp = 0; wp < p.n_w_parts; ++wp)
+        for (int tap = 0; tap < 9; ++tap)
+          tma_load_2d(s_w + (wp * 9 + tap) * kWTapBytes, &tmW, b_w, 0, p.w_row0 + (wp * 9 + tap) * p.w_row_stride);
+      uint32_t it = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        const int t = blockIdx.x + i * gridDim.x;
+        const int tx = t % p.tiles_x;
+        const int ty = (t / p.tiles_x) % p.tiles_y;
+        const int b = t / (p.tiles_x * p.tiles_y);
+        for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+          const uint32_t s = it % p.num_stages;
+          const uint32_t ph = (it / p.num_stages) & 1;
+          mbar_wait(b_empty + 8 * s, ph ^ 1);
+          mbar_arrive_expect_tx(b_full + 8 * s, p.pitch * kHaloH * 128);
+          tma_load_4d(s_stage0 + s * p.stage_bytes, &tmA, b_full + 8 * s, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_f16(128, N, p.is_bf16);
+      const uint32_t sbo = p.pitch * 128;
+      mbar_wait(b_w, 0);
+      uint32_t it = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        const uint32_t acc = i & 1;
+        const uint32_t acc_ph = (i >> 1) & 1;
+        mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * N;
+        uint32_t first = 1;
+        for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+          const uint32_t s = it % p.num_stages;
+          const uint32_t ph = (it / p.num_stages) & 1;
+          mbar_wait(b_full + 8 * s, ph);
+          tc_fence_after();
+          const uint32_t a_base = s_stage0 + s * p.stage_bytes;
+          const int nwp = (ap == 0) ? p.n_w_parts : 1;  // (hi,hi) (hi,lo) | (lo,hi)
+          for (int wp = 0; wp < nwp; ++wp) {
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap) {
+              const uint32_t a_tap = a_base + ((tap / 3) * p.pitch + (tap % 3)) * 128;
+              const uint32_t b_tap = s_w + (wp * 9 + tap) * kWTapBytes;
+              const uint32_t bo = p.base_offset_mode ? ((a_tap >> 7) & 7) : 0;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint64_t adesc = make_smem_desc_sw128(a_tap + k * 32, sbo, bo);
+                const uint64_t bdesc = make_smem_desc_sw128(b_tap + k * 32, 1024, 0);
+                umma_f16(d_tmem, adesc, bdesc, idesc, first ? 0u : 1u);
+                first = 0;
+              }
+            }
+          }
+          umma_commit(b_empty + 8 * s);  // frees this halo stage when its MMAs retire
+        }
+        umma_commit(b_tfull + 8 * acc);  // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue warps 0..3 =====================
+    const int row = warp * 32 + lane;  // GEMM row = TMEM lane
+    const int py = row >> 3, px = row & 7;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int t = blockIdx.x + i * gridDim.x;
+      const int tx = t % p.tiles_x;
+      const int ty = (t / p.tiles_x) % p.tiles_y;
+      const int b = t / (p.tiles_x * p.tiles_y);
+      const uint32_t acc = i & 1;
+      const uint32_t acc_ph = (i >> 1) & 1;
+      mbar_wait(b_tfull + 8 * acc, acc_ph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * N + (static_cast<uint32_t>(warp * 32) << 16);
+      const int y = ty * kTileH + py, x = tx * kTileW + px;
+      const bool inb = (y < p.H) && (x < p.W);
+      if constexpr (EPI == EPI_STORE16) {
+        const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
+#pragma unroll 1
+        for (int ch = 0; ch < N / 16; ++ch) {
+          uint32_t v[16];
+          tmem_ld16(taddr + ch * 16, v);
+          tmem_ld_wait();
+          if (inb) {
+            float f[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + s_bias[ch * 16 + j];
+            if (p.addend != nullptr) {
+              for (int ap = 0; ap < p.add_parts; ++ap) {
+                const uint4 *src =
+                    reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + ch * 16);
+                uint4 q0 = __ldg(src), q1 = __ldg(src + 1);
+                uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  float2 a = unpack2(w[j], p.is_bf16);
+                  f[2 * j] += a.x;
+                  f[2 * j + 1] += a.y;
+                }
+              }
+            }
+            if (p.relu) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
+            }
+            uint32_t hi[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
+            uint4 *dst = reinterpret_cast<uint4 *>(p.out16 + pix * (64 * p.out_parts) + ch * 16);
+            dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+            if (p.out_parts == 2) {
+              uint32_t lo[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float2 h = unpack2(hi[j], p.is_bf16);
+                lo[j] = pack2(f[2 * j] - h.x, f[2 * j + 1] - h.y, p.is_bf16);
+              }
+              uint4 *dl = reinterpret_cast<uint4 *>(p.out16 + pix * 128 + 64 + ch * 16);
+              dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+              dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            }
+          }
+        }
+      } else {
+        // final conv: raw = acc + bias; recon = raw + upsampled skip (enhancenet.py:51-90); optional recurrent state
+        uint32_t v[16];
+        tmem_ld16(taddr, v);
+        tmem_ld_wait();
+        if (inb) {
+          const size_t plane = static_cast<size_t>(p.H) * p.W;
+          const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;
+          float rec[16];
+          int x0, x1, y0, y1;
+          float lx0, lx1, ly0, ly1;
+          if (p.upsample == 1) {
+            bil_src(x, p.w_low, 0.25f, x0, x1, lx0, lx1);
+            bil_src(y, p.h_low, 0.25f, y0, y1, ly0, ly1);
+          } else {
+            x0 = x1 = x >> 2;
+            y0 = y1 = y >> 2;
+            lx0 = ly0 = 1.f;
+            lx1 = ly1 = 0.f;
+          }
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            if (c < p.cout) {
+              float raw = __uint_as_float(v[c]) + s_bias[c];
+              if (p.out_raw != nullptr) p.out_raw[o0 + c * plane] = raw;
+              float r = raw;
+              if (p.recon_residual && c < p.n_mask) {
+                const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(c) * p.h_low * p.w_low;
+                float sk;
+                if (p.upsample == 1) {
+                  float r0 = fmaf(lx0, __ldg(sp + y0 * p.w_low + x0), lx1 * __ldg(sp + y0 * p.w_low + x1));
+                  float r1 = fmaf(lx0, __ldg(sp + y1 * p.w_low + x0), lx1 * __ldg(sp + y1 * p.w_low + x1));
+                  sk = fmaf(ly0, r0, ly1 * r1);
+                } else {
+                  sk = __ldg(sp + y0 * p.w_low + x0);
+                }
+                r = sk + raw;
+              }
+              rec[c] = r;
+              if (p.out_recon != nullptr) p.out_recon[o0 + c * plane] = r;
+            }
+          }
+          if (p.out_state != nullptr) {
+            if (p.state_unshaded && p.cout >= 5) {
+              // mainVideoUnshaded.py:460-465: clamp mask, normalise normal (shading.py:193-207), clamp depth / ao
+              p.out_state[o0] = fminf(fmaxf(rec[0], -1.f), 1.f);
+              float len = sqrtf(rec[1] * rec[1] + rec[2] * rec[2] + rec[3] * rec[3]);
+              len = fmaxf(len, 1e-7f);
+              p.out_state[o0 + plane] = rec[1] / len;
+              p.out_state[o0 + 2 * plane] = rec[2] / len;
+              p.out_state[o0 + 3 * plane] = rec[3] / len;
+#pragma unroll
+              for (int c = 4; c < 16; ++c)
+                if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+            } else {
+#pragma unroll
+              for (int c = 0; c < 16; ++c)
+                if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(b_tempty + 8 * acc);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+}  // namespace isr

@@ -1,0 +1,30 @@
+// isr_internal.h -- declarations shared between the translation units of libisr.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace isr {
+
+void count_launch();
+
+cudaError_t launch_flatten_high(const float *in, float *out, int B, int C, int H, int W, int r, cudaStream_t s);
+cudaError_t launch_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
+                                int special_mask, int align_corners, cudaStream_t s);
+cudaError_t launch_initial_image(const float *in, float *out, int B, int Cin, int h, int w, int channels, int mode,
+                                 int ao_inverted, int r, cudaStream_t s);
+cudaError_t launch_postprocess(const float *in, float *out, int B, int C, int H, int W, int unshaded, cudaStream_t s);
+cudaError_t launch_shade(const float *in, const float *params22_host, float *out, int B, int C, int H, int W,
+                         cudaStream_t s);
+cudaError_t launch_pack_recurrent(const float *low, const float *prev, const float *flow, uint16_t *g0, uint16_t *g1,
+                                  int B, int c_low, int c_prev, int h, int w, int special_mask, int align_corners,
+                                  int nparts, int is_bf16, cudaStream_t s);
+cudaError_t launch_pack_nchw(const float *in, uint16_t *g0, uint16_t *g1, int B, int cin, int h, int w, int nparts,
+                             int is_bf16, cudaStream_t s);
+cudaError_t launch_unpack_nhwc(const uint16_t *in, float *out, int B, int H, int W, int nparts, int is_bf16,
+                               cudaStream_t s);
+cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, int w, int in_parts, int out_parts,
+                              int in_bf16, int out_bf16, int bilinear, cudaStream_t s);
+// out layout: [fmt 2 (bf16, fp16)][part 2 (hi, lo)][tap 9][group G][npad][64]
+cudaError_t launch_pack_weights(const float *w, uint16_t *out, int cout, int cin, int npad, int G, cudaStream_t s);
+
+}  // namespace isr

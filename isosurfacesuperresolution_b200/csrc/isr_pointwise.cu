@@ -1,0 +1,564 @@
+// isr_pointwise.cu -- the memory-bound passes of the path: warp + space-to-depth + concat (network-input packing),
+// flatten_high, initialImage, inter-frame post-processing, screen-space shading, NHWC 2x upsampling, weight packing.
+// Compiled with -fmad=false: the fused multiply-adds that the parity contract needs are written
+// explicitly as fmaf(); everything else must round like the reference's separate fp32 multiplies and adds.
+//
+// Reference paths are relative to /root/reference/SuperresolutionNetwork.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "isr_internal.h"
+
+namespace isr {
+
+// ------------------------------------------------------------------------------------------------------------
+// shared device helpers
+__device__ __forceinline__ void bil_src_pw(int dst, int n_in, float inv_scale, int &i0, int &i1, float &l0, float &l1) {
+  // torch upsample_bilinear2d, align_corners=False: src = max(0, inv_scale*(dst+0.5)-0.5)
+  float src = inv_scale * (static_cast<float>(dst) + 0.5f) - 0.5f;
+  src = src < 0.f ? 0.f : src;
+  int a = static_cast<int>(src);
+  a = a > n_in - 1 ? n_in - 1 : a;
+  i0 = a;
+  i1 = a < n_in - 1 ? a + 1 : a;
+  float t = src - static_cast<float>(a);
+  t = fminf(fmaxf(t, 0.f), 1.f);
+  l1 = t;
+  l0 = 1.f - t;
+}
+
+__device__ __forceinline__ float bil_sample(const float *__restrict__ p, int w, int y0, int y1, int x0, int x1,
+                                            float ly0, float ly1, float lx0, float lx1, float scale) {
+  // x first, then y; FMA placement pinned by SURVEY 7.4
+  float r0 = fmaf(lx0, scale * __ldg(p + y0 * w + x0), lx1 * (scale * __ldg(p + y0 * w + x1)));
+  float r1 = fmaf(lx0, scale * __ldg(p + y1 * w + x0), lx1 * (scale * __ldg(p + y1 * w + x1)));
+  return fmaf(ly0, r0, ly1 * r1);
+}
+
+// torch.linspace(-1, 1, n)[i] in fp32 (symmetric evaluation from both ends)
+__device__ __forceinline__ float lin_m1p1(int i, int n) {
+  if (n == 1) return -1.f;
+  float step = 2.0f / static_cast<float>(n - 1);
+  if (i < n / 2) return fmaf(step, static_cast<float>(i), -1.f);
+  return fmaf(-step, static_cast<float>(n - 1 - i), 1.f);
+}
+
+struct WarpTaps {
+  float nw, ne, sw, se;
+  int x0, y0;
+  bool vx0, vx1, vy0, vy1;
+};
+
+// models/videotools.py:65-81: flow*(-2,+2) -> bilinear x r -> + linspace grid -> grid_sample coordinates
+__device__ __forceinline__ WarpTaps warp_taps(const float *__restrict__ flow_b, int h, int w, int r, int y, int x,
+                                              int align_corners) {
+  const int H = h * r, W = w * r;
+  const float inv = 1.0f / static_cast<float>(r);
+  int fx0, fx1, fy0, fy1;
+  float lx0, lx1, ly0, ly1;
+  bil_src_pw(x, w, inv, fx0, fx1, lx0, lx1);
+  bil_src_pw(y, h, inv, fy0, fy1, ly0, ly1);
+  const float Fx = bil_sample(flow_b, w, fy0, fy1, fx0, fx1, ly0, ly1, lx0, lx1, -2.f);
+  const float Fy = bil_sample(flow_b + static_cast<size_t>(h) * w, w, fy0, fy1, fx0, fx1, ly0, ly1, lx0, lx1, 2.f);
+  const float gx = lin_m1p1(x, W) + Fx;
+  const float gy = lin_m1p1(y, H) + Fy;
+  float ix, iy;
+  if (align_corners) {  // ((g+1)/2)*(size-1)
+    ix = ((gx + 1.f) / 2.f) * static_cast<float>(W - 1);
+    iy = ((gy + 1.f) / 2.f) * static_cast<float>(H - 1);
+  } else {  // ((g+1)*size-1)/2
+    ix = fmaf(gx + 1.f, static_cast<float>(W), -1.f) / 2.f;
+    iy = fmaf(gy + 1.f, static_cast<float>(H), -1.f) / 2.f;
+  }
+  const float x0f = floorf(ix), y0f = floorf(iy);
+  const float x1f = x0f + 1.f, y1f = y0f + 1.f;
+  WarpTaps t;
+  t.nw = (x1f - ix) * (y1f - iy);
+  t.ne = (ix - x0f) * (y1f - iy);
+  t.sw = (x1f - ix) * (iy - y0f);
+  t.se = (ix - x0f) * (iy - y0f);
+  const bool okx = (x0f >= -2.f) && (x0f <= static_cast<float>(W) + 1.f);
+  const bool oky = (y0f >= -2.f) && (y0f <= static_cast<float>(H) + 1.f);
+  t.x0 = okx ? static_cast<int>(x0f) : -5;
+  t.y0 = oky ? static_cast<int>(y0f) : -5;
+  t.vx0 = t.x0 >= 0 && t.x0 < W;
+  t.vx1 = t.x0 + 1 >= 0 && t.x0 + 1 < W;
+  t.vy0 = t.y0 >= 0 && t.y0 < H;
+  t.vy1 = t.y0 + 1 >= 0 && t.y0 + 1 < H;
+  return t;
+}
+
+// grid_sample (bilinear, zeros padding) of one channel plane; special mask remap of videotools.py:77-85
+__device__ __forceinline__ float warp_gather(const float *__restrict__ p, int W, const WarpTaps &t, bool sm) {
+  float acc = 0.f;
+  const float *r0 = p + static_cast<size_t>(t.y0) * W + t.x0;
+  const float *r1 = r0 + W;
+  if (t.vy0 && t.vx0) { float v = __ldg(r0); if (sm) v = v * 0.5f + 0.5f; acc += v * t.nw; }
+  if (t.vy0 && t.vx1) { float v = __ldg(r0 + 1); if (sm) v = v * 0.5f + 0.5f; acc += v * t.ne; }
+  if (t.vy1 && t.vx0) { float v = __ldg(r1); if (sm) v = v * 0.5f + 0.5f; acc += v * t.sw; }
+  if (t.vy1 && t.vx1) { float v = __ldg(r1 + 1); if (sm) v = v * 0.5f + 0.5f; acc += v * t.se; }
+  if (sm) acc = acc * 2.f - 1.f;
+  return acc;
+}
+
+__device__ __forceinline__ uint32_t pack2_pw(float a, float b, int is_bf16) {
+  if (is_bf16) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&v);
+  }
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&v);
+}
+__device__ __forceinline__ float2 unpack2_pw(uint32_t u, int is_bf16) {
+  if (is_bf16) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162 *>(&u));
+  return __half22float2(*reinterpret_cast<__half2 *>(&u));
+}
+
+// 8 fp32 channels -> 16 B of hi (and 16 B of lo = x - hi) in NHWC 16-bit
+__device__ __forceinline__ void store_chunk8(uint16_t *dst_pix, int chunk, int nparts, const float *f, int is_bf16) {
+  uint32_t hi[4], lo[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    hi[j] = pack2_pw(f[2 * j], f[2 * j + 1], is_bf16);
+    float2 hf = unpack2_pw(hi[j], is_bf16);
+    lo[j] = pack2_pw(f[2 * j] - hf.x, f[2 * j + 1] - hf.y, is_bf16);
+  }
+  *reinterpret_cast<uint4 *>(dst_pix + chunk * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  if (nparts == 2) *reinterpret_cast<uint4 *>(dst_pix + 64 + chunk * 8) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// VideoTools.flatten_high (models/videotools.py:8-25)
+__global__ void flatten_high_kernel(const float *__restrict__ in, float *__restrict__ out, int B, int C, int H, int W,
+                                    int r) {
+  const int h = H / r, w = W / r;
+  const size_t total = static_cast<size_t>(B) * C * H * W;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    // i indexes the INPUT (coalesced reads); scatter to the output
+    const int X = static_cast<int>(i % W);
+    const int Y = static_cast<int>((i / W) % H);
+    const int c = static_cast<int>((i / (static_cast<size_t>(W) * H)) % C);
+    const int b = static_cast<int>(i / (static_cast<size_t>(W) * H * C));
+    const int oc = c * r * r + (Y % r) * r + (X % r);
+    out[((static_cast<size_t>(b) * C * r * r + oc) * h + Y / r) * w + X / r] = in[i];
+  }
+}
+
+// VideoTools.warp_upscale (models/videotools.py:49-87), fp32 NCHW in / out
+__global__ void warp_upscale_kernel(const float *__restrict__ prev, const float *__restrict__ flow,
+                                    float *__restrict__ out, int B, int C, int h, int w, int r, int special_mask,
+                                    int align_corners) {
+  const int H = h * r, W = w * r;
+  const size_t plane = static_cast<size_t>(H) * W;
+  const size_t total = static_cast<size_t>(B) * plane;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = static_cast<int>(i % W);
+    const int y = static_cast<int>((i / W) % H);
+    const int b = static_cast<int>(i / plane);
+    const WarpTaps t = warp_taps(flow + static_cast<size_t>(b) * 2 * h * w, h, w, r, y, x, align_corners);
+    for (int c = 0; c < C; ++c)
+      out[(static_cast<size_t>(b) * C + c) * plane + static_cast<size_t>(y) * W + x] =
+          warp_gather(prev + (static_cast<size_t>(b) * C + c) * plane, W, t, special_mask && c == 0);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Network-input packing for the recurrent form: cat(low, flatten_high(warp_upscale(prev, flow))) written directly as
+// NHWC 16-bit hi|lo planes in 64-channel groups (videotools.py:8-25,49-87 + mainVideoUnshaded.py:441-445 fused).
+// One block = 16 low-res pixels of one row = 64 x 4 high-res pixels = 256 threads.
+constexpr int kPackLow = 16;
+__global__ void __launch_bounds__(256)
+pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ prev, const float *__restrict__ flow,
+                      uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int B, int c_low, int c_prev, int h,
+                      int w, int special_mask, int align_corners, int nparts, int is_bf16) {
+  __shared__ float tile[kPackLow][129];
+  const int xb = blockIdx.x * kPackLow;
+  const int y = blockIdx.y;
+  const int b = blockIdx.z;
+  const int H = h * 4, W = w * 4;
+  const int tid = threadIdx.x;
+  const int cin = c_low + 16 * c_prev;
+  for (int i = tid; i < kPackLow * 128; i += 256) tile[i >> 7][i & 127] = 0.f;
+  __syncthreads();
+  for (int i = tid; i < kPackLow * c_low; i += 256) {
+    const int lp = i % kPackLow, c = i / kPackLow;
+    if (xb + lp < w) tile[lp][c] = __ldg(low + ((static_cast<size_t>(b) * c_low + c) * h + y) * w + xb + lp);
+  }
+  {
+    const int dy = tid >> 6, hx = tid & 63;
+    const int X = xb * 4 + hx, Y = y * 4 + dy;
+    if (X < W) {
+      const size_t plane = static_cast<size_t>(H) * W;
+      const float *pb = prev + static_cast<size_t>(b) * c_prev * plane;
+      const int lp = hx >> 2, dx = hx & 3;
+      if (flow != nullptr) {
+        const WarpTaps t = warp_taps(flow + static_cast<size_t>(b) * 2 * h * w, h, w, 4, Y, X, align_corners);
+        for (int c = 0; c < c_prev; ++c)
+          tile[lp][c_low + c * 16 + dy * 4 + dx] = warp_gather(pb + c * plane, W, t, special_mask && c == 0);
+      } else {
+        for (int c = 0; c < c_prev; ++c)
+          tile[lp][c_low + c * 16 + dy * 4 + dx] = __ldg(pb + c * plane + static_cast<size_t>(Y) * W + X);
+      }
+    }
+  }
+  __syncthreads();
+  const int ngroups = (cin + 63) / 64;
+  for (int i = tid; i < kPackLow * 8 * ngroups; i += 256) {
+    const int chunk = i & 7, lp = (i >> 3) % kPackLow, g = i / (8 * kPackLow);
+    if (xb + lp >= w) continue;
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = tile[lp][g * 64 + chunk * 8 + j];
+    uint16_t *dst = (g == 0 ? out_g0 : out_g1) + ((static_cast<size_t>(b) * h + y) * w + xb + lp) * (64 * nparts);
+    store_chunk8(dst, chunk, nparts, f, is_bf16);
+  }
+}
+
+// Network-input packing for the 1-argument form EnhanceNet.forward(inputs): fp32 NCHW -> NHWC 16-bit groups
+__global__ void __launch_bounds__(256)
+pack_nchw_kernel(const float *__restrict__ in, uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int B,
+                 int cin, int h, int w, int nparts, int is_bf16) {
+  __shared__ float tile[kPackLow][129];
+  const int xb = blockIdx.x * kPackLow, y = blockIdx.y, b = blockIdx.z, tid = threadIdx.x;
+  for (int i = tid; i < kPackLow * 128; i += 256) {
+    const int lp = i % kPackLow, c = i / kPackLow;
+    float v = 0.f;
+    if (c < cin && xb + lp < w) v = __ldg(in + ((static_cast<size_t>(b) * cin + c) * h + y) * w + xb + lp);
+    tile[lp][c] = v;
+  }
+  __syncthreads();
+  const int ngroups = (cin + 63) / 64;
+  for (int i = tid; i < kPackLow * 8 * ngroups; i += 256) {
+    const int chunk = i & 7, lp = (i >> 3) % kPackLow, g = i / (8 * kPackLow);
+    if (xb + lp >= w) continue;
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = tile[lp][g * 64 + chunk * 8 + j];
+    uint16_t *dst = (g == 0 ? out_g0 : out_g1) + ((static_cast<size_t>(b) * h + y) * w + xb + lp) * (64 * nparts);
+    store_chunk8(dst, chunk, nparts, f, is_bf16);
+  }
+}
+
+// debug / unit tests: NHWC 16-bit (sum of parts) -> fp32 NCHW, 64 channels
+__global__ void unpack_nhwc_kernel(const uint16_t *__restrict__ in, float *__restrict__ out, int B, int H, int W,
+                                   int nparts, int is_bf16) {
+  const size_t total = static_cast<size_t>(B) * H * W * 64;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i & 63);
+    const size_t pix = i >> 6;
+    float v = 0.f;
+    for (int pt = 0; pt < nparts; ++pt) {
+      const uint16_t u = in[pix * (64 * nparts) + pt * 64 + c];
+      v += is_bf16 ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16 *>(&u))
+                   : __half2float(*reinterpret_cast<const __half *>(&u));
+    }
+    const int x = static_cast<int>(pix % W), y = static_cast<int>((pix / W) % H);
+    const int b = static_cast<int>(pix / (static_cast<size_t>(W) * H));
+    out[((static_cast<size_t>(b) * 64 + c) * H + y) * W + x] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// initialImage (utils/initial_image.py:5-54)
+__global__ void initial_image_kernel(const float *__restrict__ in, float *__restrict__ out, int B, int Cin, int h, int w,
+                                     int channels, int mode, int ao_inverted, int r) {
+  const int H = h * r, W = w * r;
+  const size_t plane = static_cast<size_t>(H) * W;
+  const size_t total = static_cast<size_t>(B) * channels * plane;
+  const float inv = 1.0f / static_cast<float>(r);
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = static_cast<int>(i % W), y = static_cast<int>((i / W) % H);
+    const int c = static_cast<int>((i / plane) % channels);
+    const int b = static_cast<int>(i / (plane * channels));
+    float v = 0.f;
+    if (mode == 1) {  // 'unshaded' defaults: mask=-1, normal=(0,0,1), depth=0.5, ao=1 (0 if inverted)
+      v = c == 0 ? -1.f : (c == 3 ? 1.f : (c == 4 ? 0.5f : (c == 5 ? (ao_inverted ? 0.f : 1.f) : 0.f)));
+    } else if (mode == 2) {  // 'input': bilinear x r of the current input, padded with ones
+      if (c < Cin) {
+        int x0, x1, y0, y1;
+        float lx0, lx1, ly0, ly1;
+        bil_src_pw(x, w, inv, x0, x1, lx0, lx1);
+        bil_src_pw(y, h, inv, y0, y1, ly0, ly1);
+        v = bil_sample(in + (static_cast<size_t>(b) * Cin + c) * h * w, w, y0, y1, x0, x1, ly0, ly1, lx0, lx1, 1.f);
+      } else {
+        v = 1.f;
+      }
+    }
+    out[i] = v;
+  }
+}
+
+// inter-frame post-processing (mainVideoUnshaded.py:460-465; shading.py:193-207; mainVideo.py:416)
+__global__ void postprocess_kernel(const float *__restrict__ in, float *__restrict__ out, int B, int C, int H, int W,
+                                   int unshaded) {
+  const size_t plane = static_cast<size_t>(H) * W;
+  const size_t total = static_cast<size_t>(B) * plane;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t b = i / plane, o = b * C * plane + (i % plane);
+    if (!unshaded) {
+      for (int c = 0; c < C; ++c) out[o + c * plane] = fminf(fmaxf(in[o + c * plane], 0.f), 1.f);
+      continue;
+    }
+    out[o] = fminf(fmaxf(in[o], -1.f), 1.f);
+    const float nx = in[o + plane], ny = in[o + 2 * plane], nz = in[o + 3 * plane];
+    float len = sqrtf(nx * nx + ny * ny + nz * nz);
+    len = fmaxf(len, 1e-7f);
+    out[o + plane] = nx / len;
+    out[o + 2 * plane] = ny / len;
+    out[o + 3 * plane] = nz / len;
+    for (int c = 4; c < C; ++c) out[o + c * plane] = fminf(fmaxf(in[o + c * plane], 0.f), 1.f);
+  }
+}
+
+// ScreenSpaceShading.forward (utils/shading.py:148-191): one pass, one thread per pixel (4 pixels when W % 4 == 0)
+struct ShadeParams {
+  float v[22];
+};
+__device__ __forceinline__ void shade_pixel(const ShadeParams &s, float m, float nx, float ny, float nz, float aoin,
+                                            bool has_ao, float sf, float *rgb) {
+  const float aos = s.v[18];
+  const int expo = static_cast<int>(s.v[19]);
+  const bool spec = s.v[20] != 0.f, inv = s.v[21] != 0.f;
+  float ao = 1.f;
+  if (has_ao) {
+    float a = inv ? 1.f - aoin : aoin;
+    a = fminf(fmaxf(a, 0.f), 1.f);
+    ao = aos * a + (1.f - aos) * 1.f;
+  }
+  const float ldn = s.v[9] * nx + s.v[10] * ny + s.v[11] * nz;
+  const float diff = fabsf(ldn);
+  float sfac = 0.f;
+  if (spec) {
+    float cz = fminf(fmaxf(2.f * ldn * nz - s.v[11], 0.f), 1.f);  // reflect . (0,0,1)
+    float pw = 1.f;
+    for (int k = 0; k < expo; ++k) pw *= cz;
+    sfac = sf * pw;
+  }
+  const float mk = fminf(fmaxf(m * 0.5f + 0.5f, 0.f), 1.f);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float col = 0.f;
+    col += s.v[c] * s.v[12 + c];
+    col += (s.v[3 + c] * s.v[12 + c]) * diff;
+    if (spec) col += sfac * s.v[6 + c];
+    col *= ao;
+    const float bg = s.v[15 + c];
+    rgb[c] = fminf(fmaxf(bg + mk * (col - bg), 0.f), 1.f);
+  }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams s, float sf, int B, int C, size_t plane) {
+  const size_t nvec = plane / VEC;
+  const size_t total = static_cast<size_t>(B) * nvec;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t b = i / nvec, q = (i % nvec) * VEC;
+    const float *p = in + b * C * plane + q;
+    float *o = out + b * 3 * plane + q;
+    float m[VEC], nx[VEC], ny[VEC], nz[VEC], ao[VEC];
+    if constexpr (VEC == 4) {
+      float4 t;
+      t = __ldcs(reinterpret_cast<const float4 *>(p)); m[0] = t.x; m[1] = t.y; m[2] = t.z; m[3] = t.w;
+      t = __ldcs(reinterpret_cast<const float4 *>(p + plane)); nx[0] = t.x; nx[1] = t.y; nx[2] = t.z; nx[3] = t.w;
+      t = __ldcs(reinterpret_cast<const float4 *>(p + 2 * plane)); ny[0] = t.x; ny[1] = t.y; ny[2] = t.z; ny[3] = t.w;
+      t = __ldcs(reinterpret_cast<const float4 *>(p + 3 * plane)); nz[0] = t.x; nz[1] = t.y; nz[2] = t.z; nz[3] = t.w;
+      if (C >= 6) {
+        t = __ldcs(reinterpret_cast<const float4 *>(p + 5 * plane)); ao[0] = t.x; ao[1] = t.y; ao[2] = t.z; ao[3] = t.w;
+      }
+    } else {
+      m[0] = p[0]; nx[0] = p[plane]; ny[0] = p[2 * plane]; nz[0] = p[3 * plane];
+      if (C >= 6) ao[0] = p[5 * plane];
+    }
+    float rgb[VEC][3];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) shade_pixel(s, m[j], nx[j], ny[j], nz[j], C >= 6 ? ao[j] : 1.f, C >= 6, sf, rgb[j]);
+    if constexpr (VEC == 4) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        __stcs(reinterpret_cast<float4 *>(o + c * plane), make_float4(rgb[0][c], rgb[1][c], rgb[2][c], rgb[3][c]));
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[c * plane] = rgb[0][c];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// nn.Upsample(scale_factor=2, mode) on NHWC 16-bit 64-channel features (enhancenet.py:40-48,116,119)
+// one thread = one output pixel x 8 channels (16 B); input parts are summed in fp32, output re-split.
+__global__ void __launch_bounds__(256)
+upsample2x_nhwc_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out, int B, int h, int w, int in_parts,
+                       int out_parts, int in_bf16, int out_bf16, int bilinear) {
+  const int H = 2 * h, W = 2 * w;
+  const size_t total = static_cast<size_t>(B) * H * W * 8;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int chunk = static_cast<int>(i & 7);
+    const size_t pix = i >> 3;
+    const int X = static_cast<int>(pix % W), Y = static_cast<int>((pix / W) % H);
+    const size_t b = pix / (static_cast<size_t>(W) * H);
+    int x0, x1, y0, y1;
+    float lx0, lx1, ly0, ly1;
+    if (bilinear) {
+      bil_src_pw(X, w, 0.5f, x0, x1, lx0, lx1);
+      bil_src_pw(Y, h, 0.5f, y0, y1, ly0, ly1);
+    } else {
+      x0 = x1 = X >> 1; y0 = y1 = Y >> 1;
+      lx0 = ly0 = 1.f; lx1 = ly1 = 0.f;
+    }
+    float v[4][8];
+    const int ys[4] = {y0, y0, y1, y1}, xs[4] = {x0, x1, x0, x1};
+    const int ntap = bilinear ? 4 : 1;
+    for (int t = 0; t < ntap; ++t) {
+      const uint16_t *src = in + ((b * h + ys[t]) * w + xs[t]) * (64 * in_parts) + chunk * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[t][j] = 0.f;
+      for (int pt = 0; pt < in_parts; ++pt) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(src + pt * 64));
+        const uint32_t u[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f2 = unpack2_pw(u[j], in_bf16);
+          v[t][2 * j] += f2.x;
+          v[t][2 * j + 1] += f2.y;
+        }
+      }
+    }
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (bilinear) {
+        const float r0 = fmaf(lx0, v[0][j], lx1 * v[1][j]);
+        const float r1 = fmaf(lx0, v[2][j], lx1 * v[3][j]);
+        f[j] = fmaf(ly0, r0, ly1 * r1);
+      } else {
+        f[j] = v[0][j];
+      }
+    }
+    store_chunk8(out + pix * (64 * out_parts), chunk, out_parts, f, out_bf16);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// weight packing: fp32 OIHW [cout][cin][3][3] -> [fmt 2][part 2][tap 9][group G][npad][64] 16-bit (fmt 0 = bf16, 1 = fp16)
+__global__ void pack_weights_kernel(const float *__restrict__ w, uint16_t *__restrict__ out, int cout, int cin, int npad,
+                                    int G) {
+  const int per_fmt = 2 * 9 * G * npad * 64;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < per_fmt / 2; i += gridDim.x * blockDim.x) {
+    // i enumerates (tap, g, n, k); both parts and both formats are produced here
+    const int k = i & 63;
+    const int n = (i >> 6) % npad;
+    const int g = (i / (64 * npad)) % G;
+    const int tap = i / (64 * npad * G);
+    const int ci = g * 64 + k;
+    const float v = (n < cout && ci < cin) ? w[(static_cast<size_t>(n) * cin + ci) * 9 + tap] : 0.f;
+    const size_t part_stride = static_cast<size_t>(9) * G * npad * 64;
+    const size_t o = ((static_cast<size_t>(tap) * G + g) * npad + n) * 64 + k;
+    const __nv_bfloat16 bh = __float2bfloat16_rn(v);
+    const __nv_bfloat16 bl = __float2bfloat16_rn(v - __bfloat162float(bh));
+    const __half hh = __float2half_rn(v);
+    const __half hl = __float2half_rn(v - __half2float(hh));
+    out[o] = *reinterpret_cast<const uint16_t *>(&bh);
+    out[part_stride + o] = *reinterpret_cast<const uint16_t *>(&bl);
+    out[per_fmt + o] = *reinterpret_cast<const uint16_t *>(&hh);
+    out[per_fmt + part_stride + o] = *reinterpret_cast<const uint16_t *>(&hl);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// host launchers
+static inline int grid_for(size_t total, int block) {
+  size_t g = (total + block - 1) / block;
+  const size_t cap = 148 * 16;  // grid-stride loops; a multiple of the SM count
+  return static_cast<int>(g < cap ? (g == 0 ? 1 : g) : cap);
+}
+
+cudaError_t launch_flatten_high(const float *in, float *out, int B, int C, int H, int W, int r, cudaStream_t s) {
+  const size_t total = static_cast<size_t>(B) * C * H * W;
+  flatten_high_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, C, H, W, r);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
+                                int special_mask, int align_corners, cudaStream_t s) {
+  const size_t total = static_cast<size_t>(B) * h * r * w * r;
+  warp_upscale_kernel<<<grid_for(total, 256), 256, 0, s>>>(prev, flow, out, B, C, h, w, r, special_mask, align_corners);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_initial_image(const float *in, float *out, int B, int Cin, int h, int w, int channels, int mode,
+                                 int ao_inverted, int r, cudaStream_t s) {
+  const size_t total = static_cast<size_t>(B) * channels * h * r * w * r;
+  initial_image_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, Cin, h, w, channels, mode, ao_inverted, r);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_postprocess(const float *in, float *out, int B, int C, int H, int W, int unshaded, cudaStream_t s) {
+  const size_t total = static_cast<size_t>(B) * H * W;
+  postprocess_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, C, H, W, unshaded);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_shade(const float *in, const float *params22, float *out, int B, int C, int H, int W,
+                         cudaStream_t s) {
+  ShadeParams sp;
+  for (int i = 0; i < 22; ++i) sp.v[i] = params22[i];
+  const int expo = static_cast<int>(params22[19]);
+  const float sf = static_cast<float>((static_cast<double>(expo) + 2.0) / (2.0 * 3.14159265358979323846));
+  const size_t plane = static_cast<size_t>(H) * W;
+  const bool vec = (plane % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
+  if (vec)
+    shade_kernel<4><<<grid_for(B * plane / 4, 256), 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+  else
+    shade_kernel<1><<<grid_for(B * plane, 256), 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_pack_recurrent(const float *low, const float *prev, const float *flow, uint16_t *g0, uint16_t *g1,
+                                  int B, int c_low, int c_prev, int h, int w, int special_mask, int align_corners,
+                                  int nparts, int is_bf16, cudaStream_t s) {
+  dim3 grid((w + kPackLow - 1) / kPackLow, h, B);
+  pack_recurrent_kernel<<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
+                                            align_corners, nparts, is_bf16);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_pack_nchw(const float *in, uint16_t *g0, uint16_t *g1, int B, int cin, int h, int w, int nparts,
+                             int is_bf16, cudaStream_t s) {
+  dim3 grid((w + kPackLow - 1) / kPackLow, h, B);
+  pack_nchw_kernel<<<grid, 256, 0, s>>>(in, g0, g1, B, cin, h, w, nparts, is_bf16);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_unpack_nhwc(const uint16_t *in, float *out, int B, int H, int W, int nparts, int is_bf16,
+                               cudaStream_t s) {
+  const size_t total = static_cast<size_t>(B) * H * W * 64;
+  unpack_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, H, W, nparts, is_bf16);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, int w, int in_parts, int out_parts,
+                              int in_bf16, int out_bf16, int bilinear, cudaStream_t s) {
+  const size_t total = static_cast<size_t>(B) * 4 * h * w * 8;
+  upsample2x_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, h, w, in_parts, out_parts, in_bf16, out_bf16,
+                                                             bilinear);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_pack_weights(const float *w, uint16_t *out, int cout, int cin, int npad, int G, cudaStream_t s) {
+  const int n = 9 * G * npad * 64;
+  pack_weights_kernel<<<(n + 255) / 256, 256, 0, s>>>(w, out, cout, cin, npad, G);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace isr
