@@ -1,0 +1,20 @@
+# Builds libisr.so (sm_100a only) in-tree and the CPU oracle (test infrastructure).
+NVCC ?= /usr/local/cuda/bin/nvcc
+ARCH = -gencode arch=compute_100a,code=sm_100a
+PKG = isosurfacesuperresolution_b200
+CSRC = $(PKG)/csrc
+NVFLAGS = $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xptxas -v
+LIB = $(PKG)/libisr.so
+
+all: $(LIB) oracle
+$(CSRC)/isr_api.o: $(CSRC)/isr_api.cu $(CSRC)/isr_conv.cuh $(CSRC)/isr_ptx.cuh $(CSRC)/isr_internal.h include/isr.h
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+$(CSRC)/isr_pointwise.o: $(CSRC)/isr_pointwise.cu $(CSRC)/isr_internal.h
+	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
+$(LIB): $(CSRC)/isr_api.o $(CSRC)/isr_pointwise.o
+	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart static
+oracle:
+	$(MAKE) -C oracle -s
+clean:
+	rm -f $(CSRC)/*.o $(LIB)
+.PHONY: all oracle clean

@@ -182,4 +182,504 @@ static bool get_schemes(int precision, Scheme *trunk, Scheme *tail) {
   return false;
 }
 
+// ---- the network ------------------------------------------------------------------------------------------------
+struct Layer {
+  int cin = 0, cout = 0, npad = 0, G = 0;
+  uint16_t *packed = nullptr;  // [fmt 2][part 2][tap 9][G][npad][64]
+  float *bias = nullptr;       // npad floats, zero padded
+  size_t per_fmt() const { return static_cast<size_t>(2) * 9 * G * npad * 64; }
+  int rows() const { return 2 * 9 * G * npad; }
+};
+
+struct Plan {
+  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0;
+  void *ws = nullptr;
+  Scheme trunk, tail;
+  uint16_t *in_g[2] = {nullptr, nullptr};
+  std::vector<ConvLaunch> convs;  // in execution order
+  // pointwise steps interleaved with convs: up2 after conv index up_after[0], up4 after up_after[1]
+  uint16_t *f_last = nullptr, *u2 = nullptr, *c2 = nullptr, *u4 = nullptr, *c4 = nullptr;
+  int idx_post1 = 0, idx_post4 = 0, idx_final = 0;
+};
+
 }  // namespace isr
+
+struct isr_net {
+  int cin, cout, n_mask, upsample, recon_residual;
+  int G;  // 64-channel input groups of the first conv
+  isr::Layer layers[25];
+  bool loaded = false;
+  std::vector<isr::Plan *> plans;
+};
+
+namespace isr {
+
+static size_t plan_bytes(const isr_net *net, int B, int h, int w, const Scheme &trunk, const Scheme &tail,
+                         size_t *offs /* 9 offsets */) {
+  const size_t P = static_cast<size_t>(B) * h * w;
+  const size_t lo = align_up(P * 128 * trunk.na, 1024);
+  const size_t t2 = align_up(P * 4 * 128 * tail.na, 1024);
+  const size_t t4 = align_up(P * 16 * 128 * tail.na, 1024);
+  size_t o = 0;
+  size_t tmp[9];
+  if (offs == nullptr) offs = tmp;
+  offs[0] = o; o += lo;                       // in_g0
+  offs[1] = o; o += (net->G == 2 ? lo : 0);   // in_g1
+  offs[2] = o; o += (net->G == 2 ? lo : 0);   // partial
+  offs[3] = o; o += lo;                       // f0
+  offs[4] = o; o += lo;                       // f1
+  offs[5] = o; o += lo;                       // t
+  offs[6] = o; o += 2 * t2;                   // u2, c2
+  offs[7] = o; o += t4;                       // u4
+  offs[8] = o; o += t4;                       // c4
+  return o;
+}
+
+static void set_store(ConvLaunch *L, const float *bias, int relu, const uint16_t *addend, int add_parts, uint16_t *out,
+                      int out_parts) {
+  L->p.bias = bias;
+  L->p.relu = relu;
+  L->p.addend = addend;
+  L->p.add_parts = add_parts;
+  L->p.out16 = out;
+  L->p.out_parts = out_parts;
+}
+
+static int conv_for_layer(ConvLaunch *L, const Layer &ly, int g, const uint16_t *act, int B, int H, int W,
+                          const Scheme &sc) {
+  const uint16_t *wbase = ly.packed + (sc.bf16 ? 0 : ly.per_fmt());
+  return init_conv(L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16);
+}
+
+static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
+  if (!get_schemes(precision, &pl->trunk, &pl->tail)) return fail(ISR_ERR_ARG, "unknown precision %d", precision);
+  size_t offs[9];
+  const size_t need = plan_bytes(net, B, h, w, pl->trunk, pl->tail, offs);
+  if (ws == nullptr || ws_bytes < need)
+    return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, need);
+  if (reinterpret_cast<uintptr_t>(ws) % 1024 != 0) return fail(ISR_ERR_ARG, "workspace must be 1024-byte aligned");
+  pl->B = B; pl->h = h; pl->w = w; pl->precision = precision; pl->ws = ws;
+  pl->pitch = g_halo_pitch; pl->bo = g_base_offset_mode; pl->max_ctas = g_max_ctas;
+  uint8_t *base = static_cast<uint8_t *>(ws);
+  auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
+  const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
+  pl->in_g[0] = at(0);
+  pl->in_g[1] = net->G == 2 ? at(1) : nullptr;
+  uint16_t *partial = at(2), *f0 = at(3), *f1 = at(4), *t = at(5);
+  pl->u2 = at(6);
+  pl->c2 = reinterpret_cast<uint16_t *>(base + offs[6] + t2);
+  pl->u4 = at(7);
+  pl->c4 = at(8);
+  const Scheme &T = pl->trunk, &Hs = pl->tail;
+  pl->convs.clear();
+  ConvLaunch L;
+  int rc;
+  // preblock (enhancenet.py:93-95): one launch per 64-channel input group; the second adds the first's partial sums
+  if (net->G == 1) {
+    if ((rc = conv_for_layer(&L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
+    set_store(&L, net->layers[0].bias, 1, nullptr, 0, f0, T.na);
+    pl->convs.push_back(L);
+  } else {
+    if ((rc = conv_for_layer(&L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
+    set_store(&L, nullptr, 0, nullptr, 0, partial, T.na);
+    pl->convs.push_back(L);
+    if ((rc = conv_for_layer(&L, net->layers[0], 1, pl->in_g[1], B, h, w, T)) != ISR_OK) return rc;
+    set_store(&L, net->layers[0].bias, 1, partial, T.na, f0, T.na);
+    pl->convs.push_back(L);
+  }
+  // 10 residual blocks (enhancenet.py:108-112,140-141): f = f + conv(relu(conv(f)))
+  uint16_t *fc = f0, *fn = f1;
+  for (int blk = 0; blk < 10; ++blk) {
+    if ((rc = conv_for_layer(&L, net->layers[1 + 2 * blk], 0, fc, B, h, w, T)) != ISR_OK) return rc;
+    set_store(&L, net->layers[1 + 2 * blk].bias, 1, nullptr, 0, t, T.na);
+    pl->convs.push_back(L);
+    if ((rc = conv_for_layer(&L, net->layers[2 + 2 * blk], 0, t, B, h, w, T)) != ISR_OK) return rc;
+    set_store(&L, net->layers[2 + 2 * blk].bias, 0, fc, T.na, fn, T.na);
+    pl->convs.push_back(L);
+    uint16_t *sw = fc; fc = fn; fn = sw;
+  }
+  pl->f_last = fc;
+  // postblock (enhancenet.py:115-125): up2 -> conv -> relu -> up2 -> conv -> relu -> conv -> relu -> conv
+  pl->idx_post1 = static_cast<int>(pl->convs.size());
+  if ((rc = conv_for_layer(&L, net->layers[21], 0, pl->u2, B, 2 * h, 2 * w, Hs)) != ISR_OK) return rc;
+  set_store(&L, net->layers[21].bias, 1, nullptr, 0, pl->c2, Hs.na);
+  pl->convs.push_back(L);
+  pl->idx_post4 = static_cast<int>(pl->convs.size());
+  if ((rc = conv_for_layer(&L, net->layers[22], 0, pl->u4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
+  set_store(&L, net->layers[22].bias, 1, nullptr, 0, pl->c4, Hs.na);
+  pl->convs.push_back(L);
+  if ((rc = conv_for_layer(&L, net->layers[23], 0, pl->c4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
+  set_store(&L, net->layers[23].bias, 1, nullptr, 0, pl->u4, Hs.na);
+  pl->convs.push_back(L);
+  pl->idx_final = static_cast<int>(pl->convs.size());
+  if ((rc = conv_for_layer(&L, net->layers[24], 0, pl->u4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
+  L.p.bias = net->layers[24].bias;
+  L.p.cout = net->cout;
+  L.p.n_mask = net->n_mask;
+  L.p.upsample = net->upsample;
+  L.p.recon_residual = net->recon_residual;
+  L.p.h_low = h;
+  L.p.w_low = w;
+  pl->convs.push_back(L);
+  return ISR_OK;
+}
+
+static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
+  for (Plan *pl : net->plans)
+    if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
+        pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas) {
+      *out = pl;
+      return ISR_OK;
+    }
+  Plan *pl = new Plan();
+  int rc = build_plan(net, pl, B, h, w, precision, ws, ws_bytes);
+  if (rc != ISR_OK) {
+    delete pl;
+    return rc;
+  }
+  if (net->plans.size() >= 16) {  // bounded cache
+    delete net->plans.front();
+    net->plans.erase(net->plans.begin());
+  }
+  net->plans.push_back(pl);
+  *out = pl;
+  return ISR_OK;
+}
+
+// runs everything after the network-input packing
+static int run_plan(isr_net *net, Plan *pl, const float *skip_src, long long skip_bstride, float *out_recon,
+                    float *out_raw, float *out_state, int state_unshaded, cudaStream_t s) {
+  const Scheme &T = pl->trunk, &Hs = pl->tail;
+  int rc;
+  for (int i = 0; i < static_cast<int>(pl->convs.size()); ++i) {
+    if (i == pl->idx_post1)
+      ISR_CUDA(launch_upsample2x(pl->f_last, pl->u2, pl->B, pl->h, pl->w, T.na, Hs.na, T.bf16, Hs.bf16,
+                                 net->upsample == ISR_UPSAMPLE_BILINEAR, s));
+    if (i == pl->idx_post4)
+      ISR_CUDA(launch_upsample2x(pl->c2, pl->u4, pl->B, 2 * pl->h, 2 * pl->w, Hs.na, Hs.na, Hs.bf16, Hs.bf16,
+                                 net->upsample == ISR_UPSAMPLE_BILINEAR, s));
+    if (i == pl->idx_final) {
+      ConvParams &p = pl->convs[i].p;
+      p.out_raw = out_raw;
+      p.out_recon = out_recon;
+      p.out_state = out_state;
+      p.state_unshaded = state_unshaded;
+      p.skip_src = skip_src;
+      p.skip_bstride = skip_bstride;
+    }
+    if ((rc = run_conv(pl->convs[i], s)) != ISR_OK) return rc;
+  }
+  return ISR_OK;
+}
+
+}  // namespace isr
+
+// ================================================================================================================
+// C ABI
+// ================================================================================================================
+using namespace isr;
+
+static cudaStream_t S(void *stream) { return static_cast<cudaStream_t>(stream); }
+
+static int check_device() {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(ISR_ERR_CUDA, "no CUDA device: libisr has no CPU path");
+  }
+  return ISR_OK;
+}
+
+extern "C" {
+
+int isr_version(void) { return 100; }
+const char *isr_last_error(void) { return g_err.c_str(); }
+uint64_t isr_launch_count(void) { return g_launches.load(); }
+
+int isr_set_tunable(const char *key, int value) {
+  int *slot = nullptr;
+  if (key != nullptr && strcmp(key, "halo_pitch") == 0) {
+    if (value != 10 && value != 16) return fail(ISR_ERR_ARG, "halo_pitch must be 10 or 16");
+    slot = &g_halo_pitch;
+  } else if (key != nullptr && strcmp(key, "base_offset_mode") == 0) {
+    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "base_offset_mode must be 0 or 1");
+    slot = &g_base_offset_mode;
+  } else if (key != nullptr && strcmp(key, "max_ctas") == 0) {
+    if (value < 0) return fail(ISR_ERR_ARG, "max_ctas must be >= 0");
+    slot = &g_max_ctas;
+  } else {
+    return fail(ISR_ERR_ARG, "unknown tunable");
+  }
+  int old = *slot;
+  *slot = value;
+  return old;
+}
+
+int isr_flatten_high(const float *in, float *out, int B, int C, int H, int W, int r, void *stream) {
+  if (in == nullptr || out == nullptr || B <= 0 || C <= 0 || r <= 0 || H <= 0 || W <= 0 || H % r != 0 || W % r != 0)
+    return fail(ISR_ERR_ARG, "flatten_high: bad shape (H, W must be multiples of the upscale factor)");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_flatten_high(in, out, B, C, H, W, r, S(stream)));
+  return ISR_OK;
+}
+
+int isr_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
+                     int special_mask, int align_corners, void *stream) {
+  if (prev == nullptr || flow == nullptr || out == nullptr || B <= 0 || C <= 0 || h <= 0 || w <= 0 || r <= 0)
+    return fail(ISR_ERR_ARG, "warp_upscale: bad arguments");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_warp_upscale(prev, flow, out, B, C, h, w, r, special_mask, align_corners, S(stream)));
+  return ISR_OK;
+}
+
+int isr_initial_image(const float *in, float *out, int B, int Cin, int h, int w, int channels, int mode,
+                      int ao_inverted, int r, void *stream) {
+  if (mode < 0 || mode > 2) return fail(ISR_ERR_ARG, "unknown input mode");
+  if (mode == ISR_INITIAL_UNSHADED && channels != 5 && channels != 6)
+    return fail(ISR_ERR_ARG, "for mode='unshaded', channels is expected to be 5 or 6");
+  if (in == nullptr || out == nullptr || B <= 0 || Cin <= 0 || h <= 0 || w <= 0 || channels <= 0 || r <= 0)
+    return fail(ISR_ERR_ARG, "initial_image: bad arguments");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_initial_image(in, out, B, Cin, h, w, channels, mode, ao_inverted, r, S(stream)));
+  return ISR_OK;
+}
+
+int isr_postprocess(const float *in, float *out, int B, int C, int H, int W, int unshaded, void *stream) {
+  if (in == nullptr || out == nullptr || B <= 0 || C <= 0 || H <= 0 || W <= 0 || (unshaded && C < 5))
+    return fail(ISR_ERR_ARG, "postprocess: bad arguments");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_postprocess(in, out, B, C, H, W, unshaded, S(stream)));
+  return ISR_OK;
+}
+
+int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, int C, int H, int W, void *stream) {
+  if (gbuf == nullptr || params_host == nullptr || rgb == nullptr || B <= 0 || H <= 0 || W <= 0)
+    return fail(ISR_ERR_ARG, "shade: bad arguments");
+  if (C < 5) return fail(ISR_ERR_ARG, "shade: input must have at least 5 channels (shading.py:150)");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_shade(gbuf, params_host, rgb, B, C, H, W, S(stream)));
+  return ISR_OK;
+}
+
+int isr_net_create(isr_net **out, int input_channels, int output_channels, int n_mask, int upsample,
+                   int recon_residual) {
+  if (out == nullptr) return fail(ISR_ERR_ARG, "net_create: null output");
+  if (input_channels <= 0 || input_channels > 128)
+    return fail(ISR_ERR_UNSUPPORTED, "input_channels must be in [1,128] (got %d)", input_channels);
+  if (output_channels <= 0 || output_channels > 16)
+    return fail(ISR_ERR_UNSUPPORTED, "output_channels must be in [1,16] (got %d)", output_channels);
+  if (upsample != ISR_UPSAMPLE_NEAREST && upsample != ISR_UPSAMPLE_BILINEAR)
+    return fail(ISR_ERR_UNSUPPORTED, "upsample must be nearest or bilinear");
+  if (recon_residual && n_mask > output_channels)
+    return fail(ISR_ERR_ARG, "number of output channels must be at least the number of masked input channels");
+  if (n_mask < 0 || n_mask > input_channels) return fail(ISR_ERR_ARG, "bad channel mask length");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  isr_net *net = new isr_net();
+  net->cin = input_channels;
+  net->cout = output_channels;
+  net->n_mask = n_mask;
+  net->upsample = upsample;
+  net->recon_residual = recon_residual;
+  net->G = (input_channels + 63) / 64;
+  for (int i = 0; i < 25; ++i) {
+    Layer &ly = net->layers[i];
+    ly.cin = i == 0 ? input_channels : 64;
+    ly.cout = i == 24 ? output_channels : 64;
+    ly.npad = i == 24 ? 16 : 64;
+    ly.G = i == 0 ? net->G : 1;
+    if (cudaMalloc(&ly.packed, 2 * ly.per_fmt() * sizeof(uint16_t)) != cudaSuccess ||
+        cudaMalloc(&ly.bias, 64 * sizeof(float)) != cudaSuccess) {
+      isr_net_destroy(net);
+      return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
+    }
+  }
+  *out = net;
+  return ISR_OK;
+}
+
+void isr_net_destroy(isr_net *net) {
+  if (net == nullptr) return;
+  for (Plan *pl : net->plans) delete pl;
+  for (int i = 0; i < 25; ++i) {
+    if (net->layers[i].packed) cudaFree(net->layers[i].packed);
+    if (net->layers[i].bias) cudaFree(net->layers[i].bias);
+  }
+  delete net;
+}
+
+int isr_net_load_weights(isr_net *net, const float *const *params, int n_params, void *stream) {
+  if (net == nullptr || params == nullptr || n_params != 50)
+    return fail(ISR_ERR_ARG, "load_weights: expected 50 parameter tensors (useBN=False state_dict)");
+  for (int i = 0; i < 25; ++i) {
+    Layer &ly = net->layers[i];
+    if (params[2 * i] == nullptr || params[2 * i + 1] == nullptr) return fail(ISR_ERR_ARG, "load_weights: null tensor");
+    ISR_CUDA(launch_pack_weights(params[2 * i], ly.packed, ly.cout, ly.cin, ly.npad, ly.G, S(stream)));
+    ISR_CUDA(cudaMemsetAsync(ly.bias, 0, 64 * sizeof(float), S(stream)));
+    ISR_CUDA(cudaMemcpyAsync(ly.bias, params[2 * i + 1], ly.cout * sizeof(float), cudaMemcpyDeviceToDevice, S(stream)));
+  }
+  ISR_CUDA(cudaStreamSynchronize(S(stream)));
+  net->loaded = true;
+  return ISR_OK;
+}
+
+int isr_net_workspace_bytes(const isr_net *net, int B, int h, int w, int precision, size_t *bytes) {
+  Scheme t, hs;
+  if (net == nullptr || bytes == nullptr || B <= 0 || h <= 0 || w <= 0) return fail(ISR_ERR_ARG, "workspace: bad arguments");
+  if (!get_schemes(precision, &t, &hs)) return fail(ISR_ERR_ARG, "unknown precision %d", precision);
+  *bytes = plan_bytes(net, B, h, w, t, hs, nullptr);
+  return ISR_OK;
+}
+
+static int forward_common(isr_net *net, int B, int h, int w, int precision, void *ws, size_t ws_bytes, Plan **pl) {
+  if (net == nullptr || B <= 0 || h <= 0 || w <= 0) return fail(ISR_ERR_ARG, "forward: bad arguments");
+  if (!net->loaded) return fail(ISR_ERR_ARG, "forward: weights not loaded");
+  int rc = setup_kernel_attrs();
+  if (rc != ISR_OK) return rc;
+  return get_plan(net, pl, B, h, w, precision, ws, ws_bytes);
+}
+
+int isr_net_forward(isr_net *net, const float *inputs, float *out_recon, float *out_raw, float *out_state,
+                    int state_unshaded, int B, int h, int w, int precision, void *workspace, size_t workspace_bytes,
+                    void *stream) {
+  if (inputs == nullptr) return fail(ISR_ERR_ARG, "forward: null input");
+  Plan *pl = nullptr;
+  int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_pack_nchw(inputs, pl->in_g[0], pl->in_g[1], B, net->cin, h, w, pl->trunk.na, pl->trunk.bf16, S(stream)));
+  return run_plan(net, pl, inputs, static_cast<long long>(net->cin) * h * w, out_recon, out_raw, out_state,
+                  state_unshaded, S(stream));
+}
+
+int isr_net_forward_recurrent(isr_net *net, const float *low, const float *prev, const float *flow, int c_low,
+                              int c_prev, int special_mask, int align_corners, float *out_recon, float *out_raw,
+                              float *out_state, int state_unshaded, int B, int h, int w, int precision,
+                              void *workspace, size_t workspace_bytes, void *stream) {
+  if (low == nullptr || prev == nullptr) return fail(ISR_ERR_ARG, "forward_recurrent: null input");
+  if (net != nullptr && c_low + 16 * c_prev != net->cin)
+    return fail(ISR_ERR_ARG, "forward_recurrent: c_low + 16*c_prev (%d) != input_channels (%d)", c_low + 16 * c_prev,
+                net->cin);
+  if (net != nullptr && net->n_mask > c_low) return fail(ISR_ERR_ARG, "forward_recurrent: channel mask longer than c_low");
+  Plan *pl = nullptr;
+  int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_pack_recurrent(low, prev, flow, pl->in_g[0], pl->in_g[1], B, c_low, c_prev, h, w, special_mask,
+                                 align_corners, pl->trunk.na, pl->trunk.bf16, S(stream)));
+  return run_plan(net, pl, low, static_cast<long long>(c_low) * h * w, out_recon, out_raw, out_state, state_unshaded,
+                  S(stream));
+}
+
+int isr_net_forward_recurrent_host(isr_net *net, const float *low_host, const float *flow_host, float *state_dev,
+                                   int has_prev, int initial_mode, int c_low, int c_prev, int special_mask,
+                                   float *recon_host, int B, int h, int w, int precision, void *workspace,
+                                   size_t workspace_bytes, float *staging_dev, void *stream) {
+  if (net == nullptr || low_host == nullptr || state_dev == nullptr || recon_host == nullptr || staging_dev == nullptr)
+    return fail(ISR_ERR_ARG, "forward_recurrent_host: null argument");
+  if (has_prev && flow_host == nullptr) return fail(ISR_ERR_ARG, "forward_recurrent_host: flow required");
+  const size_t n_low = static_cast<size_t>(B) * c_low * h * w, n_flow = static_cast<size_t>(B) * 2 * h * w;
+  const size_t n_out = static_cast<size_t>(B) * net->cout * 16 * h * w;
+  float *low_d = staging_dev, *flow_d = staging_dev + n_low, *recon_d = staging_dev + n_low + n_flow;
+  cudaStream_t s = S(stream);
+  ISR_CUDA(cudaMemcpyAsync(low_d, low_host, n_low * sizeof(float), cudaMemcpyHostToDevice, s));
+  if (has_prev) ISR_CUDA(cudaMemcpyAsync(flow_d, flow_host, n_flow * sizeof(float), cudaMemcpyHostToDevice, s));
+  int rc;
+  if (!has_prev) {
+    rc = isr_initial_image(low_d, state_dev, B, c_low, h, w, c_prev, initial_mode, 0, 4, stream);
+    if (rc != ISR_OK) return rc;
+  }
+  rc = isr_net_forward_recurrent(net, low_d, state_dev, has_prev ? flow_d : nullptr, c_low, c_prev, special_mask, 0,
+                                 recon_d, nullptr, state_dev, net->cout == 6, B, h, w, precision, workspace,
+                                 workspace_bytes, stream);
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(cudaMemcpyAsync(recon_host, recon_d, n_out * sizeof(float), cudaMemcpyDeviceToHost, s));
+  ISR_CUDA(cudaStreamSynchronize(s));
+  return ISR_OK;
+}
+
+int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scale, void *workspace,
+                      size_t workspace_bytes, int iters, float *ms, void *stream) {
+  if (ms == nullptr || iters <= 0 || (scale != 1 && scale != 4)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");
+  Plan *pl = nullptr;
+  int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
+  if (rc != ISR_OK) return rc;
+  // scale 4: postblock.4 (64->64 at 4h x 4w, the dominant kernel); scale 1: first residual-block conv (h x w)
+  const ConvLaunch &L = pl->convs[scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1)];
+  cudaEvent_t e0, e1;
+  ISR_CUDA(cudaEventCreate(&e0));
+  ISR_CUDA(cudaEventCreate(&e1));
+  if ((rc = run_conv(L, S(stream))) != ISR_OK) return rc;  // warm-up
+  ISR_CUDA(cudaEventRecord(e0, S(stream)));
+  for (int i = 0; i < iters; ++i)
+    if ((rc = run_conv(L, S(stream))) != ISR_OK) return rc;
+  ISR_CUDA(cudaEventRecord(e1, S(stream)));
+  ISR_CUDA(cudaEventSynchronize(e1));
+  float t = 0.f;
+  ISR_CUDA(cudaEventElapsedTime(&t, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *ms = t / iters;
+  return ISR_OK;
+}
+
+int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes) {
+  if (bytes == nullptr || B <= 0 || H <= 0 || W <= 0) return fail(ISR_ERR_ARG, "bad arguments");
+  const size_t act = align_up(static_cast<size_t>(B) * H * W * 256, 1024);
+  *bytes = 3 * act + align_up(2 * 2 * 9 * 64 * 64 * sizeof(uint16_t), 1024) + 1024;
+  return ISR_OK;
+}
+
+int isr_debug_conv3x3(const float *x, const float *weight, const float *bias, const float *addend, float *out, int B,
+                      int H, int W, int cout, int relu, int fmt, int n_act_parts, int n_w_parts, void *workspace,
+                      size_t workspace_bytes, void *stream) {
+  if (x == nullptr || weight == nullptr || out == nullptr || workspace == nullptr)
+    return fail(ISR_ERR_ARG, "debug_conv: null argument");
+  if (!(cout == 64 || (cout >= 1 && cout <= 16)) || (fmt != 0 && fmt != 1) || n_act_parts < 1 || n_act_parts > 2 ||
+      n_w_parts < 1 || n_w_parts > 2 || (addend != nullptr && cout != 64))
+    return fail(ISR_ERR_ARG, "debug_conv: unsupported configuration");
+  size_t need = 0;
+  isr_debug_conv_workspace_bytes(B, H, W, &need);
+  if (workspace_bytes < need) return fail(ISR_ERR_WORKSPACE, "debug_conv: workspace too small (%zu < %zu)", workspace_bytes, need);
+  if (reinterpret_cast<uintptr_t>(workspace) % 1024 != 0) return fail(ISR_ERR_ARG, "workspace must be 1024-byte aligned");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  if ((rc = setup_kernel_attrs()) != ISR_OK) return rc;
+  cudaStream_t s = S(stream);
+  const int is_bf16 = fmt == 0;
+  const int npad = cout == 64 ? 64 : 16;
+  const size_t act = align_up(static_cast<size_t>(B) * H * W * 256, 1024);
+  uint8_t *base = static_cast<uint8_t *>(workspace);
+  uint16_t *in16 = reinterpret_cast<uint16_t *>(base), *add16 = reinterpret_cast<uint16_t *>(base + act),
+           *out16 = reinterpret_cast<uint16_t *>(base + 2 * act), *wp = reinterpret_cast<uint16_t *>(base + 3 * act);
+  float *bias_d = reinterpret_cast<float *>(base + 3 * act + align_up(2 * 2 * 9 * 64 * 64 * sizeof(uint16_t), 1024));
+  ISR_CUDA(launch_pack_nchw(x, in16, nullptr, B, 64, H, W, n_act_parts, is_bf16, s));
+  if (addend != nullptr) ISR_CUDA(launch_pack_nchw(addend, add16, nullptr, B, 64, H, W, n_act_parts, is_bf16, s));
+  ISR_CUDA(launch_pack_weights(weight, wp, cout, 64, npad, 1, s));
+  ISR_CUDA(cudaMemsetAsync(bias_d, 0, 64 * sizeof(float), s));
+  if (bias != nullptr) ISR_CUDA(cudaMemcpyAsync(bias_d, bias, cout * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  const size_t per_fmt = static_cast<size_t>(2) * 9 * npad * 64;
+  ConvLaunch L;
+  rc = init_conv(&L, npad, in16, B, H, W, n_act_parts, wp + (is_bf16 ? 0 : per_fmt), 2 * 9 * npad, 0, npad, n_w_parts,
+                 is_bf16);
+  if (rc != ISR_OK) return rc;
+  if (cout == 64) {
+    set_store(&L, bias_d, relu, addend != nullptr ? add16 : nullptr, n_act_parts, out16, 2);
+    if ((rc = run_conv(L, s)) != ISR_OK) return rc;
+    ISR_CUDA(launch_unpack_nhwc(out16, out, B, H, W, 2, is_bf16, s));
+  } else {
+    L.p.bias = bias_d;
+    L.p.cout = cout;
+    L.p.out_raw = out;
+    L.p.h_low = H / 4 > 0 ? H / 4 : 1;
+    L.p.w_low = W / 4 > 0 ? W / 4 : 1;
+    if ((rc = run_conv(L, s)) != ISR_OK) return rc;
+  }
+  return ISR_OK;
+}
+
+}  // extern "C"
