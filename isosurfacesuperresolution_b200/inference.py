@@ -1,0 +1,145 @@
+"""Inference facade: drop-in for the reference's ``inference.loadedmodel.LoadedModel``
+(/root/reference/SuperresolutionNetwork/inference/loadedmodel.py:8-121) plus ``SequenceRunner``, the forward-only frame
+recurrence of the training / PSNR scripts (mainVideoUnshaded.py:417-465, mainPSNR1.py:148-180) on the fused kernels.
+"""
+import os.path
+
+import numpy as np
+import torch
+
+from .enhancenet import EnhanceNet
+from .initial_image import initialImage
+from .shading import ScreenSpaceShading
+
+
+def _as_dropin(model):
+    if isinstance(model, EnhanceNet):
+        return model
+    if model.__class__.__name__ == "EnhanceNet":        # a reference module, e.g. from a whole-module pickle
+        return EnhanceNet.from_reference(model)
+    raise TypeError("only EnhanceNet generators are on the B200 path, got " + model.__class__.__name__)
+
+
+class LoadedModel:
+    """``LoadedModel(name, device, upscale_factor)``; ``name`` is a checkpoint path as in the reference, or a dict
+    ``{'model': module, 'parameters': {...}}`` / a module (convenience for tests)."""
+
+    def __init__(self, name, device, upscale_factor):
+        self.device = device
+        self.upscale_factor = upscale_factor
+        if isinstance(name, (str, bytes, os.PathLike)):
+            self.name = os.path.splitext(os.path.basename(name))[0]
+            # whole-module pickles (mainVideoUnshaded.py:799-811) need weights_only=False; only for trusted files
+            checkpoint = torch.load(name, map_location="cpu", weights_only=False)
+        else:
+            self.name = "model"
+            checkpoint = name if isinstance(name, dict) else {"model": name}
+        self.parameters = checkpoint.get("parameters", dict())
+        if not isinstance(self.parameters, dict):
+            self.parameters = vars(self.parameters)
+        self.model = _as_dropin(checkpoint["model"]).to(device)
+        self.model.train(False)
+
+        # first leaf module decides the channel layout (loadedmodel.py:26-55)
+        first_module = self.model
+        while True:
+            children = list(first_module.children())
+            if not children:
+                break
+            first_module = children[0]
+        self.input_channels = first_module.in_channels
+        if self.input_channels == 5 + 6 * (self.upscale_factor ** 2) or self.parameters.get("unshaded", False):
+            self.unshaded = True
+        else:
+            self.unshaded = False
+            self.input_single_channels = self.input_channels - 3 * (self.upscale_factor ** 2)
+            self.has_normal = self.input_single_channels >= 7
+            if self.has_normal:
+                self.input_single_channels -= 3
+            self.has_depth = self.input_single_channels >= 5
+            if self.has_depth:
+                self.input_single_channels -= 1
+        if "initialImage" not in self.parameters:
+            self.initial_image_mode = "input" if self.unshaded else "zero"
+        else:
+            self.initial_image_mode = self.parameters["initialImage"]
+        self.inverse_ao = self.parameters.get("aoInverted", False)
+
+    @staticmethod
+    def _inpaint_flow(current_low):
+        """loadedmodel.py:77-82: Navier-Stokes in-painting of the flow where mask == 0, on the host (OpenCV), as the
+        reference does.  (A GPU in-painter is SURVEY.md section 8f rank 1 -- not built yet.)"""
+        import cv2 as cv
+        cpu = current_low.detach().cpu().numpy()
+        out = np.empty((cpu.shape[0], 2) + cpu.shape[2:], np.float32)
+        for b in range(cpu.shape[0]):
+            hole = np.uint8(cpu[b, 3] == 0)
+            out[b, 0] = cv.inpaint(cpu[b, 8], hole, 3, cv.INPAINT_NS)
+            out[b, 1] = cv.inpaint(cpu[b, 9], hole, 3, cv.INPAINT_NS)
+        return torch.from_numpy(out).to(current_low.device)
+
+    def inference(self, current_low, prev_high, inpaint_flow=True):
+        """current_low: B x >=10 x h x w renderer output (RGB, mask, normal, depth, flow, ...) on the GPU;
+        prev_high: previous high-res result or None.  Returns the prediction B x Cout x 4h x 4w."""
+        with torch.no_grad():
+            current_low = current_low.to(self.device)
+            flow = self._inpaint_flow(current_low) if inpaint_flow else current_low[:, 8:10].contiguous()
+            if self.unshaded:
+                inp = torch.cat((current_low[:, 3:4] * 2 - 1, current_low[:, 4:8]), dim=1)
+                if prev_high is None:
+                    prev = initialImage(inp, 6, self.initial_image_mode, self.inverse_ao, self.upscale_factor)
+                    prediction, _ = self.model(inp, prev, None)
+                else:
+                    prediction, _ = self.model(inp, prev_high.to(self.device), flow, special_mask=True)
+            else:
+                if self.has_normal and self.has_depth:
+                    inp = torch.clamp(current_low[:, 0:8], 0, 1)
+                elif self.has_normal:
+                    inp = current_low[:, 0:7]
+                elif self.has_depth:
+                    inp = torch.cat((current_low[:, 0:4], current_low[:, 7:8]), dim=1)
+                else:
+                    inp = current_low[:, 0:4]
+                if prev_high is None:
+                    # loadedmodel.py:110 passes upscale_factor as aoInverted (harmless for 'zero'); reproduced
+                    prev_high = initialImage(inp, 3, self.initial_image_mode, self.upscale_factor)
+                prediction, _ = self.model(inp, prev_high.to(self.device), flow, special_mask=False)
+        return prediction
+
+
+class SequenceRunner:
+    """Forward-only frame recurrence over a batch of independent sequences (mainVideoUnshaded.py:417-465).
+
+    ``low``: B x T x c_low x h x w, ``flow``: B x T x 2 x h x w (CUDA).  Per frame: fused warp + space-to-depth + concat
+    -> EnhanceNet -> fused clamp/normalise state; optional shading of every frame."""
+
+    def __init__(self, model, initial_image="input", shading=None):
+        self.model = _as_dropin(model)
+        self.initial_image = initial_image
+        self.shading = shading
+        self.unshaded = self.model.output_channels == 6
+
+    @torch.no_grad()
+    def run(self, low, flow, keep_outputs=True):
+        B, T = low.shape[:2]
+        c_prev = self.model.output_channels
+        preds, rgbs = [], []
+        state = None
+        for j in range(T):
+            inp = low[:, j].contiguous()
+            if j == 0:
+                prev = initialImage(inp, c_prev, self.initial_image, False, 4)
+                pred, _, state = self.model(inp, prev, None, return_state=True)
+            else:
+                pred, _, state = self.model(inp, state, flow[:, j - 1].contiguous(), special_mask=self.unshaded,
+                                            return_state=True)
+            if self.shading is not None:
+                rgb = self.shading(state)
+                if keep_outputs:
+                    rgbs.append(rgb)
+            if keep_outputs:
+                preds.append(pred)
+        return preds, rgbs, state
+
+
+__all__ = ["LoadedModel", "SequenceRunner", "ScreenSpaceShading"]

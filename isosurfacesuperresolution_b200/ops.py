@@ -1,0 +1,207 @@
+"""Torch-tensor front end of the C ABI: device memory and streams come from PyTorch, the arithmetic from libisr.so.
+
+Every function requires CUDA fp32 tensors and raises otherwise -- there is no CPU path.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import INITIAL, PREC, UPSAMPLE, IsrError, check, lib
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _prep(t, name):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name}: expected a torch.Tensor")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name}: the B200 path needs CUDA tensors (got {t.device}); there is no CPU fallback")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def flatten_high(image_high, upscale_factor):
+    """VideoTools.flatten_high (models/videotools.py:8-25)."""
+    x = _prep(image_high, "image_high")
+    B, C, H, W = x.shape
+    r = int(upscale_factor)
+    assert H % r == 0 and W % r == 0
+    out = torch.empty((B, C * r * r, H // r, W // r), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        check(lib().isr_flatten_high(_p(x), _p(out), B, C, H, W, r, _stream()))
+    return out
+
+
+def warp_upscale(image_high, flow_low, upscale_factor, special_mask=False, align_corners=False):
+    """VideoTools.warp_upscale (models/videotools.py:49-87)."""
+    img, flow = _prep(image_high, "image_high"), _prep(flow_low, "flow_low")
+    B, C, H, W = img.shape
+    Bf, two, h, w = flow.shape
+    r = int(upscale_factor)
+    assert two == 2 and Bf == B and H == h * r and W == w * r     # videotools.py:63
+    out = torch.empty_like(img)
+    with torch.cuda.device(img.device):
+        check(lib().isr_warp_upscale(_p(img), _p(flow), _p(out), B, C, h, w, r, int(bool(special_mask)),
+                                     int(bool(align_corners)), _stream()))
+    return out
+
+
+def initial_image(current_input, channels, mode, ao_inverted, upscaling=4):
+    """initialImage (utils/initial_image.py:5-54)."""
+    if mode not in INITIAL:
+        raise ValueError("unknown input mode: " + str(mode))
+    if mode == "unshaded" and channels not in (5, 6):
+        raise ValueError("for mode='unshaded', channels is expected to be 5 or 6")
+    x = _prep(current_input, "current_input")
+    B, Cin, h, w = x.shape
+    out = torch.empty((B, channels, h * upscaling, w * upscaling), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        check(lib().isr_initial_image(_p(x), _p(out), B, Cin, h, w, channels, INITIAL[mode], int(bool(ao_inverted)),
+                                      int(upscaling), _stream()))
+    return out
+
+
+def postprocess(pred, unshaded=True):
+    """clamp / normalise between frames (mainVideoUnshaded.py:460-465, mainVideo.py:416)."""
+    x = _prep(pred, "pred")
+    B, C, H, W = x.shape
+    out = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        check(lib().isr_postprocess(_p(x), _p(out), B, C, H, W, int(bool(unshaded)), _stream()))
+    return out
+
+
+def shade(gbuffer, params22):
+    """ScreenSpaceShading.forward (utils/shading.py:148-191); params22: 22 python floats (include/isr.h)."""
+    x = _prep(gbuffer, "input")
+    B, C, H, W = x.shape
+    assert C >= 5                                                   # shading.py:150
+    arr = (ctypes.c_float * 22)(*[float(v) for v in params22])
+    out = torch.empty((B, 3, H, W), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        check(lib().isr_shade(_p(x), arr, _p(out), B, C, H, W, _stream()))
+    return out
+
+
+def _workspace(device, nbytes):
+    # cudaMalloc'd blocks from torch's caching allocator are 512-byte aligned; over-allocate and slice to 1024
+    buf = torch.empty(nbytes + 1024, device=device, dtype=torch.uint8)
+    off = (-buf.data_ptr()) % 1024
+    return buf, buf.data_ptr() + off
+
+
+def debug_conv3x3(x, weight, bias=None, addend=None, relu=False, fmt="bf16", n_act_parts=1, n_w_parts=1):
+    """One tensor-core conv3x3 (64 -> cout) with fp32 NCHW in/out -- unit-test hook."""
+    x = _prep(x, "x")
+    weight = _prep(weight, "weight")
+    B, C, H, W = x.shape
+    cout = weight.shape[0]
+    assert C == 64 and tuple(weight.shape[1:]) == (64, 3, 3)
+    bias = _prep(bias, "bias") if bias is not None else None
+    addend = _prep(addend, "addend") if addend is not None else None
+    out = torch.empty((B, cout, H, W), device=x.device, dtype=torch.float32)
+    n = ctypes.c_size_t(0)
+    check(lib().isr_debug_conv_workspace_bytes(B, H, W, ctypes.byref(n)))
+    buf, ptr = _workspace(x.device, n.value)
+    with torch.cuda.device(x.device):
+        check(lib().isr_debug_conv3x3(_p(x), _p(weight), _p(bias), _p(addend), _p(out), B, H, W, cout, int(bool(relu)),
+                                      0 if fmt == "bf16" else 1, n_act_parts, n_w_parts, ctypes.c_void_p(ptr),
+                                      n.value, _stream()))
+        torch.cuda.current_stream().synchronize()   # buf must outlive the kernels
+    return out
+
+
+class NetHandle:
+    """Owns an isr_net (packed weights + cached execution plans) and the activation workspace."""
+
+    def __init__(self, input_channels, output_channels, n_mask, upsample, recon_residual, device):
+        if upsample not in UPSAMPLE:
+            raise ValueError("the B200 kernels support upsample = nearest | bilinear, got " + str(upsample))
+        self.device = torch.device(device)
+        self.cin, self.cout = int(input_channels), int(output_channels)
+        self._net = ctypes.c_void_p(0)
+        with torch.cuda.device(self.device):
+            check(lib().isr_net_create(ctypes.byref(self._net), self.cin, self.cout, int(n_mask), UPSAMPLE[upsample],
+                                       int(bool(recon_residual))))
+        self._ws = {}
+
+    def __del__(self):
+        try:
+            if self._net:
+                lib().isr_net_destroy(self._net)
+                self._net = ctypes.c_void_p(0)
+        except Exception:
+            pass
+
+    def load_weights(self, tensors):
+        ts = [_prep(t.detach(), "parameter") for t in tensors]
+        assert len(ts) == 50
+        arr = (ctypes.c_void_p * 50)(*[t.data_ptr() for t in ts])
+        with torch.cuda.device(self.device):
+            check(lib().isr_net_load_weights(self._net, arr, 50, _stream()))
+
+    def workspace(self, B, h, w, precision):
+        key = (B, h, w, precision)
+        if key not in self._ws:
+            n = ctypes.c_size_t(0)
+            check(lib().isr_net_workspace_bytes(self._net, B, h, w, PREC[precision], ctypes.byref(n)))
+            if len(self._ws) >= 4:
+                self._ws.clear()
+            buf, ptr = _workspace(self.device, n.value)
+            self._ws[key] = (buf, ptr, n.value)
+        return self._ws[key]
+
+    def forward(self, inputs, precision="mixed", want_raw=True, want_state=False, state_unshaded=True):
+        x = _prep(inputs, "inputs")
+        B, C, h, w = x.shape
+        assert C == self.cin
+        _, ptr, nbytes = self.workspace(B, h, w, precision)
+        shape = (B, self.cout, 4 * h, 4 * w)
+        recon = torch.empty(shape, device=x.device, dtype=torch.float32)
+        raw = torch.empty(shape, device=x.device, dtype=torch.float32) if want_raw else None
+        state = torch.empty(shape, device=x.device, dtype=torch.float32) if want_state else None
+        with torch.cuda.device(x.device):
+            check(lib().isr_net_forward(self._net, _p(x), _p(recon), _p(raw), _p(state), int(bool(state_unshaded)), B, h,
+                                        w, PREC[precision], ctypes.c_void_p(ptr), nbytes, _stream()))
+        return recon, raw, state
+
+    def forward_recurrent(self, low, prev, flow, special_mask, precision="mixed", align_corners=False, want_raw=False,
+                          want_state=True, state_unshaded=True, out_state=None):
+        low, prev = _prep(low, "low"), _prep(prev, "previous_output")
+        flow = _prep(flow, "flow") if flow is not None else None
+        B, c_low, h, w = low.shape
+        c_prev = prev.shape[1]
+        assert tuple(prev.shape) == (B, c_prev, 4 * h, 4 * w)
+        _, ptr, nbytes = self.workspace(B, h, w, precision)
+        shape = (B, self.cout, 4 * h, 4 * w)
+        recon = torch.empty(shape, device=low.device, dtype=torch.float32)
+        raw = torch.empty(shape, device=low.device, dtype=torch.float32) if want_raw else None
+        state = None
+        if want_state:
+            state = out_state if out_state is not None else torch.empty(shape, device=low.device, dtype=torch.float32)
+        with torch.cuda.device(low.device):
+            check(lib().isr_net_forward_recurrent(self._net, _p(low), _p(prev), _p(flow), c_low, c_prev,
+                                                  int(bool(special_mask)), int(bool(align_corners)), _p(recon), _p(raw),
+                                                  _p(state), int(bool(state_unshaded)), B, h, w, PREC[precision],
+                                                  ctypes.c_void_p(ptr), nbytes, _stream()))
+        return recon, raw, state
+
+    def time_conv(self, B, h, w, precision="mixed", scale=4, iters=10):
+        _, ptr, nbytes = self.workspace(B, h, w, precision)
+        ms = ctypes.c_float(0)
+        with torch.cuda.device(self.device):
+            check(lib().isr_net_time_conv(self._net, B, h, w, PREC[precision], scale, ctypes.c_void_p(ptr), nbytes,
+                                          iters, ctypes.byref(ms), _stream()))
+        return float(ms.value)
+
+
+__all__ = ["flatten_high", "warp_upscale", "initial_image", "postprocess", "shade", "debug_conv3x3", "NetHandle",
+           "IsrError", "PREC"]

@@ -1,0 +1,272 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the committed golden vectors.
+Run on the B200 box: python -m pytest tests -m gpu.  Tolerances are the north star's: indexing bit-exact, warp 1e-5,
+network outputs 1e-2 max-abs per channel and >= 50 dB PSNR."""
+from argparse import Namespace
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def isr():
+    if not torch.cuda.is_available():
+        pytest.fail("GPU tests need a CUDA device")
+    import isosurfacesuperresolution_b200 as pkg
+    return pkg
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()
+
+
+def maxabs(a, b):
+    a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else np.asarray(a)
+    b = b.detach().cpu().numpy() if isinstance(b, torch.Tensor) else np.asarray(b)
+    return float(np.max(np.abs(a.astype(np.float64) - b.astype(np.float64))))
+
+
+# ---- indexing: bit-exact ---------------------------------------------------------------------------------------
+def test_flatten_high_bit_exact(isr, golden):
+    g = golden("flatten_high")
+    y = isr.VideoTools.flatten_high(cu(g["x"]), 4).cpu().numpy()
+    assert np.array_equal(y, g["y"])
+    # full-size property: inverse of pixel_shuffle, 1080p, 6 channels
+    x = torch.randn(1, 6, 1080, 1920, device="cuda")
+    f = isr.VideoTools.flatten_high(x, 4)
+    assert f.shape == (1, 96, 270, 480)
+    assert torch.equal(torch.nn.functional.pixel_shuffle(f, 4), x)
+
+
+# ---- warp: 1e-5 ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("flow", ["zero", "const", "smooth", "wild"])
+@pytest.mark.parametrize("special_mask", [False, True])
+def test_warp_upscale_golden(isr, golden, flow, special_mask):
+    g = golden("warp_upscale")
+    out = isr.VideoTools.warp_upscale(cu(g["img"]), cu(g[f"flow_{flow}"]), 4, special_mask=special_mask)
+    assert maxabs(out, g[f"{flow}_{int(special_mask)}"]) <= 1e-5
+
+
+def test_warp_upscale_rgb_nonsquare(isr, golden):
+    g = golden("warp_upscale_rgb")
+    assert maxabs(isr.VideoTools.warp_upscale(cu(g["img"]), cu(g["flow"]), 4), g["out"]) <= 1e-5
+
+
+def test_warp_upscale_1080p_vs_oracle(isr):
+    low, flow, ao = orc.synthetic_gbuffer(1, 270, 480, 33)
+    rng = np.random.RandomState(3)
+    img = rng.uniform(-1, 1, (1, 6, 1080, 1920)).astype(np.float32)
+    ref = orc.warp_upscale(img, flow[:, 0], 4, special_mask=True, backend="c")
+    out = isr.VideoTools.warp_upscale(cu(img), cu(flow[:, 0]), 4, special_mask=True)
+    assert maxabs(out, ref) <= 1e-5
+
+
+def test_warp_align_corners_identity(isr):
+    # with the as-trained align_corners=True convention a zero flow is the identity warp
+    img = torch.rand(2, 3, 64, 96, device="cuda")
+    out = isr.VideoTools.warp_upscale(img, torch.zeros(2, 2, 16, 24, device="cuda"), 4, align_corners=True)
+    assert maxabs(out, img) <= 2e-5
+
+
+# ---- initial image / post-process / shading --------------------------------------------------------------------
+def test_initial_image(isr, golden):
+    g = golden("initial_image")
+    cur = cu(g["cur"])
+    for mode in ("zero", "unshaded", "input"):
+        for ch in (5, 6):
+            assert maxabs(isr.initialImage(cur, ch, mode, False, 4), g[f"{mode}_{ch}"]) <= 1e-6
+    assert maxabs(isr.initialImage(cur, 6, "unshaded", True, 4), g["unshaded_6_inv"]) == 0
+    assert maxabs(isr.initialImage(cur, 3, "input", False, 4), g["input_3"]) <= 1e-6
+    with pytest.raises(ValueError):
+        isr.initialImage(cur, 4, "unshaded", False, 4)
+    with pytest.raises(ValueError):
+        isr.initialImage(cur, 6, "bogus", False, 4)
+
+
+def _shading_from_params(isr, p):
+    s = isr.ScreenSpaceShading(torch.device("cuda"))
+    s.fov(30)
+    s.ambient_light_color(np.array(p[0:3]))
+    s.diffuse_light_color(np.array(p[3:6]))
+    s.specular_light_color(np.array(p[6:9]))
+    s.specular_exponent(int(p[19]))
+    s.light_direction(np.array(p[9:12], dtype=np.float64))
+    s.material_color(np.array(p[12:15]))
+    s.background(np.array(p[15:18]))
+    s.ambient_occlusion(float(p[18]))
+    s.enable_specular = bool(p[20])
+    s.inverse_ao = bool(p[21])
+    return s
+
+
+@pytest.mark.parametrize("cfg", ["train", "gui", "nospec"])
+def test_shading_golden(isr, golden, cfg):
+    g = golden("shading")
+    s = _shading_from_params(isr, g[f"{cfg}_params"])
+    gb = cu(g["gbuffer"])
+    assert maxabs(s(gb), g[f"{cfg}_c6"]) <= 1e-5
+    assert maxabs(s(gb[:, 0:5].contiguous()), g[f"{cfg}_c5"]) <= 1e-5
+
+
+def test_shading_1080p_vs_oracle(isr):
+    low, _, ao = orc.synthetic_gbuffer(1, 270, 480, 12)
+    gb = np.concatenate([low[:, 0], ao[:, 0]], axis=1)
+    gb = np.repeat(np.repeat(gb, 4, axis=2), 4, axis=3) + np.random.RandomState(1).normal(0, 0.1, (1, 6, 1080, 1920))
+    prm = orc.shading_params(material=(1.0, 0.3, 0.0), ao_strength=0.5, background=(1.0, 1.0, 1.0))
+    s = _shading_from_params(isr, prm)
+    assert maxabs(s(cu(gb)), orc.shade(gb, prm)) <= 1e-5
+
+
+def test_postprocess(isr, golden):
+    from isosurfacesuperresolution_b200 import ops
+    g = golden("shading")
+    assert maxabs(ops.postprocess(cu(g["gbuffer"]), True), g["postprocess"]) <= 1e-6
+    x = cu(g["gbuffer"])
+    assert maxabs(ops.postprocess(x, False), torch.clamp(x, 0, 1)) == 0
+
+
+# ---- convolution kernel ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(1, 16, 8), (2, 37, 29), (1, 270, 480)])
+@pytest.mark.parametrize("mode", [("bf16", 2, 2, 2e-4), ("fp16", 2, 2, 5e-5), ("fp16", 1, 1, 2e-2), ("bf16", 1, 1, 1.5e-1)])
+def test_conv3x3_vs_fp64(isr, shape, mode):
+    from isosurfacesuperresolution_b200 import ops
+    fmt, na, nw, tol = mode
+    B, H, W = shape
+    g = torch.Generator().manual_seed(11)
+    x = (torch.rand(B, 64, H, W, generator=g) * 2 - 1).cuda()
+    w = (torch.randn(64, 64, 3, 3, generator=g) * 0.06).cuda()
+    b = torch.randn(64, generator=g).cuda()
+    ref = torch.nn.functional.conv2d(x.double(), w.double(), b.double(), padding=1)
+    out = ops.debug_conv3x3(x, w, b, fmt=fmt, n_act_parts=na, n_w_parts=nw)
+    assert maxabs(out, ref) <= tol
+    add = torch.randn(B, 64, H, W, generator=g).cuda()
+    out = ops.debug_conv3x3(x, w, b, addend=add, relu=True, fmt=fmt, n_act_parts=na, n_w_parts=nw)
+    assert maxabs(out, torch.relu(ref + add)) <= tol
+
+
+# ---- network -----------------------------------------------------------------------------------------------------
+def _net(isr, weights, cin=101, cout=6, mask=(0, 1, 2, 3, 4), ups="bilinear", recon="residual"):
+    opt = Namespace(upsample=ups, reconType=recon, useBN=False)
+    net = isr.createNetwork("EnhanceNet", 4, cin, list(mask), cout, opt)
+    if weights is not None:
+        net.load_state_dict({k: torch.from_numpy(v) for k, v in weights.items()})
+    return net.cuda().eval()
+
+
+def _check_net(out, ref, tol=1e-2, min_psnr=50.0):
+    out = out.detach().cpu().numpy()
+    for c in range(ref.shape[1]):
+        assert float(np.max(np.abs(out[:, c] - ref[:, c]))) <= tol, f"channel {c}"
+    assert orc.psnr(out, ref) >= min_psnr
+
+
+@pytest.mark.parametrize("ups", ["bilinear", "nearest"])
+@pytest.mark.parametrize("prec", ["mixed", "bf16x3", "fp16x3"])
+def test_enhancenet_forward_golden(isr, golden, weights, ups, prec):
+    g = golden("enhancenet_forward")
+    net = _net(isr, weights, ups=ups)
+    net.precision = prec
+    with torch.no_grad():
+        recon, raw = net(cu(g["x"]))
+    _check_net(raw, g[f"raw_{ups}"])
+    _check_net(recon, g[f"recon_{ups}"])
+
+
+def test_enhancenet_state_dict_roundtrip(isr, weights):
+    net = _net(isr, weights)
+    sd = net.state_dict()
+    assert list(sd.keys()) == orc.STATE_DICT_KEYS
+    for k in sd:
+        assert np.array_equal(sd[k].cpu().numpy(), weights[k])
+    first = net
+    while list(first.children()):
+        first = list(first.children())[0]
+    assert first.in_channels == 101                    # LoadedModel's layout sniffing (loadedmodel.py:26-35)
+
+
+def test_enhancenet_direct_and_shaded(isr, golden, weights):
+    g = golden("enhancenet_forward")
+    net = _net(isr, weights, recon="direct")
+    with torch.no_grad():
+        recon, raw = net(cu(g["x"]))
+    _check_net(recon, g["recon_direct"])
+    assert torch.equal(recon, raw)
+    # shaded variant (56 -> 3): weights rebuilt by the same seeded constructor as the reference's
+    torch.manual_seed(1234)
+    net_s = _net(isr, None, cin=56, cout=3, mask=(0, 1, 2))
+    ws = [float(sum(v.double().sum() for v in net_s.state_dict().values())),
+          float(sum(v.double().abs().sum() for v in net_s.state_dict().values()))]
+    assert np.allclose(ws, g["shaded_weight_sum"], rtol=1e-6)
+    with torch.no_grad():
+        rs, raws = net_s(cu(g["shaded_x"]))
+    _check_net(raws, g["shaded_raw"])
+    _check_net(rs, g["shaded_recon"])
+
+
+def test_enhancenet_c1_vs_oracle(isr, weights):
+    """Config 1: 128x128 -> 512x512, uniform stress input and synthetic G-buffer input, vs the fp32 CPU oracle."""
+    net = _net(isr, weights)
+    rng = np.random.RandomState(7)
+    x = rng.uniform(-1, 1, (1, 101, 128, 128)).astype(np.float32)
+    ref_recon, ref_raw = orc.enhancenet_forward(weights, x, "bilinear", "residual", 5, backend="torch")
+    with torch.no_grad():
+        recon, raw = net(cu(x))
+    _check_net(raw, ref_raw)
+    _check_net(recon, ref_recon)
+
+
+def test_sequence_recurrence_golden(isr, golden, weights):
+    g = golden("sequence_unshaded")
+    net = _net(isr, weights)
+    shd = _shading_from_params(isr, g["shade_params"])
+    runner = isr.SequenceRunner(net, initial_image="input", shading=shd)
+    preds, rgbs, _ = runner.run(cu(g["low"]), cu(g["flow"]))
+    for j in range(3):
+        _check_net(preds[j], g[f"pred_{j}"])
+        assert maxabs(rgbs[j], g[f"rgb_{j}"]) <= 2e-2
+
+
+def test_fused_recurrent_equals_unfused(isr, weights):
+    """forward(low, prev, flow) == forward(cat(low, flatten_high(warp_upscale(prev, flow)))) -- same kernels downstream,
+    so the packed inputs must agree to the last bit of the 16-bit operands."""
+    net = _net(isr, weights)
+    low, flow, ao = orc.synthetic_gbuffer(2, 24, 40, 5, T=2)
+    prev = torch.rand(2, 6, 96, 160, device="cuda") * 2 - 1
+    with torch.no_grad():
+        a, _ = net(cu(low[:, 1]), prev, cu(flow[:, 0]), special_mask=True)
+        warped = isr.VideoTools.warp_upscale(prev, cu(flow[:, 0]), 4, special_mask=True)
+        single = torch.cat((cu(low[:, 1]), isr.VideoTools.flatten_high(warped, 4)), dim=1)
+        b, _ = net(single)
+    assert torch.equal(a, b)
+
+
+def test_loaded_model_facade(isr, weights):
+    net = _net(isr, weights)
+    lm = isr.LoadedModel({"model": net, "parameters": {"initialImage": "input"}}, torch.device("cuda"), 4)
+    assert lm.unshaded and lm.input_channels == 101 and lm.initial_image_mode == "input"
+    low, flow, ao = orc.synthetic_gbuffer(1, 32, 48, 8, T=2)
+    frame = np.zeros((1, 12, 32, 48), np.float32)
+    frame[:, 3] = low[:, 0, 0] * 0.5 + 0.5
+    frame[:, 4:8] = low[:, 0, 1:5]
+    frame[:, 8:10] = flow[:, 0]
+    p0 = lm.inference(cu(frame), None)
+    p1 = lm.inference(cu(frame), p0)
+    assert p0.shape == (1, 6, 128, 192) and p1.shape == p0.shape and torch.isfinite(p1).all()
+    # frame 0 against the oracle
+    inp = np.concatenate([frame[:, 3:4] * 2 - 1, frame[:, 4:8]], axis=1)
+    prev = orc.initial_image(inp, 6, "input", False, 4)
+    single = np.concatenate([inp, orc.flatten_high(prev, 4)], axis=1)
+    ref, _ = orc.enhancenet_forward(weights, single, "bilinear", "residual", 5, backend="torch")
+    _check_net(p0, ref)
+
+
+def test_no_cpu_fallback(isr, weights):
+    net = _net(isr, weights).cpu()
+    with torch.no_grad(), pytest.raises(RuntimeError):
+        net(torch.zeros(1, 101, 8, 8))
+    with pytest.raises(RuntimeError):
+        isr.VideoTools.flatten_high(torch.zeros(1, 6, 8, 8), 4)
