@@ -134,15 +134,13 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   p.tiles_x = (W + kTileW - 1) / kTileW;
   p.tiles_y = (H + kTileH - 1) / kTileH;
   p.num_tiles = p.tiles_x * p.tiles_y * B;
-  p.pitch = g_halo_pitch;
-  p.base_offset_mode = g_base_offset_mode;
   p.n_act_parts = n_act_parts;
   p.n_w_parts = n_w_parts;
   p.is_bf16 = is_bf16;
   p.w_row0 = w_row0;
   p.w_row_stride = w_row_stride;
   const size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * 9 * n * 128, 1024);
-  p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(p.pitch) * kHaloH * 128, 1024));
+  p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kPitch) * kHaloH * 128, 1024));
   const size_t avail = kSmemLimit - kStaticSmem - 1024 - w_bytes - 256;
   int stages = static_cast<int>(avail / p.stage_bytes);
   if (stages > 8) stages = 8;
@@ -151,7 +149,7 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   L->smem = 1024 + w_bytes + static_cast<size_t>(stages) * p.stage_bytes + 256;
   int cap = g_max_ctas > 0 ? g_max_ctas : num_sms();
   L->grid = p.num_tiles < cap ? p.num_tiles : cap;
-  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, p.pitch, kHaloH, is_bf16);
+  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kPitch, kHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
   return make_w_map(&L->tmW, wpacked, w_rows_total, n, is_bf16);
 }
@@ -400,10 +398,10 @@ uint64_t isr_launch_count(void) { return g_launches.load(); }
 int isr_set_tunable(const char *key, int value) {
   int *slot = nullptr;
   if (key != nullptr && strcmp(key, "halo_pitch") == 0) {
-    if (value != 10 && value != 16) return fail(ISR_ERR_ARG, "halo_pitch must be 10 or 16");
+    if (value != 10) return fail(ISR_ERR_ARG, "halo_pitch is fixed at 10 (validated on B200, profiles/r01_probe_umma_addressing.json)");
     slot = &g_halo_pitch;
   } else if (key != nullptr && strcmp(key, "base_offset_mode") == 0) {
-    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "base_offset_mode must be 0 or 1");
+    if (value != 0) return fail(ISR_ERR_ARG, "base_offset_mode is fixed at 0 (validated on B200)");
     slot = &g_base_offset_mode;
   } else if (key != nullptr && strcmp(key, "max_ctas") == 0) {
     if (value < 0) return fail(ISR_ERR_ARG, "max_ctas must be >= 0");
@@ -479,6 +477,7 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
   if (recon_residual && n_mask > output_channels)
     return fail(ISR_ERR_ARG, "number of output channels must be at least the number of masked input channels");
   if (n_mask < 0 || n_mask > input_channels) return fail(ISR_ERR_ARG, "bad channel mask length");
+  if (recon_residual && n_mask > 8) return fail(ISR_ERR_UNSUPPORTED, "channel masks longer than 8 are not supported");
   int rc = check_device();
   if (rc != ISR_OK) return rc;
   isr_net *net = new isr_net();

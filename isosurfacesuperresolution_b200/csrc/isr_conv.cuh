@@ -11,7 +11,10 @@
 //     (ky*pitch + kx) rows, 8-row-group stride = pitch*128 B) -- no im2col copy, no re-read.
 //   * All nine taps' weights ([part][tap][Cout][64], K-major, 128B swizzle) stay resident in shared memory for the whole
 //     persistent CTA; accumulators live in TMEM (double buffered: epilogue of tile i overlaps the MMAs of tile i+1).
-//   * Warp roles: warps 0-3 epilogue (TMEM lanes 32w..32w+31), warp 4 TMA producer, warp 5 MMA issuer + TMEM owner.
+//   * Warp roles: warps 0-7 epilogue in two groups of four (group g drains accumulator buffer g; warp w reads TMEM lanes
+//     32*(w%4)..+31), warp 8 TMA producer, warp 9 MMA issuer + TMEM owner.
+//   * 64-wide epilogue: tcgen05.ld 16x256b + a permuted GEMM-column order (pack_weights_kernel) leave 16 consecutive
+//     channels of a pixel in each thread, so a warp's 16-byte stores cover whole 128-byte lines (no smem staging).
 //   * Split precision ("x3"): passes (Ahi,Whi), (Ahi,Wlo), (Alo,Whi) accumulate into the same TMEM tile.
 #pragma once
 #include <cuda.h>
@@ -25,15 +28,14 @@ namespace isr {
 constexpr int kTileW = 8;
 constexpr int kTileH = 16;
 constexpr int kHaloH = kTileH + 2;
-constexpr int kConvThreads = 192;
+constexpr int kPitch = kTileW + 2;  // halo pitch in pixels; 8-row-group stride of the A descriptors = kPitch * 128 B
+constexpr int kConvThreads = 320;  // warps 0-7 epilogue (two groups of 4), warp 8 TMA producer, warp 9 MMA issuer
 
 enum { EPI_STORE16 = 0, EPI_FINAL = 1 };
 
 struct ConvParams {
   int B, H, W;
   int tiles_x, tiles_y, num_tiles;
-  int pitch;             // halo pitch in pixels (10 = exact halo, 16 = 1024B-aligned 8-row groups)
-  int base_offset_mode;  // 1: descriptor base_offset = (start >> 7) & 7
   int n_act_parts;       // 1 | 2 (input channel dim = 64 * n_act_parts)
   int n_w_parts;         // 1 | 2
   int is_bf16;
@@ -102,7 +104,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (threadIdx.x < 64) s_bias[threadIdx.x] = (p.bias != nullptr && threadIdx.x < N) ? p.bias[threadIdx.x] : 0.f;
 
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmW);
     for (int s = 0; s < p.num_stages; ++s) {
@@ -117,7 +119,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_barrier_init();
   }
   constexpr uint32_t kTmemCols = (2 * N < 32) ? 32 : 2 * N;
-  if (warp == 5) tmem_alloc(s_tptr, kTmemCols);
+  if (warp == 9) tmem_alloc(s_tptr, kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -127,142 +129,158 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int my_tiles = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                        static_cast<int>(gridDim.x);
 
-  if (warp == 4) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+  if (warp == 8) {
+    // ===================== TMA producer (whole warp runs the loop; one elected lane issues) =====================
+    if (elect_one()) {
       mbar_arrive_expect_tx(b_w, w_bytes);
       for (int wp = 0; wp < p.n_w_parts; ++wp)
         for (int tap = 0; tap < 9; ++tap)
           tma_load_2d(s_w + (wp * 9 + tap) * kWTapBytes, &tmW, b_w, 0, p.w_row0 + (wp * 9 + tap) * p.w_row_stride);
-      uint32_t it = 0;
-      for (int i = 0; i < my_tiles; ++i) {
-        const int t = blockIdx.x + i * gridDim.x;
-        const int tx = t % p.tiles_x;
-        const int ty = (t / p.tiles_x) % p.tiles_y;
-        const int b = t / (p.tiles_x * p.tiles_y);
-        for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
-          const uint32_t s = it % p.num_stages;
-          const uint32_t ph = (it / p.num_stages) & 1;
-          mbar_wait(b_empty + 8 * s, ph ^ 1);
-          mbar_arrive_expect_tx(b_full + 8 * s, p.pitch * kHaloH * 128);
-          tma_load_4d(s_stage0 + s * p.stage_bytes, &tmA, b_full + 8 * s, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
-        }
-      }
     }
-  } else if (warp == 5) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_f16(128, N, p.is_bf16);
-      const uint32_t sbo = p.pitch * 128;
-      mbar_wait(b_w, 0);
-      uint32_t it = 0;
-      for (int i = 0; i < my_tiles; ++i) {
-        const uint32_t acc = i & 1;
-        const uint32_t acc_ph = (i >> 1) & 1;
-        mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * N;
-        uint32_t first = 1;
-        for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
-          const uint32_t s = it % p.num_stages;
-          const uint32_t ph = (it / p.num_stages) & 1;
-          mbar_wait(b_full + 8 * s, ph);
-          tc_fence_after();
-          const uint32_t a_base = s_stage0 + s * p.stage_bytes;
-          const int nwp = (ap == 0) ? p.n_w_parts : 1;  // (hi,hi) (hi,lo) | (lo,hi)
-          for (int wp = 0; wp < nwp; ++wp) {
-#pragma unroll
-            for (int tap = 0; tap < 9; ++tap) {
-              const uint32_t a_tap = a_base + ((tap / 3) * p.pitch + (tap % 3)) * 128;
-              const uint32_t b_tap = s_w + (wp * 9 + tap) * kWTapBytes;
-              const uint32_t bo = p.base_offset_mode ? ((a_tap >> 7) & 7) : 0;
-#pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const uint64_t adesc = make_smem_desc_sw128(a_tap + k * 32, sbo, bo);
-                const uint64_t bdesc = make_smem_desc_sw128(b_tap + k * 32, 1024, 0);
-                umma_f16(d_tmem, adesc, bdesc, idesc, first ? 0u : 1u);
-                first = 0;
-              }
-            }
-          }
-          umma_commit(b_empty + 8 * s);  // frees this halo stage when its MMAs retire
-        }
-        umma_commit(b_tfull + 8 * acc);  // accumulator complete -> epilogue
-      }
-    }
-  } else {
-    // ===================== epilogue warps 0..3 =====================
-    const int row = warp * 32 + lane;  // GEMM row = TMEM lane
-    const int py = row >> 3, px = row & 7;
+    __syncwarp();
+    uint32_t it = 0;
     for (int i = 0; i < my_tiles; ++i) {
       const int t = blockIdx.x + i * gridDim.x;
       const int tx = t % p.tiles_x;
       const int ty = (t / p.tiles_x) % p.tiles_y;
       const int b = t / (p.tiles_x * p.tiles_y);
+      for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+        const uint32_t s = it % p.num_stages;
+        const uint32_t ph = (it / p.num_stages) & 1;
+        mbar_wait(b_empty + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(b_full + 8 * s, kPitch * kHaloH * 128);
+          tma_load_4d(s_stage0 + s * p.stage_bytes, &tmA, b_full + 8 * s, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 9) {
+    // ===================== MMA issuer (whole warp runs the loop; one elected lane issues) =====================
+    const uint32_t idesc = make_idesc_f16(128, N, p.is_bf16);
+    const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
+    mbar_wait(b_w, 0);
+    uint32_t it = 0;
+    for (int i = 0; i < my_tiles; ++i) {
       const uint32_t acc = i & 1;
       const uint32_t acc_ph = (i >> 1) & 1;
-      mbar_wait(b_tfull + 8 * acc, acc_ph);
+      mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + acc * N + (static_cast<uint32_t>(warp * 32) << 16);
-      const int y = ty * kTileH + py, x = tx * kTileW + px;
-      const bool inb = (y < p.H) && (x < p.W);
+      const uint32_t d_tmem = tmem_base + acc * N;
+      uint32_t first = 1;
+      for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+        const uint32_t s = it % p.num_stages;
+        const uint32_t ph = (it / p.num_stages) & 1;
+        mbar_wait(b_full + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t a_base = s_stage0 + s * p.stage_bytes;
+        const uint64_t a_desc0 = make_smem_desc_sw128(a_base, kPitch * 128, 0);
+        const int nwp = (ap == 0) ? p.n_w_parts : 1;  // (hi,hi) (hi,lo) | (lo,hi)
+        if (elect_one()) {
+          for (int wp = 0; wp < nwp; ++wp) {
+            const uint64_t b_desc0 = b_desc_base + static_cast<uint64_t>((wp * 9 * kWTapBytes) >> 4);
+#pragma unroll
+            for (int tap = 0; tap < 9; ++tap) {
+              // tap (ky,kx): the same halo tile, start address shifted by (ky*pitch + kx) pixel rows of 128 B
+              const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
+              const uint64_t bdesc = b_desc0 + static_cast<uint64_t>((tap * kWTapBytes) >> 4);
+              umma_f16_k64(d_tmem, adesc, bdesc, idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
+            }
+            first = 0;
+          }
+          umma_commit(b_empty + 8 * s);  // frees this halo stage when its MMAs retire
+          if (ap == p.n_act_parts - 1) umma_commit(b_tfull + 8 * acc);  // accumulator complete -> epilogue
+        }
+        __syncwarp();
+        first = 0;
+      }
+    }
+  } else {
+    // ===================== epilogue warps 0..7: group g = warp/4 drains accumulator buffer g =====================
+    const int grp = warp >> 2, q = warp & 3;
+    for (int i = grp; i < my_tiles; i += 2) {
+      const int t = blockIdx.x + i * gridDim.x;
+      const int tx = t % p.tiles_x;
+      const int ty = (t / p.tiles_x) % p.tiles_y;
+      const int b = t / (p.tiles_x * p.tiles_y);
+      const uint32_t acc = grp;
+      const uint32_t acc_ph = (i >> 1) & 1;
+      const uint32_t taddr = tmem_base + acc * N + (static_cast<uint32_t>(q * 32) << 16);
       if constexpr (EPI == EPI_STORE16) {
-        const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
+        // thread (m = lane%4, rr = lane/4): pixel column rr of image rows 4q..4q+3 of the tile, channels 16m..16m+15
+        const int m = lane & 3, rr = lane >> 2;
+        const int x = tx * kTileW + rr;
+        float bias_r[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) bias_r[j] = s_bias[16 * m + j];
+        mbar_wait(b_tfull + 8 * acc, acc_ph);
+        tc_fence_after();
 #pragma unroll 1
-        for (int ch = 0; ch < N / 16; ++ch) {
-          uint32_t v[16];
-          tmem_ld16(taddr + ch * 16, v);
+        for (int half = 0; half < 2; ++half) {
+          uint32_t v[32];
+          tmem_ld_16x256b_x8(taddr + (static_cast<uint32_t>(half * 16) << 16), v);
           tmem_ld_wait();
-          if (inb) {
-            float f[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]) + s_bias[ch * 16 + j];
-            if (p.addend != nullptr) {
-              for (int ap = 0; ap < p.add_parts; ++ap) {
-                const uint4 *src =
-                    reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + ch * 16);
-                uint4 q0 = __ldg(src), q1 = __ldg(src + 1);
-                uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+          for (int hh = 0; hh < 2; ++hh) {
+            const int y = ty * kTileH + 4 * q + 2 * half + hh;
+            if (y < p.H && x < p.W) {
+              const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
+              float f[16];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                  float2 a = unpack2(w[j], p.is_bf16);
-                  f[2 * j] += a.x;
-                  f[2 * j + 1] += a.y;
+              for (int rep = 0; rep < 8; ++rep) {
+                f[2 * rep] = __uint_as_float(v[4 * rep + 2 * hh]) + bias_r[2 * rep];
+                f[2 * rep + 1] = __uint_as_float(v[4 * rep + 2 * hh + 1]) + bias_r[2 * rep + 1];
+              }
+              if (p.addend != nullptr) {
+                for (int ap = 0; ap < p.add_parts; ++ap) {
+                  const uint4 *src =
+                      reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m);
+                  const uint4 q0 = __ldg(src), q1 = __ldg(src + 1);
+                  const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) {
+                    const float2 a = unpack2(w[j], p.is_bf16);
+                    f[2 * j] += a.x;
+                    f[2 * j + 1] += a.y;
+                  }
                 }
               }
-            }
-            if (p.relu) {
+              if (p.relu) {
 #pragma unroll
-              for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
-            }
-            uint32_t hi[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
-            uint4 *dst = reinterpret_cast<uint4 *>(p.out16 + pix * (64 * p.out_parts) + ch * 16);
-            dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-            dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-            if (p.out_parts == 2) {
-              uint32_t lo[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                float2 h = unpack2(hi[j], p.is_bf16);
-                lo[j] = pack2(f[2 * j] - h.x, f[2 * j + 1] - h.y, p.is_bf16);
+                for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
               }
-              uint4 *dl = reinterpret_cast<uint4 *>(p.out16 + pix * 128 + 64 + ch * 16);
-              dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-              dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+              uint32_t hi[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
+              uint4 *dst = reinterpret_cast<uint4 *>(p.out16 + pix * (64 * p.out_parts) + 16 * m);
+              dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+              if (p.out_parts == 2) {
+                uint32_t lo[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float2 h = unpack2(hi[j], p.is_bf16);
+                  lo[j] = pack2(f[2 * j] - h.x, f[2 * j + 1] - h.y, p.is_bf16);
+                }
+                uint4 *dl = reinterpret_cast<uint4 *>(p.out16 + pix * 128 + 64 + 16 * m);
+                dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+              }
             }
           }
         }
       } else {
-        // final conv: raw = acc + bias; recon = raw + upsampled skip (enhancenet.py:51-90); optional recurrent state
-        uint32_t v[16];
-        tmem_ld16(taddr, v);
-        tmem_ld_wait();
-        if (inb) {
-          const size_t plane = static_cast<size_t>(p.H) * p.W;
-          const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;
-          float rec[16];
+        // final conv: raw = acc + bias; recon = raw + upsampled skip (enhancenet.py:51-90); optional recurrent state.
+        // thread = GEMM row (32x32b load): pixel (py, px) = (row/8, row%8); NCHW fp32 planes, 8 px = one 32 B sector.
+        const int row = q * 32 + lane;
+        const int y = ty * kTileH + (row >> 3), x = tx * kTileW + (row & 7);
+        const bool inb = (y < p.H) && (x < p.W);
+        // the skip taps do not depend on the accumulator: fetch them before waiting for the MMAs
+        constexpr int kSkipPrefetch = 8;
+        float sk[kSkipPrefetch];
+#pragma unroll
+        for (int c = 0; c < kSkipPrefetch; ++c) sk[c] = 0.f;
+        if (inb && p.recon_residual) {
           int x0, x1, y0, y1;
           float lx0, lx1, ly0, ly1;
           if (p.upsample == 1) {
@@ -275,23 +293,36 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             lx1 = ly1 = 0.f;
           }
 #pragma unroll
+          for (int c = 0; c < kSkipPrefetch; ++c) {
+            if (c < p.n_mask) {
+              const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(c) * p.h_low * p.w_low;
+              if (p.upsample == 1) {
+                const float r0 = fmaf(lx0, __ldg(sp + y0 * p.w_low + x0), lx1 * __ldg(sp + y0 * p.w_low + x1));
+                const float r1 = fmaf(lx0, __ldg(sp + y1 * p.w_low + x0), lx1 * __ldg(sp + y1 * p.w_low + x1));
+                sk[c] = fmaf(ly0, r0, ly1 * r1);
+              } else {
+                sk[c] = __ldg(sp + y0 * p.w_low + x0);
+              }
+            }
+          }
+        }
+        mbar_wait(b_tfull + 8 * acc, acc_ph);
+        tc_fence_after();
+        uint32_t v[16];
+        tmem_ld16(taddr, v);
+        tmem_ld_wait();
+        if (inb) {
+          const size_t plane = static_cast<size_t>(p.H) * p.W;
+          const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;
+          float rec[16];
+#pragma unroll
           for (int c = 0; c < 16; ++c) {
+            rec[c] = 0.f;
             if (c < p.cout) {
-              float raw = __uint_as_float(v[c]) + s_bias[c];
+              const float raw = __uint_as_float(v[c]) + s_bias[c];
               if (p.out_raw != nullptr) p.out_raw[o0 + c * plane] = raw;
               float r = raw;
-              if (p.recon_residual && c < p.n_mask) {
-                const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(c) * p.h_low * p.w_low;
-                float sk;
-                if (p.upsample == 1) {
-                  float r0 = fmaf(lx0, __ldg(sp + y0 * p.w_low + x0), lx1 * __ldg(sp + y0 * p.w_low + x1));
-                  float r1 = fmaf(lx0, __ldg(sp + y1 * p.w_low + x0), lx1 * __ldg(sp + y1 * p.w_low + x1));
-                  sk = fmaf(ly0, r0, ly1 * r1);
-                } else {
-                  sk = __ldg(sp + y0 * p.w_low + x0);
-                }
-                r = sk + raw;
-              }
+              if (p.recon_residual && c < p.n_mask && c < kSkipPrefetch) r = sk[c < kSkipPrefetch ? c : 0] + raw;
               rec[c] = r;
               if (p.out_recon != nullptr) p.out_recon[o0 + c * plane] = r;
             }
@@ -324,7 +355,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem_base, kTmemCols);
+  if (warp == 9) tmem_dealloc(tmem_base, kTmemCols);
 }
 
 }  // namespace isr

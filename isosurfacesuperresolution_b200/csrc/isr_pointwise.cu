@@ -133,17 +133,16 @@ __device__ __forceinline__ void store_chunk8(uint16_t *dst_pix, int chunk, int n
 // VideoTools.flatten_high (models/videotools.py:8-25)
 __global__ void flatten_high_kernel(const float *__restrict__ in, float *__restrict__ out, int B, int C, int H, int W,
                                     int r) {
+  // one block per input row (b, c, Y): coalesced reads, r-strided scatter
   const int h = H / r, w = W / r;
-  const size_t total = static_cast<size_t>(B) * C * H * W;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    // i indexes the INPUT (coalesced reads); scatter to the output
-    const int X = static_cast<int>(i % W);
-    const int Y = static_cast<int>((i / W) % H);
-    const int c = static_cast<int>((i / (static_cast<size_t>(W) * H)) % C);
-    const int b = static_cast<int>(i / (static_cast<size_t>(W) * H * C));
-    const int oc = c * r * r + (Y % r) * r + (X % r);
-    out[((static_cast<size_t>(b) * C * r * r + oc) * h + Y / r) * w + X / r] = in[i];
+  const int Y = blockIdx.x % H;
+  const int c = (blockIdx.x / H) % C;
+  const int b = blockIdx.x / (H * C);
+  const float *src = in + static_cast<size_t>(blockIdx.x) * W;
+  const int dy = Y % r, y = Y / r;
+  for (int X = threadIdx.x; X < W; X += blockDim.x) {
+    const int oc = c * r * r + dy * r + (X % r);
+    out[((static_cast<size_t>(b) * C * r * r + oc) * h + y) * w + X / r] = src[X];
   }
 }
 
@@ -151,14 +150,11 @@ __global__ void flatten_high_kernel(const float *__restrict__ in, float *__restr
 __global__ void warp_upscale_kernel(const float *__restrict__ prev, const float *__restrict__ flow,
                                     float *__restrict__ out, int B, int C, int h, int w, int r, int special_mask,
                                     int align_corners) {
+  // one block per output row (b, y)
   const int H = h * r, W = w * r;
   const size_t plane = static_cast<size_t>(H) * W;
-  const size_t total = static_cast<size_t>(B) * plane;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int x = static_cast<int>(i % W);
-    const int y = static_cast<int>((i / W) % H);
-    const int b = static_cast<int>(i / plane);
+  const int y = blockIdx.x % H, b = blockIdx.x / H;
+  for (int x = threadIdx.x; x < W; x += blockDim.x) {
     const WarpTaps t = warp_taps(flow + static_cast<size_t>(b) * 2 * h * w, h, w, r, y, x, align_corners);
     for (int c = 0; c < C; ++c)
       out[(static_cast<size_t>(b) * C + c) * plane + static_cast<size_t>(y) * W + x] =
@@ -267,15 +263,14 @@ __global__ void unpack_nhwc_kernel(const uint16_t *__restrict__ in, float *__res
 // initialImage (utils/initial_image.py:5-54)
 __global__ void initial_image_kernel(const float *__restrict__ in, float *__restrict__ out, int B, int Cin, int h, int w,
                                      int channels, int mode, int ao_inverted, int r) {
+  // one block per output row (b, c, y)
   const int H = h * r, W = w * r;
-  const size_t plane = static_cast<size_t>(H) * W;
-  const size_t total = static_cast<size_t>(B) * channels * plane;
   const float inv = 1.0f / static_cast<float>(r);
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int x = static_cast<int>(i % W), y = static_cast<int>((i / W) % H);
-    const int c = static_cast<int>((i / plane) % channels);
-    const int b = static_cast<int>(i / (plane * channels));
+  const int y = blockIdx.x % H;
+  const int c = (blockIdx.x / H) % channels;
+  const int b = blockIdx.x / (H * channels);
+  float *dst = out + static_cast<size_t>(blockIdx.x) * W;
+  for (int x = threadIdx.x; x < W; x += blockDim.x) {
     float v = 0.f;
     if (mode == 1) {  // 'unshaded' defaults: mask=-1, normal=(0,0,1), depth=0.5, ao=1 (0 if inverted)
       v = c == 0 ? -1.f : (c == 3 ? 1.f : (c == 4 ? 0.5f : (c == 5 ? (ao_inverted ? 0.f : 1.f) : 0.f)));
@@ -290,18 +285,18 @@ __global__ void initial_image_kernel(const float *__restrict__ in, float *__rest
         v = 1.f;
       }
     }
-    out[i] = v;
+    dst[x] = v;
   }
 }
 
 // inter-frame post-processing (mainVideoUnshaded.py:460-465; shading.py:193-207; mainVideo.py:416)
 __global__ void postprocess_kernel(const float *__restrict__ in, float *__restrict__ out, int B, int C, int H, int W,
                                    int unshaded) {
+  // one block per row (b, y)
   const size_t plane = static_cast<size_t>(H) * W;
-  const size_t total = static_cast<size_t>(B) * plane;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const size_t b = i / plane, o = b * C * plane + (i % plane);
+  const int y = blockIdx.x % H, b = blockIdx.x / H;
+  for (int x = threadIdx.x; x < W; x += blockDim.x) {
+    const size_t o = static_cast<size_t>(b) * C * plane + static_cast<size_t>(y) * W + x;
     if (!unshaded) {
       for (int c = 0; c < C; ++c) out[o + c * plane] = fminf(fmaxf(in[o + c * plane], 0.f), 1.f);
       continue;
@@ -357,11 +352,10 @@ __device__ __forceinline__ void shade_pixel(const ShadeParams &s, float m, float
 template <int VEC>
 __global__ void __launch_bounds__(256)
 shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams s, float sf, int B, int C, size_t plane) {
-  const size_t nvec = plane / VEC;
-  const size_t total = static_cast<size_t>(B) * nvec;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const size_t b = i / nvec, q = (i % nvec) * VEC;
+  const unsigned nvec = static_cast<unsigned>(plane / VEC);
+  const size_t b = blockIdx.y;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {
+    const size_t q = static_cast<size_t>(i) * VEC;
     const float *p = in + b * C * plane + q;
     float *o = out + b * 3 * plane + q;
     float m[VEC], nx[VEC], ny[VEC], nz[VEC], ao[VEC];
@@ -398,14 +392,14 @@ shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams 
 __global__ void __launch_bounds__(256)
 upsample2x_nhwc_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out, int B, int h, int w, int in_parts,
                        int out_parts, int in_bf16, int out_bf16, int bilinear) {
+  // one block per output row (b, Y); thread = (pixel, 8-channel chunk)
   const int H = 2 * h, W = 2 * w;
-  const size_t total = static_cast<size_t>(B) * H * W * 8;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int chunk = static_cast<int>(i & 7);
-    const size_t pix = i >> 3;
-    const int X = static_cast<int>(pix % W), Y = static_cast<int>((pix / W) % H);
-    const size_t b = pix / (static_cast<size_t>(W) * H);
+  const int Y = blockIdx.x % H;
+  const size_t b = blockIdx.x / H;
+  for (int i = threadIdx.x; i < W * 8; i += blockDim.x) {
+    const int chunk = i & 7;
+    const int X = i >> 3;
+    const size_t pix = (b * H + Y) * W + X;
     int x0, x1, y0, y1;
     float lx0, lx1, ly0, ly1;
     if (bilinear) {
@@ -460,7 +454,10 @@ __global__ void pack_weights_kernel(const float *__restrict__ w, uint16_t *__res
     const int g = (i / (64 * npad)) % G;
     const int tap = i / (64 * npad * G);
     const int ci = g * 64 + k;
-    const float v = (n < cout && ci < cin) ? w[(static_cast<size_t>(n) * cin + ci) * 9 + tap] : 0.f;
+    // 64-wide layers: GEMM column n carries output channel 16*((n%8)/2) + 2*(n/8) + n%2, so that the epilogue's
+    // 16x256b TMEM load leaves 16 CONSECUTIVE channels (32 B) of a pixel in each thread (isr_conv.cuh)
+    const int co = (npad == 64) ? (16 * ((n & 7) >> 1) + 2 * (n >> 3) + (n & 1)) : n;
+    const float v = (co < cout && ci < cin) ? w[(static_cast<size_t>(co) * cin + ci) * 9 + tap] : 0.f;
     const size_t part_stride = static_cast<size_t>(9) * G * npad * 64;
     const size_t o = ((static_cast<size_t>(tap) * G + g) * npad + n) * 64 + k;
     const __nv_bfloat16 bh = __float2bfloat16_rn(v);
@@ -483,28 +480,24 @@ static inline int grid_for(size_t total, int block) {
 }
 
 cudaError_t launch_flatten_high(const float *in, float *out, int B, int C, int H, int W, int r, cudaStream_t s) {
-  const size_t total = static_cast<size_t>(B) * C * H * W;
-  flatten_high_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, C, H, W, r);
+  flatten_high_kernel<<<B * C * H, 256, 0, s>>>(in, out, B, C, H, W, r);
   count_launch();
   return cudaGetLastError();
 }
 cudaError_t launch_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
                                 int special_mask, int align_corners, cudaStream_t s) {
-  const size_t total = static_cast<size_t>(B) * h * r * w * r;
-  warp_upscale_kernel<<<grid_for(total, 256), 256, 0, s>>>(prev, flow, out, B, C, h, w, r, special_mask, align_corners);
+  warp_upscale_kernel<<<B * h * r, 256, 0, s>>>(prev, flow, out, B, C, h, w, r, special_mask, align_corners);
   count_launch();
   return cudaGetLastError();
 }
 cudaError_t launch_initial_image(const float *in, float *out, int B, int Cin, int h, int w, int channels, int mode,
                                  int ao_inverted, int r, cudaStream_t s) {
-  const size_t total = static_cast<size_t>(B) * channels * h * r * w * r;
-  initial_image_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, Cin, h, w, channels, mode, ao_inverted, r);
+  initial_image_kernel<<<B * channels * h * r, 256, 0, s>>>(in, out, B, Cin, h, w, channels, mode, ao_inverted, r);
   count_launch();
   return cudaGetLastError();
 }
 cudaError_t launch_postprocess(const float *in, float *out, int B, int C, int H, int W, int unshaded, cudaStream_t s) {
-  const size_t total = static_cast<size_t>(B) * H * W;
-  postprocess_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, C, H, W, unshaded);
+  postprocess_kernel<<<B * H, 256, 0, s>>>(in, out, B, C, H, W, unshaded);
   count_launch();
   return cudaGetLastError();
 }
@@ -516,10 +509,13 @@ cudaError_t launch_shade(const float *in, const float *params22, float *out, int
   const float sf = static_cast<float>((static_cast<double>(expo) + 2.0) / (2.0 * 3.14159265358979323846));
   const size_t plane = static_cast<size_t>(H) * W;
   const bool vec = (plane % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
-  if (vec)
-    shade_kernel<4><<<grid_for(B * plane / 4, 256), 256, 0, s>>>(in, out, sp, sf, B, C, plane);
-  else
-    shade_kernel<1><<<grid_for(B * plane, 256), 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+  if (vec) {
+    dim3 grid(grid_for(plane / 4, 256), B);
+    shade_kernel<4><<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+  } else {
+    dim3 grid(grid_for(plane, 256), B);
+    shade_kernel<1><<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+  }
   count_launch();
   return cudaGetLastError();
 }
@@ -548,9 +544,7 @@ cudaError_t launch_unpack_nhwc(const uint16_t *in, float *out, int B, int H, int
 }
 cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, int w, int in_parts, int out_parts,
                               int in_bf16, int out_bf16, int bilinear, cudaStream_t s) {
-  const size_t total = static_cast<size_t>(B) * 4 * h * w * 8;
-  upsample2x_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, h, w, in_parts, out_parts, in_bf16, out_bf16,
-                                                             bilinear);
+  upsample2x_nhwc_kernel<<<B * 2 * h, 256, 0, s>>>(in, out, B, h, w, in_parts, out_parts, in_bf16, out_bf16, bilinear);
   count_launch();
   return cudaGetLastError();
 }
