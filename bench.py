@@ -137,8 +137,7 @@ def run_b200(args, rank, world, local_rank):
     import torch.distributed as dist
 
     import isosurfacesuperresolution_b200 as isr
-    from isosurfacesuperresolution_b200 import _lib, ops
-    from oracle import oracle as orc          # synthetic input generator only (shared with the tests)
+    from isosurfacesuperresolution_b200 import _lib, sharding, synthetic   # the product leg never imports oracle/
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -160,7 +159,7 @@ def run_b200(args, rank, world, local_rank):
 
     B, T, h, w = B_SEQ, T_FRAMES, H_LOW, W_LOW
     # 2 distinct sequences generated on the host, tiled to B (generation cost only), per-rank seed
-    low_np, flow_np, _ = orc.synthetic_gbuffer(2, h, w, 4321 + 1 + rank, T=T)
+    low_np, flow_np, _ = synthetic.synthetic_gbuffer(2, h, w, sharding.rank_seed(4321 + 1, rank), T=T)
     low = torch.from_numpy(np.tile(low_np, (B // 2, 1, 1, 1, 1))).to(dev)
     flow = torch.from_numpy(np.tile(flow_np, (B // 2, 1, 1, 1, 1))).to(dev)
     H, W = 4 * h, 4 * w
