@@ -23,6 +23,7 @@ static std::atomic<uint64_t> g_launches{0};
 static int g_halo_pitch = 10;
 static int g_base_offset_mode = 0;
 static int g_max_ctas = 0;
+static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
@@ -116,9 +117,13 @@ static int num_sms() {
 static int setup_kernel_attrs() {
   static bool done = false;
   if (done) return ISR_OK;
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<64, EPI_STORE16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<64, EPI_STORE16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<64, EPI_STORE16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   done = true;
   return ISR_OK;
@@ -155,10 +160,15 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
 }
 
 static int run_conv(const ConvLaunch &L, cudaStream_t s) {
-  if (L.n == 64)
-    conv3x3_umma_kernel<64, EPI_STORE16><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+  const bool stack = L.p.n_w_parts == 2 && g_stack_w;
+  if (L.n == 64 && stack)
+    conv3x3_umma_kernel<64, EPI_STORE16, 1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+  else if (L.n == 64)
+    conv3x3_umma_kernel<64, EPI_STORE16, 0><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+  else if (stack)
+    conv3x3_umma_kernel<16, EPI_FINAL, 1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   else
-    conv3x3_umma_kernel<16, EPI_FINAL><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    conv3x3_umma_kernel<16, EPI_FINAL, 0><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   count_launch();
   ISR_CUDA(cudaGetLastError());
   return ISR_OK;
@@ -168,14 +178,18 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
 struct Scheme {
   int bf16, na, nw;  // operand format, activation parts, weight parts
 };
-static bool get_schemes(int precision, Scheme *trunk, Scheme *tail) {
+static bool get_schemes(int precision, Scheme *trunk, Scheme *tail, int *fin_nw = nullptr) {
+  int dummy;
+  if (fin_nw == nullptr) fin_nw = &dummy;
+  *fin_nw = 0;  // 0 = same as the tail
   switch (precision) {
     case ISR_PREC_BF16: *trunk = {1, 1, 1}; *tail = {1, 1, 1}; return true;
     case ISR_PREC_BF16X3: *trunk = {1, 2, 2}; *tail = {1, 2, 2}; return true;
-    case ISR_PREC_MIXED: *trunk = {1, 2, 2}; *tail = {0, 1, 1}; return true;
+    case ISR_PREC_MIXED: *trunk = {1, 2, 2}; *tail = {0, 1, 1}; *fin_nw = 2; return true;
     case ISR_PREC_FP16: *trunk = {0, 1, 1}; *tail = {0, 1, 1}; return true;
     case ISR_PREC_FP16X3: *trunk = {0, 2, 2}; *tail = {0, 2, 2}; return true;
     case ISR_PREC_MIXED2: *trunk = {1, 2, 2}; *tail = {0, 2, 1}; return true;
+    case ISR_PREC_MIXED3: *trunk = {1, 2, 2}; *tail = {0, 1, 2}; return true;
   }
   return false;
 }
@@ -193,6 +207,7 @@ struct Plan {
   int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0;
   void *ws = nullptr;
   Scheme trunk, tail;
+  int fin_nw = 0;
   uint16_t *in_g[2] = {nullptr, nullptr};
   std::vector<ConvLaunch> convs;  // in execution order
   // pointwise steps interleaved with convs: up2 after conv index up_after[0], up4 after up_after[1]
@@ -250,7 +265,8 @@ static int conv_for_layer(ConvLaunch *L, const Layer &ly, int g, const uint16_t 
 }
 
 static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
-  if (!get_schemes(precision, &pl->trunk, &pl->tail)) return fail(ISR_ERR_ARG, "unknown precision %d", precision);
+  if (!get_schemes(precision, &pl->trunk, &pl->tail, &pl->fin_nw))
+    return fail(ISR_ERR_ARG, "unknown precision %d", precision);
   size_t offs[9];
   const size_t need = plan_bytes(net, B, h, w, pl->trunk, pl->tail, offs);
   if (ws == nullptr || ws_bytes < need)
@@ -310,7 +326,9 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   set_store(&L, net->layers[23].bias, 1, nullptr, 0, pl->u4, Hs.na);
   pl->convs.push_back(L);
   pl->idx_final = static_cast<int>(pl->convs.size());
-  if ((rc = conv_for_layer(&L, net->layers[24], 0, pl->u4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
+  Scheme Fs = Hs;
+  if (pl->fin_nw > 0) Fs.nw = pl->fin_nw;
+  if ((rc = conv_for_layer(&L, net->layers[24], 0, pl->u4, B, 4 * h, 4 * w, Fs)) != ISR_OK) return rc;
   L.p.bias = net->layers[24].bias;
   L.p.cout = net->cout;
   L.p.n_mask = net->n_mask;
@@ -406,6 +424,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "max_ctas") == 0) {
     if (value < 0) return fail(ISR_ERR_ARG, "max_ctas must be >= 0");
     slot = &g_max_ctas;
+  } else if (key != nullptr && strcmp(key, "stack_w") == 0) {
+    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "stack_w must be 0 or 1");
+    slot = &g_stack_w;
   } else {
     return fail(ISR_ERR_ARG, "unknown tunable");
   }

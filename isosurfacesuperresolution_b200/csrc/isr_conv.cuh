@@ -83,7 +83,10 @@ __device__ __forceinline__ void bil_src(int dst, int n_in, float inv_scale, int 
   l0 = 1.f - t;
 }
 
-template <int N, int EPI>
+// STACK = 1 (split precision, N = 64 only): the hi and lo weight planes of a tap sit back to back in shared memory and
+// are ONE N=128 B operand, so A_hi*W_hi^T and A_hi*W_lo^T are a single M128xN128 MMA (67.7 cycles measured) instead of two
+// N=64 MMAs (2 x 53.9, profiles/r01_probe_mma_cycles.json); the epilogue adds accumulator columns c and 64+c.
+template <int N, int EPI, int STACK>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const ConvParams p) {
@@ -118,7 +121,8 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     fence_barrier_init();
   }
-  constexpr uint32_t kTmemCols = (2 * N < 32) ? 32 : 2 * N;
+  constexpr uint32_t kAccCols = STACK ? 2 * N : N;   // TMEM columns of one accumulator buffer
+  constexpr uint32_t kTmemCols = (2 * kAccCols < 32) ? 32 : 2 * kAccCols;
   if (warp == 9) tmem_alloc(s_tptr, kTmemCols);
   tc_fence_before();
   __syncthreads();
@@ -135,7 +139,8 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_arrive_expect_tx(b_w, w_bytes);
       for (int wp = 0; wp < p.n_w_parts; ++wp)
         for (int tap = 0; tap < 9; ++tap)
-          tma_load_2d(s_w + (wp * 9 + tap) * kWTapBytes, &tmW, b_w, 0, p.w_row0 + (wp * 9 + tap) * p.w_row_stride);
+          tma_load_2d(s_w + (STACK ? (tap * 2 + wp) : (wp * 9 + tap)) * kWTapBytes, &tmW, b_w, 0,
+                      p.w_row0 + (wp * 9 + tap) * p.w_row_stride);
     }
     __syncwarp();
     uint32_t it = 0;
@@ -158,6 +163,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp == 9) {
     // ===================== MMA issuer (whole warp runs the loop; one elected lane issues) =====================
     const uint32_t idesc = make_idesc_f16(128, N, p.is_bf16);
+    const uint32_t idesc2 = make_idesc_f16(128, 2 * N, p.is_bf16);   // STACK: [W_hi ; W_lo] as one N=128 operand
     const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
     mbar_wait(b_w, 0);
     uint32_t it = 0;
@@ -166,7 +172,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t acc_ph = (i >> 1) & 1;
       mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
       tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * N;
+      const uint32_t d_tmem = tmem_base + acc * kAccCols;
       uint32_t first = 1;
       for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
         const uint32_t s = it % p.num_stages;
@@ -175,18 +181,28 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tc_fence_after();
         const uint32_t a_base = s_stage0 + s * p.stage_bytes;
         const uint64_t a_desc0 = make_smem_desc_sw128(a_base, kPitch * 128, 0);
-        const int nwp = (ap == 0) ? p.n_w_parts : 1;  // (hi,hi) (hi,lo) | (lo,hi)
         if (elect_one()) {
-          for (int wp = 0; wp < nwp; ++wp) {
-            const uint64_t b_desc0 = b_desc_base + static_cast<uint64_t>((wp * 9 * kWTapBytes) >> 4);
+          if constexpr (STACK) {
+            // pass 0: A_hi x [W_hi ; W_lo] (N=128, zero-initialises all 128 columns); pass 1: A_lo x W_hi (N=64)
 #pragma unroll
             for (int tap = 0; tap < 9; ++tap) {
-              // tap (ky,kx): the same halo tile, start address shifted by (ky*pitch + kx) pixel rows of 128 B
               const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
-              const uint64_t bdesc = b_desc0 + static_cast<uint64_t>((tap * kWTapBytes) >> 4);
-              umma_f16_k64(d_tmem, adesc, bdesc, idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
+              const uint64_t bdesc = b_desc_base + static_cast<uint64_t>((tap * 2 * kWTapBytes) >> 4);
+              umma_f16_k64(d_tmem, adesc, bdesc, ap == 0 ? idesc2 : idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
             }
-            first = 0;
+          } else {
+            const int nwp = (ap == 0) ? p.n_w_parts : 1;  // (hi,hi) (hi,lo) | (lo,hi)
+            for (int wp = 0; wp < nwp; ++wp) {
+              const uint64_t b_desc0 = b_desc_base + static_cast<uint64_t>((wp * 9 * kWTapBytes) >> 4);
+#pragma unroll
+              for (int tap = 0; tap < 9; ++tap) {
+                // tap (ky,kx): the same halo tile, start address shifted by (ky*pitch + kx) pixel rows of 128 B
+                const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
+                const uint64_t bdesc = b_desc0 + static_cast<uint64_t>((tap * kWTapBytes) >> 4);
+                umma_f16_k64(d_tmem, adesc, bdesc, idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
+              }
+              first = 0;
+            }
           }
           umma_commit(b_empty + 8 * s);  // frees this halo stage when its MMAs retire
           if (ap == p.n_act_parts - 1) umma_commit(b_tfull + 8 * acc);  // accumulator complete -> epilogue
@@ -205,7 +221,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int b = t / (p.tiles_x * p.tiles_y);
       const uint32_t acc = grp;
       const uint32_t acc_ph = (i >> 1) & 1;
-      const uint32_t taddr = tmem_base + acc * N + (static_cast<uint32_t>(q * 32) << 16);
+      const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
       if constexpr (EPI == EPI_STORE16) {
         // thread (m = lane%4, rr = lane/4): pixel column rr of image rows 4q..4q+3 of the tile, channels 16m..16m+15
         const int m = lane & 3, rr = lane >> 2;
@@ -213,13 +229,42 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         float bias_r[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) bias_r[j] = s_bias[16 * m + j];
+        // residual addend (the block's skip): fetched BEFORE waiting for the accumulator, so its HBM latency hides
+        // behind the tile's MMAs.  ad[pixel j = 2*half+hh][part][2 x 16 B]
+        uint4 ad[4][2][2];
+        const bool has_add = p.addend != nullptr;
+        if (has_add) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int y = ty * kTileH + 4 * q + j;
+            const bool ok = (y < p.H) && (x < p.W);
+            const size_t pix = (static_cast<size_t>(b) * p.H + (ok ? y : 0)) * p.W + (ok ? x : 0);
+#pragma unroll
+            for (int ap = 0; ap < 2; ++ap) {
+              if (ap < p.add_parts) {
+                const uint4 *src =
+                    reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m);
+                ad[j][ap][0] = __ldg(src);
+                ad[j][ap][1] = __ldg(src + 1);
+              }
+            }
+          }
+        }
         mbar_wait(b_tfull + 8 * acc, acc_ph);
         tc_fence_after();
-#pragma unroll 1
+#pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
           tmem_ld_16x256b_x8(taddr + (static_cast<uint32_t>(half * 16) << 16), v);
-          tmem_ld_wait();
+          if constexpr (STACK) {
+            uint32_t v2[32];
+            tmem_ld_16x256b_x8(taddr + N + (static_cast<uint32_t>(half * 16) << 16), v2);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
+          } else {
+            tmem_ld_wait();
+          }
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
             const int y = ty * kTileH + 4 * q + 2 * half + hh;
@@ -231,17 +276,18 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 f[2 * rep] = __uint_as_float(v[4 * rep + 2 * hh]) + bias_r[2 * rep];
                 f[2 * rep + 1] = __uint_as_float(v[4 * rep + 2 * hh + 1]) + bias_r[2 * rep + 1];
               }
-              if (p.addend != nullptr) {
-                for (int ap = 0; ap < p.add_parts; ++ap) {
-                  const uint4 *src =
-                      reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m);
-                  const uint4 q0 = __ldg(src), q1 = __ldg(src + 1);
-                  const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+              if (has_add) {
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) {
-                    const float2 a = unpack2(w[j], p.is_bf16);
-                    f[2 * j] += a.x;
-                    f[2 * j + 1] += a.y;
+                for (int ap = 0; ap < 2; ++ap) {
+                  if (ap < p.add_parts) {
+                    const uint4 q0 = ad[2 * half + hh][ap][0], q1 = ad[2 * half + hh][ap][1];
+                    const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                      const float2 a = unpack2(w[j], p.is_bf16);
+                      f[2 * j] += a.x;
+                      f[2 * j + 1] += a.y;
+                    }
                   }
                 }
               }
@@ -310,7 +356,15 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tc_fence_after();
         uint32_t v[16];
         tmem_ld16(taddr, v);
-        tmem_ld_wait();
+        if constexpr (STACK) {   // columns 16..31 hold A x W_lo^T
+          uint32_t v2[16];
+          tmem_ld16(taddr + N, v2);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 16; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
+        } else {
+          tmem_ld_wait();
+        }
         if (inb) {
           const size_t plane = static_cast<size_t>(p.H) * p.W;
           const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;

@@ -387,58 +387,88 @@ shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams 
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// nn.Upsample(scale_factor=2, mode) on NHWC 16-bit 64-channel features (enhancenet.py:40-48,116,119)
-// one thread = one output pixel x 8 channels (16 B); input parts are summed in fp32, output re-split.
+// nn.Upsample(scale_factor=2, mode) on NHWC 16-bit 64-channel features (enhancenet.py:40-48,116,119).
+// One thread = one SOURCE pixel (i, j) x one 8-channel chunk (16 B): it loads the 3x3 source neighbourhood once (9 x 16 B
+// per input part, all loads issued up front) and writes the 2x2 output block.  Output 2j uses source columns
+// (j-1, j), output 2j+1 uses (j, j+1) (align_corners=False, index clamp at the borders); the weights come from the same
+// bil_src_pw() as every other bilinear site, so the arithmetic (x first, then y, FMA placement) is unchanged.
+// Input parts are summed in fp32, the output is re-split into hi/lo when out_parts == 2.
+__device__ __forceinline__ void load_chunk_sum(const uint16_t *__restrict__ src, int in_parts, int in_bf16, float *v) {
+  uint4 q[2];
+  q[0] = __ldg(reinterpret_cast<const uint4 *>(src));
+  if (in_parts == 2) q[1] = __ldg(reinterpret_cast<const uint4 *>(src + 64));
+  const uint32_t u[4] = {q[0].x, q[0].y, q[0].z, q[0].w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 f2 = unpack2_pw(u[j], in_bf16);
+    v[2 * j] = f2.x;
+    v[2 * j + 1] = f2.y;
+  }
+  if (in_parts == 2) {
+    const uint32_t l[4] = {q[1].x, q[1].y, q[1].z, q[1].w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f2 = unpack2_pw(l[j], in_bf16);
+      v[2 * j] += f2.x;
+      v[2 * j + 1] += f2.y;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 upsample2x_nhwc_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out, int B, int h, int w, int in_parts,
                        int out_parts, int in_bf16, int out_bf16, int bilinear) {
-  // one block per output row (b, Y); thread = (pixel, 8-channel chunk)
   const int H = 2 * h, W = 2 * w;
-  const int Y = blockIdx.x % H;
-  const size_t b = blockIdx.x / H;
-  for (int i = threadIdx.x; i < W * 8; i += blockDim.x) {
-    const int chunk = i & 7;
-    const int X = i >> 3;
-    const size_t pix = (b * H + Y) * W + X;
-    int x0, x1, y0, y1;
-    float lx0, lx1, ly0, ly1;
-    if (bilinear) {
-      bil_src_pw(X, w, 0.5f, x0, x1, lx0, lx1);
-      bil_src_pw(Y, h, 0.5f, y0, y1, ly0, ly1);
-    } else {
-      x0 = x1 = X >> 1; y0 = y1 = Y >> 1;
-      lx0 = ly0 = 1.f; lx1 = ly1 = 0.f;
+  const size_t total = static_cast<size_t>(B) * h * w * 8;
+  const size_t in_pitch = static_cast<size_t>(64) * in_parts, out_pitch = static_cast<size_t>(64) * out_parts;
+  for (size_t idx = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int chunk = static_cast<int>(idx & 7);
+    const size_t sp = idx >> 3;
+    const int j = static_cast<int>(sp % w);
+    const int i = static_cast<int>((sp / w) % h);
+    const size_t b = sp / (static_cast<size_t>(w) * h);
+    const uint16_t *img = in + b * h * w * in_pitch + chunk * 8;
+    uint16_t *obase = out + ((b * H + 2 * i) * W + 2 * j) * out_pitch;
+    if (!bilinear) {
+      float v[8];
+      load_chunk_sum(img + (static_cast<size_t>(i) * w + j) * in_pitch, in_parts, in_bf16, v);
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx)
+          store_chunk8(obase + (static_cast<size_t>(dy) * W + dx) * out_pitch, chunk, out_parts, v, out_bf16);
+      continue;
     }
-    float v[4][8];
-    const int ys[4] = {y0, y0, y1, y1}, xs[4] = {x0, x1, x0, x1};
-    const int ntap = bilinear ? 4 : 1;
-    for (int t = 0; t < ntap; ++t) {
-      const uint16_t *src = in + ((b * h + ys[t]) * w + xs[t]) * (64 * in_parts) + chunk * 8;
+    const int rows[3] = {i > 0 ? i - 1 : 0, i, i < h - 1 ? i + 1 : h - 1};
+    const int cols[3] = {j > 0 ? j - 1 : 0, j, j < w - 1 ? j + 1 : w - 1};
+    float v[3][3][8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[t][j] = 0.f;
-      for (int pt = 0; pt < in_parts; ++pt) {
-        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(src + pt * 64));
-        const uint32_t u[4] = {q.x, q.y, q.z, q.w};
+    for (int r = 0; r < 3; ++r)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 f2 = unpack2_pw(u[j], in_bf16);
-          v[t][2 * j] += f2.x;
-          v[t][2 * j + 1] += f2.y;
+      for (int c = 0; c < 3; ++c)
+        load_chunk_sum(img + (static_cast<size_t>(rows[r]) * w + cols[c]) * in_pitch, in_parts, in_bf16, v[r][c]);
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+      int y0, y1;
+      float ly0, ly1;
+      bil_src_pw(2 * i + dy, h, 0.5f, y0, y1, ly0, ly1);
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        int x0, x1;
+        float lx0, lx1;
+        bil_src_pw(2 * j + dx, w, 0.5f, x0, x1, lx0, lx1);
+        float f[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          // taps: rows (dy, dy+1), columns (dx, dx+1) of the neighbourhood
+          const float r0 = fmaf(lx0, v[dy][dx][k], lx1 * v[dy][dx + 1][k]);
+          const float r1 = fmaf(lx0, v[dy + 1][dx][k], lx1 * v[dy + 1][dx + 1][k]);
+          f[k] = fmaf(ly0, r0, ly1 * r1);
         }
+        store_chunk8(obase + (static_cast<size_t>(dy) * W + dx) * out_pitch, chunk, out_parts, f, out_bf16);
       }
     }
-    float f[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      if (bilinear) {
-        const float r0 = fmaf(lx0, v[0][j], lx1 * v[1][j]);
-        const float r1 = fmaf(lx0, v[2][j], lx1 * v[3][j]);
-        f[j] = fmaf(ly0, r0, ly1 * r1);
-      } else {
-        f[j] = v[0][j];
-      }
-    }
-    store_chunk8(out + pix * (64 * out_parts), chunk, out_parts, f, out_bf16);
   }
 }
 
@@ -544,7 +574,9 @@ cudaError_t launch_unpack_nhwc(const uint16_t *in, float *out, int B, int H, int
 }
 cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, int w, int in_parts, int out_parts,
                               int in_bf16, int out_bf16, int bilinear, cudaStream_t s) {
-  upsample2x_nhwc_kernel<<<B * 2 * h, 256, 0, s>>>(in, out, B, h, w, in_parts, out_parts, in_bf16, out_bf16, bilinear);
+  const size_t total = static_cast<size_t>(B) * h * w * 8;
+  upsample2x_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, h, w, in_parts, out_parts, in_bf16, out_bf16,
+                                                             bilinear);
   count_launch();
   return cudaGetLastError();
 }
