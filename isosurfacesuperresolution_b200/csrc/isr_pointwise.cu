@@ -388,85 +388,123 @@ shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams 
 
 // ------------------------------------------------------------------------------------------------------------
 // nn.Upsample(scale_factor=2, mode) on NHWC 16-bit 64-channel features (enhancenet.py:40-48,116,119).
-// One thread = one SOURCE pixel (i, j) x one 8-channel chunk (16 B): it loads the 3x3 source neighbourhood once (9 x 16 B
-// per input part, all loads issued up front) and writes the 2x2 output block.  Output 2j uses source columns
-// (j-1, j), output 2j+1 uses (j, j+1) (align_corners=False, index clamp at the borders); the weights come from the same
-// bil_src_pw() as every other bilinear site, so the arithmetic (x first, then y, FMA placement) is unchanged.
-// Input parts are summed in fp32, the output is re-split into hi/lo when out_parts == 2.
-__device__ __forceinline__ void load_chunk_sum(const uint16_t *__restrict__ src, int in_parts, int in_bf16, float *v) {
-  uint4 q[2];
-  q[0] = __ldg(reinterpret_cast<const uint4 *>(src));
-  if (in_parts == 2) q[1] = __ldg(reinterpret_cast<const uint4 *>(src + 64));
-  const uint32_t u[4] = {q[0].x, q[0].y, q[0].z, q[0].w};
+// One thread = one source column j x one 8-channel chunk (16 B), walking down a strip of kUpStrip source rows.  Per
+// source row it loads 3 x 16 B (columns j-1, j, j+1), forms the two horizontal interpolants (output columns 2j, 2j+1) and
+// keeps those of the last three rows in registers; the two output rows 2i, 2i+1 are vertical interpolations of them.
+// Weights come from the same bil_src_pw() as every other bilinear site and the operation order is unchanged
+// (x first: fmaf(lx0, a, lx1*b); then y: fmaf(ly0, r0, ly1*r1)); borders clamp the index as torch does.
+// Everything format-dependent is a template parameter: the kernel must stay under ~300 issue slots per 64 B written to
+// be HBM-bound rather than issue-bound (the generic version ran at 1.25 TB/s).
+constexpr int kUpStrip = 8;
+
+template <int IN_PARTS, int IN_BF16>
+__device__ __forceinline__ void load_chunk_sum(const uint16_t *__restrict__ src, float *v) {
+  const uint4 q0 = __ldg(reinterpret_cast<const uint4 *>(src));
+  const uint32_t u[4] = {q0.x, q0.y, q0.z, q0.w};
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const float2 f2 = unpack2_pw(u[j], in_bf16);
+    const float2 f2 = unpack2_pw(u[j], IN_BF16);
     v[2 * j] = f2.x;
     v[2 * j + 1] = f2.y;
   }
-  if (in_parts == 2) {
-    const uint32_t l[4] = {q[1].x, q[1].y, q[1].z, q[1].w};
+  if constexpr (IN_PARTS == 2) {
+    const uint4 q1 = __ldg(reinterpret_cast<const uint4 *>(src + 64));
+    const uint32_t l[4] = {q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const float2 f2 = unpack2_pw(l[j], in_bf16);
+      const float2 f2 = unpack2_pw(l[j], IN_BF16);
       v[2 * j] += f2.x;
       v[2 * j + 1] += f2.y;
     }
   }
 }
 
+template <int OUT_PARTS, int OUT_BF16>
+__device__ __forceinline__ void store_chunk8_t(uint16_t *dst_pix, int chunk, const float *f) {
+  uint32_t hi[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) hi[j] = pack2_pw(f[2 * j], f[2 * j + 1], OUT_BF16);
+  *reinterpret_cast<uint4 *>(dst_pix + chunk * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  if constexpr (OUT_PARTS == 2) {
+    uint32_t lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 hf = unpack2_pw(hi[j], OUT_BF16);
+      lo[j] = pack2_pw(f[2 * j] - hf.x, f[2 * j + 1] - hf.y, OUT_BF16);
+    }
+    *reinterpret_cast<uint4 *>(dst_pix + 64 + chunk * 8) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
+}
+
+template <int IN_PARTS, int IN_BF16, int OUT_PARTS, int OUT_BF16, int BILINEAR>
 __global__ void __launch_bounds__(256)
-upsample2x_nhwc_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out, int B, int h, int w, int in_parts,
-                       int out_parts, int in_bf16, int out_bf16, int bilinear) {
+upsample2x_nhwc_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ out, int B, int h, int w) {
   const int H = 2 * h, W = 2 * w;
-  const size_t total = static_cast<size_t>(B) * h * w * 8;
-  const size_t in_pitch = static_cast<size_t>(64) * in_parts, out_pitch = static_cast<size_t>(64) * out_parts;
-  for (size_t idx = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; idx < total;
-       idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int chunk = static_cast<int>(idx & 7);
-    const size_t sp = idx >> 3;
-    const int j = static_cast<int>(sp % w);
-    const int i = static_cast<int>((sp / w) % h);
-    const size_t b = sp / (static_cast<size_t>(w) * h);
-    const uint16_t *img = in + b * h * w * in_pitch + chunk * 8;
-    uint16_t *obase = out + ((b * H + 2 * i) * W + 2 * j) * out_pitch;
-    if (!bilinear) {
+  const int item = blockIdx.x * 256 + threadIdx.x;   // (j, chunk)
+  if (item >= w * 8) return;
+  const int chunk = item & 7, j = item >> 3;
+  const int nstrips = (h + kUpStrip - 1) / kUpStrip;
+  const int strip = blockIdx.y % nstrips;
+  const size_t b = blockIdx.y / nstrips;
+  const int i0 = strip * kUpStrip;
+  const int i1 = min(i0 + kUpStrip, h);
+  constexpr size_t in_pitch = 64 * IN_PARTS, out_pitch = 64 * OUT_PARTS;
+  const uint16_t *img = in + b * h * w * in_pitch + chunk * 8;
+  uint16_t *oimg = out + b * H * W * out_pitch;
+  if constexpr (!BILINEAR) {
+    for (int i = i0; i < i1; ++i) {
       float v[8];
-      load_chunk_sum(img + (static_cast<size_t>(i) * w + j) * in_pitch, in_parts, in_bf16, v);
+      load_chunk_sum<IN_PARTS, IN_BF16>(img + (static_cast<size_t>(i) * w + j) * in_pitch, v);
 #pragma unroll
       for (int dy = 0; dy < 2; ++dy)
 #pragma unroll
         for (int dx = 0; dx < 2; ++dx)
-          store_chunk8(obase + (static_cast<size_t>(dy) * W + dx) * out_pitch, chunk, out_parts, v, out_bf16);
-      continue;
+          store_chunk8_t<OUT_PARTS, OUT_BF16>(oimg + (static_cast<size_t>(2 * i + dy) * W + 2 * j + dx) * out_pitch, chunk, v);
     }
-    const int rows[3] = {i > 0 ? i - 1 : 0, i, i < h - 1 ? i + 1 : h - 1};
-    const int cols[3] = {j > 0 ? j - 1 : 0, j, j < w - 1 ? j + 1 : w - 1};
-    float v[3][3][8];
+    return;
+  }
+  const int cm = j > 0 ? j - 1 : 0, cp = j < w - 1 ? j + 1 : w - 1;
+  float lx[2][2];
+  {
+    int a0, a1;
+    bil_src_pw(2 * j, w, 0.5f, a0, a1, lx[0][0], lx[0][1]);
+    bil_src_pw(2 * j + 1, w, 0.5f, a0, a1, lx[1][0], lx[1][1]);
+  }
+  float hx[3][2][8];   // horizontal interpolants of source rows i-1, i, i+1 for output columns 2j, 2j+1
+  auto hrow = [&](int r, float (*dst)[8]) {
+    const uint16_t *rowp = img + static_cast<size_t>(r) * w * in_pitch;
+    float vm[8], vc[8], vp[8];
+    load_chunk_sum<IN_PARTS, IN_BF16>(rowp + static_cast<size_t>(cm) * in_pitch, vm);
+    load_chunk_sum<IN_PARTS, IN_BF16>(rowp + static_cast<size_t>(j) * in_pitch, vc);
+    load_chunk_sum<IN_PARTS, IN_BF16>(rowp + static_cast<size_t>(cp) * in_pitch, vp);
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
+    for (int k = 0; k < 8; ++k) {
+      dst[0][k] = fmaf(lx[0][0], vm[k], lx[0][1] * vc[k]);
+      dst[1][k] = fmaf(lx[1][0], vc[k], lx[1][1] * vp[k]);
+    }
+  };
+  hrow(i0 > 0 ? i0 - 1 : 0, hx[1]);
+  hrow(i0, hx[2]);
+  for (int i = i0; i < i1; ++i) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c)
-        load_chunk_sum(img + (static_cast<size_t>(rows[r]) * w + cols[c]) * in_pitch, in_parts, in_bf16, v[r][c]);
+    for (int d = 0; d < 2; ++d)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        hx[0][d][k] = hx[1][d][k];
+        hx[1][d][k] = hx[2][d][k];
+      }
+    hrow(i < h - 1 ? i + 1 : h - 1, hx[2]);
 #pragma unroll
     for (int dy = 0; dy < 2; ++dy) {
-      int y0, y1;
+      int a0, a1;
       float ly0, ly1;
-      bil_src_pw(2 * i + dy, h, 0.5f, y0, y1, ly0, ly1);
+      bil_src_pw(2 * i + dy, h, 0.5f, a0, a1, ly0, ly1);
 #pragma unroll
       for (int dx = 0; dx < 2; ++dx) {
-        int x0, x1;
-        float lx0, lx1;
-        bil_src_pw(2 * j + dx, w, 0.5f, x0, x1, lx0, lx1);
         float f[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          // taps: rows (dy, dy+1), columns (dx, dx+1) of the neighbourhood
-          const float r0 = fmaf(lx0, v[dy][dx][k], lx1 * v[dy][dx + 1][k]);
-          const float r1 = fmaf(lx0, v[dy + 1][dx][k], lx1 * v[dy + 1][dx + 1][k]);
-          f[k] = fmaf(ly0, r0, ly1 * r1);
-        }
-        store_chunk8(obase + (static_cast<size_t>(dy) * W + dx) * out_pitch, chunk, out_parts, f, out_bf16);
+        for (int k = 0; k < 8; ++k) f[k] = fmaf(ly0, hx[dy][dx][k], ly1 * hx[dy + 1][dx][k]);
+        store_chunk8_t<OUT_PARTS, OUT_BF16>(oimg + (static_cast<size_t>(2 * i + dy) * W + 2 * j + dx) * out_pitch, chunk, f);
       }
     }
   }
@@ -572,11 +610,27 @@ cudaError_t launch_unpack_nhwc(const uint16_t *in, float *out, int B, int H, int
   count_launch();
   return cudaGetLastError();
 }
+template <int IP, int IB, int OP, int OB>
+static void launch_up_t(const uint16_t *in, uint16_t *out, int B, int h, int w, int bilinear, dim3 grid, cudaStream_t s) {
+  if (bilinear)
+    upsample2x_nhwc_kernel<IP, IB, OP, OB, 1><<<grid, 256, 0, s>>>(in, out, B, h, w);
+  else
+    upsample2x_nhwc_kernel<IP, IB, OP, OB, 0><<<grid, 256, 0, s>>>(in, out, B, h, w);
+}
 cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, int w, int in_parts, int out_parts,
                               int in_bf16, int out_bf16, int bilinear, cudaStream_t s) {
-  const size_t total = static_cast<size_t>(B) * h * w * 8;
-  upsample2x_nhwc_kernel<<<grid_for(total, 256), 256, 0, s>>>(in, out, B, h, w, in_parts, out_parts, in_bf16, out_bf16,
-                                                             bilinear);
+  const int nstrips = (h + kUpStrip - 1) / kUpStrip;
+  dim3 grid((w * 8 + 255) / 256, B * nstrips);
+  const int key = (in_parts == 2 ? 8 : 0) | (in_bf16 ? 4 : 0) | (out_parts == 2 ? 2 : 0) | (out_bf16 ? 1 : 0);
+  switch (key) {
+#define ISR_UP_CASE(k, IP, IB, OP, OB) \
+  case k: launch_up_t<IP, IB, OP, OB>(in, out, B, h, w, bilinear, grid, s); break;
+    ISR_UP_CASE(0, 1, 0, 1, 0) ISR_UP_CASE(1, 1, 0, 1, 1) ISR_UP_CASE(2, 1, 0, 2, 0) ISR_UP_CASE(3, 1, 0, 2, 1)
+    ISR_UP_CASE(4, 1, 1, 1, 0) ISR_UP_CASE(5, 1, 1, 1, 1) ISR_UP_CASE(6, 1, 1, 2, 0) ISR_UP_CASE(7, 1, 1, 2, 1)
+    ISR_UP_CASE(8, 2, 0, 1, 0) ISR_UP_CASE(9, 2, 0, 1, 1) ISR_UP_CASE(10, 2, 0, 2, 0) ISR_UP_CASE(11, 2, 0, 2, 1)
+    ISR_UP_CASE(12, 2, 1, 1, 0) ISR_UP_CASE(13, 2, 1, 1, 1) ISR_UP_CASE(14, 2, 1, 2, 0) ISR_UP_CASE(15, 2, 1, 2, 1)
+#undef ISR_UP_CASE
+  }
   count_launch();
   return cudaGetLastError();
 }
