@@ -14,6 +14,7 @@
 
 #include "../../include/isr.h"
 #include "isr_conv.cuh"
+#include "isr_conv_final.cuh"
 #include "isr_internal.h"
 
 namespace isr {
@@ -23,6 +24,7 @@ static std::atomic<uint64_t> g_launches{0};
 static int g_halo_pitch = 10;
 static int g_base_offset_mode = 0;
 static int g_max_ctas = 0;
+static int g_final_stacked = 1;   // output conv: tap-stacked kernel (isr_conv_final.cuh) when Cout <= 8
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
@@ -97,6 +99,7 @@ struct ConvLaunch {
   CUtensorMap tmA, tmW;
   ConvParams p;
   int n;  // 64 (EPI_STORE16) or 16 (EPI_FINAL)
+  int cp = 0;  // > 0: tap-stacked output conv (conv3x3_final_kernel<cp>)
   size_t smem;
   int grid;
 };
@@ -124,6 +127,12 @@ static int setup_kernel_attrs() {
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   done = true;
   return ISR_OK;
@@ -159,7 +168,55 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   return make_w_map(&L->tmW, wpacked, w_rows_total, n, is_bf16);
 }
 
+static int final_cp(int cout) { return cout <= 4 ? 4 : (cout <= 6 ? 6 : 8); }
+static int final_rows(int cp) { return (9 * cp + 15) / 16 * 16; }
+static size_t final_pbytes(int cp) {
+  const int ld = (9 * cp + 7) / 8 * 8;
+  const int pitch4 = ((ld / 4) % 2 == 0) ? ld / 4 + 1 : ld / 4;
+  return align_up(static_cast<size_t>(kPitch) * kHaloH * pitch4 * 16, 1024);
+}
+
+// tap-stacked output conv: wpacked = [part 2][nrows][64] of the chosen format
+static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H, int W, int n_act_parts,
+                           const void *wpacked, int n_w_parts, int is_bf16) {
+  memset(&L->p, 0, sizeof L->p);
+  const int nrows = final_rows(cp);
+  L->n = nrows;
+  L->cp = cp;
+  ConvParams &p = L->p;
+  p.B = B; p.H = H; p.W = W;
+  p.tiles_x = (W + kTileW - 1) / kTileW;
+  p.tiles_y = (H + kTileH - 1) / kTileH;
+  p.num_tiles = p.tiles_x * p.tiles_y * B;
+  p.n_act_parts = n_act_parts;
+  p.n_w_parts = n_w_parts;
+  p.is_bf16 = is_bf16;
+  p.w_row0 = 0;
+  p.w_row_stride = nrows;
+  const size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * nrows * 128, 1024);
+  p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kPitch) * kHaloH * 128, 1024));
+  const size_t fixed = 1024 + w_bytes + 2 * final_pbytes(cp) + 256;
+  int stages = static_cast<int>((kSmemLimit - kStaticSmem - fixed) / p.stage_bytes);
+  if (stages > 8) stages = 8;
+  if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "final conv smem plan: fewer than 2 halo stages fit");
+  p.num_stages = stages;
+  L->smem = fixed + static_cast<size_t>(stages) * p.stage_bytes;
+  int cap = g_max_ctas > 0 ? g_max_ctas : num_sms();
+  L->grid = p.num_tiles < cap ? p.num_tiles : cap;
+  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kPitch, kHaloH, is_bf16);
+  if (rc != ISR_OK) return rc;
+  return make_w_map(&L->tmW, wpacked, 2 * nrows, nrows, is_bf16);
+}
+
 static int run_conv(const ConvLaunch &L, cudaStream_t s) {
+  if (L.cp > 0) {
+    if (L.cp == 4) conv3x3_final_kernel<4><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else if (L.cp == 6) conv3x3_final_kernel<6><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else conv3x3_final_kernel<8><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    count_launch();
+    ISR_CUDA(cudaGetLastError());
+    return ISR_OK;
+  }
   const bool stack = L.p.n_w_parts == 2 && g_stack_w;
   if (L.n == 64 && stack)
     conv3x3_umma_kernel<64, EPI_STORE16, 1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
@@ -199,12 +256,13 @@ struct Layer {
   int cin = 0, cout = 0, npad = 0, G = 0;
   uint16_t *packed = nullptr;  // [fmt 2][part 2][tap 9][G][npad][64]
   float *bias = nullptr;       // npad floats, zero padded
+  uint16_t *packed_fin = nullptr;  // output conv only: tap-stacked [fmt 2][part 2][nrows][64]
   size_t per_fmt() const { return static_cast<size_t>(2) * 9 * G * npad * 64; }
   int rows() const { return 2 * 9 * G * npad; }
 };
 
 struct Plan {
-  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0;
+  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0, fin_stacked = 0, stack_w = 0;
   void *ws = nullptr;
   Scheme trunk, tail;
   int fin_nw = 0;
@@ -274,6 +332,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   if (reinterpret_cast<uintptr_t>(ws) % 1024 != 0) return fail(ISR_ERR_ARG, "workspace must be 1024-byte aligned");
   pl->B = B; pl->h = h; pl->w = w; pl->precision = precision; pl->ws = ws;
   pl->pitch = g_halo_pitch; pl->bo = g_base_offset_mode; pl->max_ctas = g_max_ctas;
+  pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w;
   uint8_t *base = static_cast<uint8_t *>(ws);
   auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
   const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
@@ -328,7 +387,13 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->idx_final = static_cast<int>(pl->convs.size());
   Scheme Fs = Hs;
   if (pl->fin_nw > 0) Fs.nw = pl->fin_nw;
-  if ((rc = conv_for_layer(&L, net->layers[24], 0, pl->u4, B, 4 * h, 4 * w, Fs)) != ISR_OK) return rc;
+  if (net->layers[24].packed_fin != nullptr && g_final_stacked) {
+    const int cp = final_cp(net->cout), nrows = final_rows(cp);
+    const uint16_t *wb = net->layers[24].packed_fin + (Fs.bf16 ? 0 : static_cast<size_t>(2) * nrows * 64);
+    if ((rc = init_conv_final(&L, cp, pl->u4, B, 4 * h, 4 * w, Fs.na, wb, Fs.nw, Fs.bf16)) != ISR_OK) return rc;
+  } else if ((rc = conv_for_layer(&L, net->layers[24], 0, pl->u4, B, 4 * h, 4 * w, Fs)) != ISR_OK) {
+    return rc;
+  }
   L.p.bias = net->layers[24].bias;
   L.p.cout = net->cout;
   L.p.n_mask = net->n_mask;
@@ -343,7 +408,8 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
 static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
   for (Plan *pl : net->plans)
     if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
-        pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas) {
+        pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
+        pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w) {
       *out = pl;
       return ISR_OK;
     }
@@ -424,6 +490,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "max_ctas") == 0) {
     if (value < 0) return fail(ISR_ERR_ARG, "max_ctas must be >= 0");
     slot = &g_max_ctas;
+  } else if (key != nullptr && strcmp(key, "final_stacked") == 0) {
+    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "final_stacked must be 0 or 1");
+    slot = &g_final_stacked;
   } else if (key != nullptr && strcmp(key, "stack_w") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "stack_w must be 0 or 1");
     slot = &g_stack_w;
@@ -520,6 +589,13 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
       return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
     }
   }
+  if (output_channels <= 8) {
+    const int nrows = final_rows(final_cp(output_channels));
+    if (cudaMalloc(&net->layers[24].packed_fin, static_cast<size_t>(4) * nrows * 64 * sizeof(uint16_t)) != cudaSuccess) {
+      isr_net_destroy(net);
+      return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
+    }
+  }
   *out = net;
   return ISR_OK;
 }
@@ -530,6 +606,7 @@ void isr_net_destroy(isr_net *net) {
   for (int i = 0; i < 25; ++i) {
     if (net->layers[i].packed) cudaFree(net->layers[i].packed);
     if (net->layers[i].bias) cudaFree(net->layers[i].bias);
+    if (net->layers[i].packed_fin) cudaFree(net->layers[i].packed_fin);
   }
   delete net;
 }
@@ -541,6 +618,9 @@ int isr_net_load_weights(isr_net *net, const float *const *params, int n_params,
     Layer &ly = net->layers[i];
     if (params[2 * i] == nullptr || params[2 * i + 1] == nullptr) return fail(ISR_ERR_ARG, "load_weights: null tensor");
     ISR_CUDA(launch_pack_weights(params[2 * i], ly.packed, ly.cout, ly.cin, ly.npad, ly.G, S(stream)));
+    if (ly.packed_fin != nullptr)
+      ISR_CUDA(launch_pack_weights_final(params[2 * i], ly.packed_fin, ly.cout, final_cp(ly.cout),
+                                         final_rows(final_cp(ly.cout)), S(stream)));
     ISR_CUDA(cudaMemsetAsync(ly.bias, 0, 64 * sizeof(float), S(stream)));
     ISR_CUDA(cudaMemcpyAsync(ly.bias, params[2 * i + 1], ly.cout * sizeof(float), cudaMemcpyDeviceToDevice, S(stream)));
   }

@@ -338,18 +338,25 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             lx0 = ly0 = 1.f;
             lx1 = ly1 = 0.f;
           }
+          // all taps of all channels are issued before the first use (no per-channel branch)
+          const int o00 = y0 * p.w_low + x0, o01 = y0 * p.w_low + x1, o10 = y1 * p.w_low + x0, o11 = y1 * p.w_low + x1;
+          const int nm = p.n_mask > 0 ? p.n_mask : 1;
+          float t00[kSkipPrefetch], t01[kSkipPrefetch], t10[kSkipPrefetch], t11[kSkipPrefetch];
 #pragma unroll
           for (int c = 0; c < kSkipPrefetch; ++c) {
-            if (c < p.n_mask) {
-              const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(c) * p.h_low * p.w_low;
-              if (p.upsample == 1) {
-                const float r0 = fmaf(lx0, __ldg(sp + y0 * p.w_low + x0), lx1 * __ldg(sp + y0 * p.w_low + x1));
-                const float r1 = fmaf(lx0, __ldg(sp + y1 * p.w_low + x0), lx1 * __ldg(sp + y1 * p.w_low + x1));
-                sk[c] = fmaf(ly0, r0, ly1 * r1);
-              } else {
-                sk[c] = __ldg(sp + y0 * p.w_low + x0);
-              }
-            }
+            const int cc = c < nm ? c : nm - 1;
+            const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(cc) * p.h_low * p.w_low;
+            t00[c] = __ldg(sp + o00);
+            t01[c] = __ldg(sp + o01);
+            t10[c] = __ldg(sp + o10);
+            t11[c] = __ldg(sp + o11);
+          }
+#pragma unroll
+          for (int c = 0; c < kSkipPrefetch; ++c) {
+            const float r0 = fmaf(lx0, t00[c], lx1 * t01[c]);
+            const float r1 = fmaf(lx0, t10[c], lx1 * t11[c]);
+            const float v = p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00[c];
+            sk[c] = c < p.n_mask ? v : 0.f;
           }
         }
         mbar_wait(b_tfull + 8 * acc, acc_ph);

@@ -1,0 +1,292 @@
+// isr_conv_final.cuh -- the network's output convolution (64 -> Cout <= 8, 3x3, pad 1) with its fused epilogue
+// (/root/reference/SuperresolutionNetwork/models/enhancenet.py:124 postblock[8], :51-90 _recon_image;
+//  mainVideoUnshaded.py:460-465 clamp / normalise), as a TAP-STACKED implicit GEMM.
+//
+// Why not the generic kernel: a tcgen05.mma with operands in shared memory costs ~54 cycles for every N <= 64
+// (profiles/r01_probe_mma_cycles.json), so 9 taps x 4 k-steps of N=16 MMAs cost as much as a 64-channel layer while using
+// 7.6 % of the tensor pipe.  Here the nine taps are stacked along N instead of being nine shifted A windows:
+//     P[halo pixel r, tap*CP + co] = sum_ci X[r, ci] * W[co, ci, tap]          (one un-shifted pass over the halo tile)
+//     out[p, co] = sum_tap P[p + shift(tap), tap*CP + co]                      (gather in the epilogue, via shared memory)
+// The 10x18 halo (180 pixel rows of 128 B, contiguous in shared memory) is covered by two M=128 row groups (rows 0..127
+// and 52..179): 2 x 4 = 8 MMAs per pass instead of 36.  CP = Cout padded to {4, 6, 8}; N = 9*CP rounded up to 16.
+//
+// Warp roles as in isr_conv.cuh: warps 0-3 / 4-7 = epilogue group 0 / 1 (group g drains accumulator buffer g and owns
+// gather buffer g), warp 8 = TMA producer, warp 9 = MMA issuer + TMEM owner.
+#pragma once
+#include "isr_conv.cuh"
+
+namespace isr {
+
+template <int CP>
+struct FinalCfg {
+  static constexpr int kCols = 9 * CP;                       // useful accumulator columns
+  static constexpr int kN = (kCols + 15) / 16 * 16;          // UMMA N
+  static constexpr int kLd = (kCols + 7) / 8 * 8;            // columns fetched from TMEM (x8 loads)
+  static constexpr int kPitch4 = ((kLd / 4) % 2 == 0) ? kLd / 4 + 1 : kLd / 4;   // odd number of 16 B units: conflict-free
+  static constexpr int kPPitch = kPitch4 * 4;                // floats per halo row in the gather buffer
+  static constexpr int kPBytes = ((kPitch * kHaloH * kPPitch * 4) + 1023) / 1024 * 1024;
+  static constexpr uint32_t kTmemCols = (4 * kN <= 256) ? 256 : 512;
+};
+
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t *v) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+template <int CP>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                     const ConvParams p) {
+  using C = FinalCfg<CP>;
+  constexpr int N = C::kN;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  constexpr uint32_t kWPartBytes = N * 128;                  // one weight part: N rows of 64 16-bit
+  const uint32_t w_bytes = p.n_w_parts * kWPartBytes;
+  const uint32_t s_w = smem_base;
+  const uint32_t s_p0 = s_w + ((w_bytes + 1023u) & ~1023u);  // two gather buffers
+  const uint32_t s_stage0 = s_p0 + 2 * C::kPBytes;
+  const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
+  const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
+                 b_tempty = s_bar + 152, s_tptr = s_bar + 168;
+  __shared__ float s_bias[8];
+  if (threadIdx.x < 8) s_bias[threadIdx.x] = (p.bias != nullptr && threadIdx.x < p.cout) ? p.bias[threadIdx.x] : 0.f;
+
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(b_full + 8 * s, 1);
+      mbar_init(b_empty + 8 * s, 1);
+    }
+    mbar_init(b_w, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(b_tfull + 8 * a, 1);
+      mbar_init(b_tempty + 8 * a, 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 9) tmem_alloc(s_tptr, C::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(s_tptr));
+
+  const int my_tiles = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                       static_cast<int>(gridDim.x);
+
+  if (warp == 8) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      mbar_arrive_expect_tx(b_w, w_bytes);
+      for (int wp = 0; wp < p.n_w_parts; ++wp)
+        tma_load_2d(s_w + wp * kWPartBytes, &tmW, b_w, 0, p.w_row0 + wp * p.w_row_stride);
+    }
+    __syncwarp();
+    uint32_t it = 0;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int t = blockIdx.x + i * gridDim.x;
+      const int tx = t % p.tiles_x;
+      const int ty = (t / p.tiles_x) % p.tiles_y;
+      const int b = t / (p.tiles_x * p.tiles_y);
+      for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+        const uint32_t s = it % p.num_stages;
+        const uint32_t ph = (it / p.num_stages) & 1;
+        mbar_wait(b_empty + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(b_full + 8 * s, kPitch * kHaloH * 128);
+          tma_load_4d(s_stage0 + s * p.stage_bytes, &tmA, b_full + 8 * s, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 9) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = make_idesc_f16(128, N, p.is_bf16);
+    const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
+    mbar_wait(b_w, 0);
+    uint32_t it = 0;
+    for (int i = 0; i < my_tiles; ++i) {
+      const uint32_t acc = i & 1;
+      const uint32_t acc_ph = (i >> 1) & 1;
+      mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * (2 * N);
+      uint32_t first = 1;
+      for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+        const uint32_t s = it % p.num_stages;
+        const uint32_t ph = (it / p.num_stages) & 1;
+        mbar_wait(b_full + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t a_base = s_stage0 + s * p.stage_bytes;
+        // halo rows are contiguous 128-byte rows: canonical K-major SW128 tiles, 8-row groups 1024 B apart
+        const uint64_t a_desc_g0 = make_smem_desc_sw128(a_base, 1024, 0);               // halo rows 0..127
+        const uint64_t a_desc_g1 = make_smem_desc_sw128(a_base + 52 * 128, 1024, 0);    // halo rows 52..179
+        const int nwp = (ap == 0) ? p.n_w_parts : 1;  // (hi,hi) (hi,lo) | (lo,hi)
+        if (elect_one()) {
+          for (int wp = 0; wp < nwp; ++wp) {
+            const uint64_t bdesc = b_desc_base + static_cast<uint64_t>((wp * kWPartBytes) >> 4);
+            umma_f16_k64(d_tmem, a_desc_g0, bdesc, idesc, first ? 0u : 1u);
+            umma_f16_k64(d_tmem + N, a_desc_g1, bdesc, idesc, first ? 0u : 1u);
+            first = 0;
+          }
+          umma_commit(b_empty + 8 * s);
+          if (ap == p.n_act_parts - 1) umma_commit(b_tfull + 8 * acc);
+        }
+        __syncwarp();
+        first = 0;
+      }
+    }
+  } else {
+    // ===================== epilogue warps 0..7 =====================
+    const int grp = warp >> 2, q = warp & 3;
+    const uint32_t s_p = s_p0 + grp * C::kPBytes;
+    float *P = reinterpret_cast<float *>(smem_raw + (s_p - smem_u32(smem_raw)));
+    for (int i = grp; i < my_tiles; i += 2) {
+      const int t = blockIdx.x + i * gridDim.x;
+      const int tx = t % p.tiles_x;
+      const int ty = (t / p.tiles_x) % p.tiles_y;
+      const int b = t / (p.tiles_x * p.tiles_y);
+      const uint32_t acc = grp;
+      const uint32_t acc_ph = (i >> 1) & 1;
+      const uint32_t taddr = tmem_base + acc * (2 * N) + (static_cast<uint32_t>(q * 32) << 16);
+      const int row = q * 32 + lane;   // output pixel of this thread inside the tile
+      const int py = row >> 3, px = row & 7;
+      const int y = ty * kTileH + py, x = tx * kTileW + px;
+      const bool inb = (y < p.H) && (x < p.W);
+      // skip taps do not depend on the accumulator: fetch them before waiting for the MMAs
+      float sk[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) sk[c] = 0.f;
+      if (inb && p.recon_residual) {
+        int x0, x1, y0, y1;
+        float lx0, lx1, ly0, ly1;
+        if (p.upsample == 1) {
+          bil_src(x, p.w_low, 0.25f, x0, x1, lx0, lx1);
+          bil_src(y, p.h_low, 0.25f, y0, y1, ly0, ly1);
+        } else {
+          x0 = x1 = x >> 2;
+          y0 = y1 = y >> 2;
+          lx0 = ly0 = 1.f;
+          lx1 = ly1 = 0.f;
+        }
+        // all taps of all channels are issued before the first use (a per-channel branch serialises the round trips:
+        // 40 % of this kernel's stall samples were long-scoreboard waits on exactly these loads)
+        const int o00 = y0 * p.w_low + x0, o01 = y0 * p.w_low + x1, o10 = y1 * p.w_low + x0, o11 = y1 * p.w_low + x1;
+        const int nm = p.n_mask > 0 ? p.n_mask : 1;
+        float t00[CP], t01[CP], t10[CP], t11[CP];
+#pragma unroll
+        for (int c = 0; c < CP; ++c) {
+          const int cc = c < nm ? c : nm - 1;
+          const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(cc) * p.h_low * p.w_low;
+          t00[c] = __ldg(sp + o00);
+          t01[c] = __ldg(sp + o01);
+          t10[c] = __ldg(sp + o10);
+          t11[c] = __ldg(sp + o11);
+        }
+#pragma unroll
+        for (int c = 0; c < CP; ++c) {
+          const float r0 = fmaf(lx0, t00[c], lx1 * t01[c]);
+          const float r1 = fmaf(lx0, t10[c], lx1 * t11[c]);
+          const float v = p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00[c];
+          sk[c] = c < p.n_mask ? v : 0.f;
+        }
+      }
+      mbar_wait(b_tfull + 8 * acc, acc_ph);
+      tc_fence_after();
+      // ---- phase A: per-tap partial sums TMEM -> registers -> gather buffer (row = halo pixel) ----
+      {
+        uint32_t v[C::kLd];
+#pragma unroll
+        for (int c8 = 0; c8 < C::kLd / 8; ++c8) tmem_ld8(taddr + 8 * c8, v + 8 * c8);
+        tmem_ld_wait();
+        float4 *dst = reinterpret_cast<float4 *>(P + static_cast<size_t>(row) * C::kPPitch);
+#pragma unroll
+        for (int c4 = 0; c4 < C::kLd / 4; ++c4)
+          dst[c4] = make_float4(__uint_as_float(v[4 * c4]), __uint_as_float(v[4 * c4 + 1]),
+                                __uint_as_float(v[4 * c4 + 2]), __uint_as_float(v[4 * c4 + 3]));
+        if (q >= 2) {   // second row group: accumulator lane L holds halo row 52 + L; rows 128..179 are new
+#pragma unroll
+          for (int c8 = 0; c8 < C::kLd / 8; ++c8) tmem_ld8(taddr + N + 8 * c8, v + 8 * c8);
+          tmem_ld_wait();
+          const int hr = 52 + row;
+          if (hr >= 128) {
+            float4 *d2 = reinterpret_cast<float4 *>(P + static_cast<size_t>(hr) * C::kPPitch);
+#pragma unroll
+            for (int c4 = 0; c4 < C::kLd / 4; ++c4)
+              d2[c4] = make_float4(__uint_as_float(v[4 * c4]), __uint_as_float(v[4 * c4 + 1]),
+                                   __uint_as_float(v[4 * c4 + 2]), __uint_as_float(v[4 * c4 + 3]));
+          }
+        }
+      }
+      // the accumulator buffer is free as soon as it is in shared memory
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(b_tempty + 8 * acc);
+      named_bar_sync(1 + grp, 128);
+      // ---- phase B: out[p, co] = sum over taps of P[p + shift(tap)][tap*CP + co] ----
+      float rec[CP];
+#pragma unroll
+      for (int c = 0; c < CP; ++c) rec[c] = s_bias[c];
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        const float *src = P + static_cast<size_t>((py + tap / 3) * kPitch + px + tap % 3) * C::kPPitch + tap * CP;
+#pragma unroll
+        for (int c2 = 0; c2 < CP / 2; ++c2) {
+          const float2 f = *reinterpret_cast<const float2 *>(src + 2 * c2);
+          rec[2 * c2] += f.x;
+          rec[2 * c2 + 1] += f.y;
+        }
+      }
+      if (inb) {
+        const size_t plane = static_cast<size_t>(p.H) * p.W;
+        const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;
+#pragma unroll
+        for (int c = 0; c < CP; ++c) {
+          if (c < p.cout) {
+            const float raw = rec[c];
+            if (p.out_raw != nullptr) p.out_raw[o0 + c * plane] = raw;
+            if (p.recon_residual && c < p.n_mask) rec[c] = sk[c] + raw;
+            if (p.out_recon != nullptr) p.out_recon[o0 + c * plane] = rec[c];
+          }
+        }
+        if (p.out_state != nullptr) {
+          if (p.state_unshaded && p.cout >= 5) {
+            if constexpr (CP >= 6) {
+              // mainVideoUnshaded.py:460-465: clamp mask, normalise normal (shading.py:193-207), clamp depth / ao
+              p.out_state[o0] = fminf(fmaxf(rec[0], -1.f), 1.f);
+              float len = sqrtf(rec[1] * rec[1] + rec[2] * rec[2] + rec[3] * rec[3]);
+              len = fmaxf(len, 1e-7f);
+              p.out_state[o0 + plane] = rec[1] / len;
+              p.out_state[o0 + 2 * plane] = rec[2] / len;
+              p.out_state[o0 + 3 * plane] = rec[3] / len;
+#pragma unroll
+              for (int c = 4; c < CP; ++c)
+                if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < CP; ++c)
+              if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+          }
+        }
+      }
+      named_bar_sync(1 + grp, 128);   // gather buffer free for this group's next tile
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) tmem_dealloc(tmem_base, C::kTmemCols);
+}
+
+}  // namespace isr

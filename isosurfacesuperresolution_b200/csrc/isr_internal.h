@@ -26,5 +26,7 @@ cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, i
                               int in_bf16, int out_bf16, int bilinear, cudaStream_t s);
 // out layout: [fmt 2 (bf16, fp16)][part 2 (hi, lo)][tap 9][group G][npad][64]
 cudaError_t launch_pack_weights(const float *w, uint16_t *out, int cout, int cin, int npad, int G, cudaStream_t s);
+// tap-stacked output-conv weights: [fmt 2][part 2][nrows (n = tap*cp + co)][64]
+cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s);
 
 }  // namespace isr

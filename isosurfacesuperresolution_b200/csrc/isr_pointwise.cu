@@ -539,6 +539,26 @@ __global__ void pack_weights_kernel(const float *__restrict__ w, uint16_t *__res
   }
 }
 
+// tap-stacked weights of the output conv (isr_conv_final.cuh): fp32 OIHW [cout][64][3][3] ->
+// [fmt 2][part 2][n = tap*cp + co, padded to nrows][64] 16-bit
+__global__ void pack_weights_final_kernel(const float *__restrict__ w, uint16_t *__restrict__ out, int cout, int cp,
+                                          int nrows) {
+  const int per_part = nrows * 64;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < per_part; i += gridDim.x * blockDim.x) {
+    const int k = i & 63, n = i >> 6;
+    const int tap = n / cp, co = n % cp;
+    const float v = (tap < 9 && co < cout) ? w[(static_cast<size_t>(co) * 64 + k) * 9 + tap] : 0.f;
+    const __nv_bfloat16 bh = __float2bfloat16_rn(v);
+    const __nv_bfloat16 bl = __float2bfloat16_rn(v - __bfloat162float(bh));
+    const __half hh = __float2half_rn(v);
+    const __half hl = __float2half_rn(v - __half2float(hh));
+    out[i] = *reinterpret_cast<const uint16_t *>(&bh);
+    out[per_part + i] = *reinterpret_cast<const uint16_t *>(&bl);
+    out[2 * per_part + i] = *reinterpret_cast<const uint16_t *>(&hh);
+    out[3 * per_part + i] = *reinterpret_cast<const uint16_t *>(&hl);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // host launchers
 static inline int grid_for(size_t total, int block) {
@@ -631,6 +651,11 @@ cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, i
     ISR_UP_CASE(12, 2, 1, 1, 0) ISR_UP_CASE(13, 2, 1, 1, 1) ISR_UP_CASE(14, 2, 1, 2, 0) ISR_UP_CASE(15, 2, 1, 2, 1)
 #undef ISR_UP_CASE
   }
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s) {
+  pack_weights_final_kernel<<<(nrows * 64 + 255) / 256, 256, 0, s>>>(w, out, cout, cp, nrows);
   count_launch();
   return cudaGetLastError();
 }
