@@ -15,6 +15,7 @@
 #include "../../include/isr.h"
 #include "isr_conv.cuh"
 #include "isr_conv_final.cuh"
+#include "isr_conv_pair.cuh"
 #include "isr_internal.h"
 
 namespace isr {
@@ -24,6 +25,7 @@ static std::atomic<uint64_t> g_launches{0};
 static int g_halo_pitch = 10;
 static int g_base_offset_mode = 0;
 static int g_max_ctas = 0;
+static int g_cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta_group::2, isr_conv_pair.cuh)
 static int g_final_stacked = 1;   // output conv: tap-stacked kernel (isr_conv_final.cuh) when Cout <= 8
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
 
@@ -100,6 +102,7 @@ struct ConvLaunch {
   ConvParams p;
   int n;  // 64 (EPI_STORE16) or 16 (EPI_FINAL)
   int cp = 0;  // > 0: tap-stacked output conv (conv3x3_final_kernel<cp>)
+  int pair = 0;  // 1: CTA-pair kernel (conv3x3_pair_kernel)
   size_t smem;
   int grid;
 };
@@ -128,6 +131,10 @@ static int setup_kernel_attrs() {
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -153,7 +160,11 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   p.is_bf16 = is_bf16;
   p.w_row0 = w_row0;
   p.w_row_stride = w_row_stride;
-  const size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * 9 * n * 128, 1024);
+  L->pair = (n == 64 && g_cta_pair) ? 1 : 0;
+  const bool stack = n_w_parts == 2 && g_stack_w;
+  // weight bytes per CTA: the pair kernel keeps half of the B operand per CTA (+ its half of W_hi when stacked)
+  size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * 9 * n * 128, 1024);
+  if (L->pair) w_bytes = align_up(static_cast<size_t>(stack ? 3 : n_w_parts) * 9 * (n / 2) * 128, 1024);
   p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kPitch) * kHaloH * 128, 1024));
   const size_t avail = kSmemLimit - kStaticSmem - 1024 - w_bytes - 256;
   int stages = static_cast<int>(avail / p.stage_bytes);
@@ -163,9 +174,15 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   L->smem = 1024 + w_bytes + static_cast<size_t>(stages) * p.stage_bytes + 256;
   int cap = g_max_ctas > 0 ? g_max_ctas : num_sms();
   L->grid = p.num_tiles < cap ? p.num_tiles : cap;
+  if (L->pair) {
+    const int want = 2 * ((p.num_tiles + 1) / 2);
+    cap &= ~1;
+    if (cap < 2) cap = 2;
+    L->grid = want < cap ? want : cap;
+  }
   int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kPitch, kHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
-  return make_w_map(&L->tmW, wpacked, w_rows_total, n, is_bf16);
+  return make_w_map(&L->tmW, wpacked, w_rows_total, L->pair ? n / 2 : n, is_bf16);
 }
 
 static int final_cp(int cout) { return cout <= 4 ? 4 : (cout <= 6 ? 6 : 8); }
@@ -195,7 +212,7 @@ static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H,
   p.w_row_stride = nrows;
   const size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * nrows * 128, 1024);
   p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kPitch) * kHaloH * 128, 1024));
-  const size_t fixed = 1024 + w_bytes + 2 * final_pbytes(cp) + 256;
+  const size_t fixed = 1024 + w_bytes + kFinalGroups * final_pbytes(cp) + 256;
   int stages = static_cast<int>((kSmemLimit - kStaticSmem - fixed) / p.stage_bytes);
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "final conv smem plan: fewer than 2 halo stages fit");
@@ -210,15 +227,19 @@ static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H,
 
 static int run_conv(const ConvLaunch &L, cudaStream_t s) {
   if (L.cp > 0) {
-    if (L.cp == 4) conv3x3_final_kernel<4><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else if (L.cp == 6) conv3x3_final_kernel<6><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else conv3x3_final_kernel<8><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    if (L.cp == 4) conv3x3_final_kernel<4><<<L.grid, kFinalThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else if (L.cp == 6) conv3x3_final_kernel<6><<<L.grid, kFinalThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else conv3x3_final_kernel<8><<<L.grid, kFinalThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
     count_launch();
     ISR_CUDA(cudaGetLastError());
     return ISR_OK;
   }
   const bool stack = L.p.n_w_parts == 2 && g_stack_w;
-  if (L.n == 64 && stack)
+  if (L.pair && stack)
+    conv3x3_pair_kernel<1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+  else if (L.pair)
+    conv3x3_pair_kernel<0><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+  else if (L.n == 64 && stack)
     conv3x3_umma_kernel<64, EPI_STORE16, 1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   else if (L.n == 64)
     conv3x3_umma_kernel<64, EPI_STORE16, 0><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
@@ -262,7 +283,7 @@ struct Layer {
 };
 
 struct Plan {
-  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0, fin_stacked = 0, stack_w = 0;
+  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0, fin_stacked = 0, stack_w = 0, cta_pair = 0;
   void *ws = nullptr;
   Scheme trunk, tail;
   int fin_nw = 0;
@@ -332,7 +353,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   if (reinterpret_cast<uintptr_t>(ws) % 1024 != 0) return fail(ISR_ERR_ARG, "workspace must be 1024-byte aligned");
   pl->B = B; pl->h = h; pl->w = w; pl->precision = precision; pl->ws = ws;
   pl->pitch = g_halo_pitch; pl->bo = g_base_offset_mode; pl->max_ctas = g_max_ctas;
-  pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w;
+  pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w; pl->cta_pair = g_cta_pair;
   uint8_t *base = static_cast<uint8_t *>(ws);
   auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
   const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
@@ -409,7 +430,7 @@ static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision
   for (Plan *pl : net->plans)
     if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
         pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
-        pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w) {
+        pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair) {
       *out = pl;
       return ISR_OK;
     }
@@ -490,6 +511,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "max_ctas") == 0) {
     if (value < 0) return fail(ISR_ERR_ARG, "max_ctas must be >= 0");
     slot = &g_max_ctas;
+  } else if (key != nullptr && strcmp(key, "cta_pair") == 0) {
+    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "cta_pair must be 0 or 1");
+    slot = &g_cta_pair;
   } else if (key != nullptr && strcmp(key, "final_stacked") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "final_stacked must be 0 or 1");
     slot = &g_final_stacked;

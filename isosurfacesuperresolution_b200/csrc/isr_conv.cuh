@@ -83,6 +83,109 @@ __device__ __forceinline__ void bil_src(int dst, int n_in, float inv_scale, int 
   l0 = 1.f - t;
 }
 
+// Epilogue of a 64-wide layer for one 8x16 tile (one warp = TMEM lanes 32q..32q+31): waits for the accumulator, then
+// bias (+ residual addend) (+ ReLU) -> 16-bit NHWC hi (and lo) planes.  Shared by the single-CTA and the CTA-pair kernel.
+// thread (m = lane%4, rr = lane/4): pixel column rr of image rows 4q..4q+3 of the tile, channels 16m..16m+15
+template <int N, int STACK>
+__device__ __forceinline__ void epilogue_store16(const ConvParams &p, const float *s_bias, uint32_t taddr, int q, int lane,
+                                                 int b, int ty, int tx, bool tile_valid, uint32_t bar_tfull,
+                                                 uint32_t acc_ph) {
+  const uint32_t b_tfull = bar_tfull;
+  constexpr uint32_t acc = 0;   // bar_tfull already addresses this tile's accumulator barrier
+    // thread (m = lane%4, rr = lane/4): pixel column rr of image rows 4q..4q+3 of the tile, channels 16m..16m+15
+    const int m = lane & 3, rr = lane >> 2;
+    const int x = tx * kTileW + rr;
+    float bias_r[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) bias_r[j] = s_bias[16 * m + j];
+    // residual addend (the block's skip): fetched BEFORE waiting for the accumulator, so its HBM latency hides
+    // behind the tile's MMAs.  ad[pixel j = 2*half+hh][part][2 x 16 B]
+    uint4 ad[4][2][2];
+    const bool has_add = p.addend != nullptr;
+    if (has_add) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int y = ty * kTileH + 4 * q + j;
+        const bool ok = tile_valid && (y < p.H) && (x < p.W);
+        const size_t pix = (static_cast<size_t>(b) * p.H + (ok ? y : 0)) * p.W + (ok ? x : 0);
+#pragma unroll
+        for (int ap = 0; ap < 2; ++ap) {
+          if (ap < p.add_parts) {
+            const uint4 *src =
+                reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m);
+            ad[j][ap][0] = __ldg(src);
+            ad[j][ap][1] = __ldg(src + 1);
+          }
+        }
+      }
+    }
+    mbar_wait(b_tfull + 8 * acc, acc_ph);
+    tc_fence_after();
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint32_t v[32];
+      tmem_ld_16x256b_x8(taddr + (static_cast<uint32_t>(half * 16) << 16), v);
+      if constexpr (STACK) {
+        uint32_t v2[32];
+        tmem_ld_16x256b_x8(taddr + N + (static_cast<uint32_t>(half * 16) << 16), v2);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
+      } else {
+        tmem_ld_wait();
+      }
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const int y = ty * kTileH + 4 * q + 2 * half + hh;
+        if (tile_valid && y < p.H && x < p.W) {
+          const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
+          float f[16];
+#pragma unroll
+          for (int rep = 0; rep < 8; ++rep) {
+            f[2 * rep] = __uint_as_float(v[4 * rep + 2 * hh]) + bias_r[2 * rep];
+            f[2 * rep + 1] = __uint_as_float(v[4 * rep + 2 * hh + 1]) + bias_r[2 * rep + 1];
+          }
+          if (has_add) {
+#pragma unroll
+            for (int ap = 0; ap < 2; ++ap) {
+              if (ap < p.add_parts) {
+                const uint4 q0 = ad[2 * half + hh][ap][0], q1 = ad[2 * half + hh][ap][1];
+                const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float2 a = unpack2(w[j], p.is_bf16);
+                  f[2 * j] += a.x;
+                  f[2 * j + 1] += a.y;
+                }
+              }
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          uint32_t hi[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
+          uint4 *dst = reinterpret_cast<uint4 *>(p.out16 + pix * (64 * p.out_parts) + 16 * m);
+          dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+          if (p.out_parts == 2) {
+            uint32_t lo[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float2 h = unpack2(hi[j], p.is_bf16);
+              lo[j] = pack2(f[2 * j] - h.x, f[2 * j + 1] - h.y, p.is_bf16);
+            }
+            uint4 *dl = reinterpret_cast<uint4 *>(p.out16 + pix * 128 + 64 + 16 * m);
+            dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+          }
+        }
+      }
+    }
+}
+
 // STACK = 1 (split precision, N = 64 only): the hi and lo weight planes of a tap sit back to back in shared memory and
 // are ONE N=128 B operand, so A_hi*W_hi^T and A_hi*W_lo^T are a single M128xN128 MMA (67.7 cycles measured) instead of two
 // N=64 MMAs (2 x 53.9, profiles/r01_probe_mma_cycles.json); the epilogue adds accumulator columns c and 64+c.
@@ -223,98 +326,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t acc_ph = (i >> 1) & 1;
       const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
       if constexpr (EPI == EPI_STORE16) {
-        // thread (m = lane%4, rr = lane/4): pixel column rr of image rows 4q..4q+3 of the tile, channels 16m..16m+15
-        const int m = lane & 3, rr = lane >> 2;
-        const int x = tx * kTileW + rr;
-        float bias_r[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) bias_r[j] = s_bias[16 * m + j];
-        // residual addend (the block's skip): fetched BEFORE waiting for the accumulator, so its HBM latency hides
-        // behind the tile's MMAs.  ad[pixel j = 2*half+hh][part][2 x 16 B]
-        uint4 ad[4][2][2];
-        const bool has_add = p.addend != nullptr;
-        if (has_add) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int y = ty * kTileH + 4 * q + j;
-            const bool ok = (y < p.H) && (x < p.W);
-            const size_t pix = (static_cast<size_t>(b) * p.H + (ok ? y : 0)) * p.W + (ok ? x : 0);
-#pragma unroll
-            for (int ap = 0; ap < 2; ++ap) {
-              if (ap < p.add_parts) {
-                const uint4 *src =
-                    reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m);
-                ad[j][ap][0] = __ldg(src);
-                ad[j][ap][1] = __ldg(src + 1);
-              }
-            }
-          }
-        }
-        mbar_wait(b_tfull + 8 * acc, acc_ph);
-        tc_fence_after();
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          uint32_t v[32];
-          tmem_ld_16x256b_x8(taddr + (static_cast<uint32_t>(half * 16) << 16), v);
-          if constexpr (STACK) {
-            uint32_t v2[32];
-            tmem_ld_16x256b_x8(taddr + N + (static_cast<uint32_t>(half * 16) << 16), v2);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
-          } else {
-            tmem_ld_wait();
-          }
-#pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            const int y = ty * kTileH + 4 * q + 2 * half + hh;
-            if (y < p.H && x < p.W) {
-              const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
-              float f[16];
-#pragma unroll
-              for (int rep = 0; rep < 8; ++rep) {
-                f[2 * rep] = __uint_as_float(v[4 * rep + 2 * hh]) + bias_r[2 * rep];
-                f[2 * rep + 1] = __uint_as_float(v[4 * rep + 2 * hh + 1]) + bias_r[2 * rep + 1];
-              }
-              if (has_add) {
-#pragma unroll
-                for (int ap = 0; ap < 2; ++ap) {
-                  if (ap < p.add_parts) {
-                    const uint4 q0 = ad[2 * half + hh][ap][0], q1 = ad[2 * half + hh][ap][1];
-                    const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                      const float2 a = unpack2(w[j], p.is_bf16);
-                      f[2 * j] += a.x;
-                      f[2 * j + 1] += a.y;
-                    }
-                  }
-                }
-              }
-              if (p.relu) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) f[j] = fmaxf(f[j], 0.f);
-              }
-              uint32_t hi[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
-              uint4 *dst = reinterpret_cast<uint4 *>(p.out16 + pix * (64 * p.out_parts) + 16 * m);
-              dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-              dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-              if (p.out_parts == 2) {
-                uint32_t lo[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                  const float2 h = unpack2(hi[j], p.is_bf16);
-                  lo[j] = pack2(f[2 * j] - h.x, f[2 * j + 1] - h.y, p.is_bf16);
-                }
-                uint4 *dl = reinterpret_cast<uint4 *>(p.out16 + pix * 128 + 64 + 16 * m);
-                dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
-              }
-            }
-          }
-        }
+        epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, true, b_tfull + 8 * acc, acc_ph);
       } else {
         // final conv: raw = acc + bias; recon = raw + upsampled skip (enhancenet.py:51-90); optional recurrent state.
         // thread = GEMM row (32x32b load): pixel (py, px) = (row/8, row%8); NCHW fp32 planes, 8 px = one 32 B sector.

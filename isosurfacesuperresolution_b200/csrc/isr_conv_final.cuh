@@ -10,12 +10,15 @@
 // The 10x18 halo (180 pixel rows of 128 B, contiguous in shared memory) is covered by two M=128 row groups (rows 0..127
 // and 52..179): 2 x 4 = 8 MMAs per pass instead of 36.  CP = Cout padded to {4, 6, 8}; N = 9*CP rounded up to 16.
 //
-// Warp roles as in isr_conv.cuh: warps 0-3 / 4-7 = epilogue group 0 / 1 (group g drains accumulator buffer g and owns
-// gather buffer g), warp 8 = TMA producer, warp 9 = MMA issuer + TMEM owner.
+// Warp roles as in isr_conv.cuh: warps 0-3 / 4-7 = epilogue group 0 / 1 (kFinalGroups groups; group g drains accumulator
+// buffer g and owns gather buffer g), then the TMA producer warp and the MMA issuer warp (TMEM owner).
 #pragma once
 #include "isr_conv.cuh"
 
 namespace isr {
+
+constexpr int kFinalGroups = 3;                                   // epilogue groups of four warps
+constexpr int kFinalThreads = (4 * kFinalGroups + 2) * 32;        // + TMA producer warp + MMA issuer warp
 
 template <int CP>
 struct FinalCfg {
@@ -25,7 +28,7 @@ struct FinalCfg {
   static constexpr int kPitch4 = ((kLd / 4) % 2 == 0) ? kLd / 4 + 1 : kLd / 4;   // odd number of 16 B units: conflict-free
   static constexpr int kPPitch = kPitch4 * 4;                // floats per halo row in the gather buffer
   static constexpr int kPBytes = ((kPitch * kHaloH * kPPitch * 4) + 1023) / 1024 * 1024;
-  static constexpr uint32_t kTmemCols = (4 * kN <= 256) ? 256 : 512;
+  static constexpr uint32_t kTmemCols = (2 * kFinalGroups * kN <= 256) ? 256 : 512;   // one accumulator pair per group
 };
 
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t *v) {
@@ -39,7 +42,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 template <int CP>
-__global__ void __launch_bounds__(kConvThreads, 1)
+__global__ void __launch_bounds__(kFinalThreads, 1)
 conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                      const ConvParams p) {
   using C = FinalCfg<CP>;
@@ -53,14 +56,19 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const uint32_t w_bytes = p.n_w_parts * kWPartBytes;
   const uint32_t s_w = smem_base;
   const uint32_t s_p0 = s_w + ((w_bytes + 1023u) & ~1023u);  // two gather buffers
-  const uint32_t s_stage0 = s_p0 + 2 * C::kPBytes;
+  const uint32_t s_stage0 = s_p0 + kFinalGroups * C::kPBytes;
   const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
+  // barrier block: full[8], empty[8], wbar, tmem_full[G], tmem_empty[G], tmem_ptr.  One accumulator buffer PER GROUP: a
+  // group must observe every phase of the barriers it waits on (parity waits alias after two phases), so buffers are
+  // not shared between groups.
   const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
-                 b_tempty = s_bar + 152, s_tptr = s_bar + 168;
+                 b_tempty = b_tfull + 8 * kFinalGroups, s_tptr = b_tempty + 8 * kFinalGroups;
+  static_assert(136 + 16 * kFinalGroups + 4 <= 256, "barrier block overflows its 256-byte reservation");
   __shared__ float s_bias[8];
   if (threadIdx.x < 8) s_bias[threadIdx.x] = (p.bias != nullptr && threadIdx.x < p.cout) ? p.bias[threadIdx.x] : 0.f;
 
-  if (warp == 8 && lane == 0) {
+  constexpr int kTmaWarp = 4 * kFinalGroups, kMmaWarp = 4 * kFinalGroups + 1;
+  if (warp == kTmaWarp && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmW);
     for (int s = 0; s < p.num_stages; ++s) {
@@ -68,13 +76,13 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       mbar_init(b_empty + 8 * s, 1);
     }
     mbar_init(b_w, 1);
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < kFinalGroups; ++a) {
       mbar_init(b_tfull + 8 * a, 1);
       mbar_init(b_tempty + 8 * a, 4);
     }
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc(s_tptr, C::kTmemCols);
+  if (warp == kMmaWarp) tmem_alloc(s_tptr, C::kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -84,7 +92,7 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const int my_tiles = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                        static_cast<int>(gridDim.x);
 
-  if (warp == 8) {
+  if (warp == kTmaWarp) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       mbar_arrive_expect_tx(b_w, w_bytes);
@@ -109,15 +117,15 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         __syncwarp();
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == kMmaWarp) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = make_idesc_f16(128, N, p.is_bf16);
     const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
     mbar_wait(b_w, 0);
     uint32_t it = 0;
     for (int i = 0; i < my_tiles; ++i) {
-      const uint32_t acc = i & 1;
-      const uint32_t acc_ph = (i >> 1) & 1;
+      const uint32_t acc = i % kFinalGroups;
+      const uint32_t acc_ph = (i / kFinalGroups) & 1;
       mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * (2 * N);
@@ -147,43 +155,39 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       }
     }
   } else {
-    // ===================== epilogue warps 0..7 =====================
+    // ===================== epilogue warps: group g handles tiles g, g+G, ... (accumulator buffer = tile & 1) ======
     const int grp = warp >> 2, q = warp & 3;
     const uint32_t s_p = s_p0 + grp * C::kPBytes;
     float *P = reinterpret_cast<float *>(smem_raw + (s_p - smem_u32(smem_raw)));
-    for (int i = grp; i < my_tiles; i += 2) {
+    for (int i = grp; i < my_tiles; i += kFinalGroups) {
       const int t = blockIdx.x + i * gridDim.x;
       const int tx = t % p.tiles_x;
       const int ty = (t / p.tiles_x) % p.tiles_y;
       const int b = t / (p.tiles_x * p.tiles_y);
       const uint32_t acc = grp;
-      const uint32_t acc_ph = (i >> 1) & 1;
+      const uint32_t acc_ph = (i / kFinalGroups) & 1;
       const uint32_t taddr = tmem_base + acc * (2 * N) + (static_cast<uint32_t>(q * 32) << 16);
       const int row = q * 32 + lane;   // output pixel of this thread inside the tile
       const int py = row >> 3, px = row & 7;
       const int y = ty * kTileH + py, x = tx * kTileW + px;
       const bool inb = (y < p.H) && (x < p.W);
       // skip taps do not depend on the accumulator: fetch them before waiting for the MMAs
-      float sk[8];
+      // only the LOADS are issued here; the interpolation happens after the gather, so their latency hides behind it
+      float lx0 = 1.f, lx1 = 0.f, ly0 = 1.f, ly1 = 0.f;
+      float t00[CP], t01[CP], t10[CP], t11[CP];
 #pragma unroll
-      for (int c = 0; c < 8; ++c) sk[c] = 0.f;
+      for (int c = 0; c < CP; ++c) t00[c] = t01[c] = t10[c] = t11[c] = 0.f;
       if (inb && p.recon_residual) {
         int x0, x1, y0, y1;
-        float lx0, lx1, ly0, ly1;
         if (p.upsample == 1) {
           bil_src(x, p.w_low, 0.25f, x0, x1, lx0, lx1);
           bil_src(y, p.h_low, 0.25f, y0, y1, ly0, ly1);
         } else {
           x0 = x1 = x >> 2;
           y0 = y1 = y >> 2;
-          lx0 = ly0 = 1.f;
-          lx1 = ly1 = 0.f;
         }
-        // all taps of all channels are issued before the first use (a per-channel branch serialises the round trips:
-        // 40 % of this kernel's stall samples were long-scoreboard waits on exactly these loads)
         const int o00 = y0 * p.w_low + x0, o01 = y0 * p.w_low + x1, o10 = y1 * p.w_low + x0, o11 = y1 * p.w_low + x1;
         const int nm = p.n_mask > 0 ? p.n_mask : 1;
-        float t00[CP], t01[CP], t10[CP], t11[CP];
 #pragma unroll
         for (int c = 0; c < CP; ++c) {
           const int cc = c < nm ? c : nm - 1;
@@ -192,13 +196,6 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           t01[c] = __ldg(sp + o01);
           t10[c] = __ldg(sp + o10);
           t11[c] = __ldg(sp + o11);
-        }
-#pragma unroll
-        for (int c = 0; c < CP; ++c) {
-          const float r0 = fmaf(lx0, t00[c], lx1 * t01[c]);
-          const float r1 = fmaf(lx0, t10[c], lx1 * t11[c]);
-          const float v = p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00[c];
-          sk[c] = c < p.n_mask ? v : 0.f;
         }
       }
       mbar_wait(b_tfull + 8 * acc, acc_ph);
@@ -255,7 +252,12 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           if (c < p.cout) {
             const float raw = rec[c];
             if (p.out_raw != nullptr) p.out_raw[o0 + c * plane] = raw;
-            if (p.recon_residual && c < p.n_mask) rec[c] = sk[c] + raw;
+            if (p.recon_residual && c < p.n_mask) {
+              // _recon_image (enhancenet.py:67-71): bilinear (x first, then y) or nearest 4x skip + raw
+              const float r0 = fmaf(lx0, t00[c], lx1 * t01[c]);
+              const float r1 = fmaf(lx0, t10[c], lx1 * t11[c]);
+              rec[c] = (p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00[c]) + raw;
+            }
             if (p.out_recon != nullptr) p.out_recon[o0 + c * plane] = rec[c];
           }
         }
@@ -286,7 +288,7 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem_base, C::kTmemCols);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, C::kTmemCols);
 }
 
 }  // namespace isr

@@ -1,0 +1,260 @@
+// isr_conv_pair.cuh -- the 64-wide conv3x3 layers as a CTA-PAIR implicit GEMM (tcgen05.mma.cta_group::2, M = 256).
+//
+// Why: a tcgen05.mma with both operands in shared memory costs ~54 cycles per instruction for every N <= 64 when issued
+// for one CTA (M = 128), but 43 cycles for a CTA pair (M = 256): 21.5 cycles per 128-pixel tile instead of 54, and 64
+// instead of 2 x 67.7 at N = 128 (profiles/r01_probe_mma_cycles.json, r01_probe_mma2.json).  The pair also halves the
+// weight footprint: each CTA keeps only its half of the B operand (N/2 rows per tap).
+//
+// Structure (both CTAs run the same code; rank 0 = leader):
+//   * each CTA owns one 8x16 tile per iteration (tiles 2j and 2j+1), loads ITS halo into ITS shared memory, and drains
+//     ITS half of the accumulator (TMEM lanes 0..127 of its own SM) with the same epilogue as the single-CTA kernel;
+//   * only the leader's MMA warp issues instructions; descriptors are shared-memory OFFSETS valid in both CTAs, so the
+//     two CTAs use identical layouts and advance their halo stages in lock step;
+//   * barriers: full[s] and the weight barrier live in the LEADER (2 arrivals + both CTAs' TMA bytes, the peer's TMA
+//     signals it through .cta_group::2); empty[s] and tmem_full[a] are per CTA and are arrived by a multicast
+//     tcgen05.commit; tmem_empty[a] lives in the leader and collects 4 epilogue warps x 2 CTAs.
+//   * STACK (split precision): pass 0 = A_hi x [W_hi ; W_lo] as one N=128 operand (leader holds the 64 W_hi rows of a
+//     tap, the peer the 64 W_lo rows), pass 1 = A_lo x W_hi with N=64 (each CTA holds 32 rows of W_hi).
+#pragma once
+#include "isr_conv.cuh"
+
+namespace isr {
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr), "r"(bytes)
+               : "memory");
+}
+// TMA loads whose completion bytes are credited to a barrier that may live in the pair's other CTA
+__device__ __forceinline__ void tma2_load_2d(uint32_t dst, const void *tmap, uint32_t bar_cluster, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma2_load_4d(uint32_t dst, const void *tmap, uint32_t bar_cluster, int c0, int c1, int c2,
+                                             int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, "
+      "%6}], [%2];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// four M256 x N x K16 MMAs covering K = 64 of one tap (see umma_f16_k64)
+__device__ __forceinline__ void umma2_f16_k64(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate_first) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t.reg .b64 a1, a2, a3, b1, b2, b3;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.eq.b32 q, %3, %3;\n\t"
+      "add.s64 a1, %1, 2;\n\t"
+      "add.s64 b1, %2, 2;\n\t"
+      "add.s64 a2, %1, 4;\n\t"
+      "add.s64 b2, %2, 4;\n\t"
+      "add.s64 a3, %1, 6;\n\t"
+      "add.s64 b3, %2, 6;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], a1, b1, %3, q;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], a2, b2, %3, q;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], a3, b3, %3, q;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate_first)
+      : "memory");
+}
+// arrive on the barrier at this offset in BOTH CTAs when all previously issued MMAs of the pair have completed
+__device__ __forceinline__ void umma2_commit_multicast(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+
+// N = 64 output channels.  Weight rows of one CTA per tap: STACK: 64 (X region: W_hi for the leader, W_lo for the peer)
+// + 32 (Y region: its half of W_hi); otherwise 32 per weight part.
+template <int STACK>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
+conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                    const ConvParams p) {
+  constexpr int N = 64;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+
+  constexpr uint32_t kHalfTap = (N / 2) * 128;   // 32 weight rows = 4 KB
+  const uint32_t w_bytes = STACK ? 9 * 3 * kHalfTap : p.n_w_parts * 9 * kHalfTap;   // per CTA
+  const uint32_t s_w = smem_base;
+  const uint32_t s_wy = s_w + 9 * 2 * kHalfTap;   // STACK: Y region after the X region
+  const uint32_t s_stage0 = s_w + ((w_bytes + 1023u) & ~1023u);
+  const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
+  const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
+                 b_tempty = s_bar + 152, s_tptr = s_bar + 168;
+  __shared__ float s_bias[64];
+  if (threadIdx.x < 64) s_bias[threadIdx.x] = p.bias != nullptr ? p.bias[threadIdx.x] : 0.f;
+
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(b_full + 8 * s, 2);    // used in the leader: one arrive.expect_tx per CTA
+      mbar_init(b_empty + 8 * s, 1);   // per CTA: multicast commit
+    }
+    mbar_init(b_w, 2);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(b_tfull + 8 * a, 1);   // per CTA: multicast commit
+      mbar_init(b_tempty + 8 * a, 8);  // leader: 4 epilogue warps x 2 CTAs
+    }
+    fence_barrier_init();
+  }
+  constexpr uint32_t kAccCols = STACK ? 2 * N : N;
+  constexpr uint32_t kTmemCols = 2 * kAccCols;
+  if (warp == 9) tmem_alloc2(s_tptr, kTmemCols);
+  tc_fence_before();
+  cluster_sync_all();   // barriers of both CTAs initialised, TMEM allocated
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(s_tptr));
+
+  const int num_pairs = static_cast<int>(gridDim.x) >> 1;
+  const int pair_id = static_cast<int>(blockIdx.x) >> 1;
+  const int pair_tiles = (p.num_tiles + 1) >> 1;
+  const int my_iters = (pair_tiles - pair_id + num_pairs - 1) / num_pairs;
+
+  if (warp == 8) {
+    // ===================== TMA producer (one per CTA) =====================
+    const uint32_t lead_w = mapa_shared(b_w, 0);
+    if (elect_one()) {
+      mbar_arrive_expect_tx_cluster(lead_w, w_bytes);
+      if constexpr (STACK) {
+        for (int tap = 0; tap < 9; ++tap) {
+          const int row_x = p.w_row0 + (static_cast<int>(rank) * 9 + tap) * p.w_row_stride;   // part = rank
+          tma2_load_2d(s_w + tap * 2 * kHalfTap, &tmW, lead_w, 0, row_x);
+          tma2_load_2d(s_w + tap * 2 * kHalfTap + kHalfTap, &tmW, lead_w, 0, row_x + N / 2);
+          tma2_load_2d(s_wy + tap * kHalfTap, &tmW, lead_w, 0, p.w_row0 + tap * p.w_row_stride + static_cast<int>(rank) * (N / 2));
+        }
+      } else {
+        for (int wp = 0; wp < p.n_w_parts; ++wp)
+          for (int tap = 0; tap < 9; ++tap)
+            tma2_load_2d(s_w + (wp * 9 + tap) * kHalfTap, &tmW, lead_w, 0,
+                         p.w_row0 + (wp * 9 + tap) * p.w_row_stride + static_cast<int>(rank) * (N / 2));
+      }
+    }
+    __syncwarp();
+    uint32_t it = 0;
+    for (int i = 0; i < my_iters; ++i) {
+      const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
+      const bool valid = t < p.num_tiles;
+      const int tx = t % p.tiles_x;
+      const int ty = (t / p.tiles_x) % p.tiles_y;
+      const int b = valid ? t / (p.tiles_x * p.tiles_y) : p.B;   // invalid tile: fully out of bounds = zero fill
+      for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+        const uint32_t s = it % p.num_stages;
+        const uint32_t ph = (it / p.num_stages) & 1;
+        mbar_wait(b_empty + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          const uint32_t lead_full = mapa_shared(b_full + 8 * s, 0);
+          mbar_arrive_expect_tx_cluster(lead_full, kPitch * kHaloH * 128);
+          tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA, lead_full, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 9) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (rank == 0) {
+      const uint32_t idesc = make_idesc_f16(256, N, p.is_bf16);
+      const uint32_t idesc2 = make_idesc_f16(256, 2 * N, p.is_bf16);
+      const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
+      const uint64_t by_desc_base = make_smem_desc_sw128(s_wy, 1024, 0);
+      mbar_wait(b_w, 0);
+      uint32_t it = 0;
+      for (int i = 0; i < my_iters; ++i) {
+        const uint32_t acc = i & 1;
+        const uint32_t acc_ph = (i >> 1) & 1;
+        mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kAccCols;
+        uint32_t first = 1;
+        for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+          const uint32_t s = it % p.num_stages;
+          const uint32_t ph = (it / p.num_stages) & 1;
+          mbar_wait(b_full + 8 * s, ph);
+          tc_fence_after();
+          const uint32_t a_base = s_stage0 + s * p.stage_bytes;
+          const uint64_t a_desc0 = make_smem_desc_sw128(a_base, kPitch * 128, 0);
+          if (elect_one()) {
+            if constexpr (STACK) {
+#pragma unroll
+              for (int tap = 0; tap < 9; ++tap) {
+                const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
+                const uint64_t bdesc = ap == 0 ? b_desc_base + static_cast<uint64_t>((tap * 2 * kHalfTap) >> 4)
+                                               : by_desc_base + static_cast<uint64_t>((tap * kHalfTap) >> 4);
+                umma2_f16_k64(d_tmem, adesc, bdesc, ap == 0 ? idesc2 : idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
+              }
+            } else {
+              const int nwp = (ap == 0) ? p.n_w_parts : 1;  // (hi,hi) (hi,lo) | (lo,hi)
+              for (int wp = 0; wp < nwp; ++wp) {
+#pragma unroll
+                for (int tap = 0; tap < 9; ++tap) {
+                  const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
+                  const uint64_t bdesc = b_desc_base + static_cast<uint64_t>(((wp * 9 + tap) * kHalfTap) >> 4);
+                  umma2_f16_k64(d_tmem, adesc, bdesc, idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
+                }
+                first = 0;
+              }
+            }
+            umma2_commit_multicast(b_empty + 8 * s);  // frees this halo stage in both CTAs
+            if (ap == p.n_act_parts - 1) umma2_commit_multicast(b_tfull + 8 * acc);
+          }
+          __syncwarp();
+          first = 0;
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 0..7: group g = warp/4 drains accumulator buffer g =====================
+    const int grp = warp >> 2, q = warp & 3;
+    for (int i = grp; i < my_iters; i += 2) {
+      const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
+      const bool valid = t < p.num_tiles;
+      const int tx = t % p.tiles_x;
+      const int ty = (t / p.tiles_x) % p.tiles_y;
+      const int b = valid ? t / (p.tiles_x * p.tiles_y) : 0;
+      const uint32_t acc = grp;
+      const uint32_t acc_ph = (i >> 1) & 1;
+      const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
+      epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_shared(b_tempty + 8 * acc, 0));
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();   // the leader's MMAs read the peer's shared memory: nobody leaves before everything retired
+  if (warp == 9) tmem_dealloc2(tmem_base, kTmemCols);
+}
+
+}  // namespace isr

@@ -49,7 +49,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 }
 // Bounded wait: a protocol bug must surface as a trapped kernel (CUDA error), never as a hung GPU box.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  for (uint32_t spin = 0; spin < (1u << 26); ++spin)
+  for (uint32_t spin = 0; spin < (1u << 22); ++spin)
     if (mbar_try_wait(bar, parity)) return;
   __trap();
 }

@@ -320,3 +320,25 @@ def test_output_conv_tap_stacked_equals_generic(isr, golden, weights, prec):
     assert maxabs(outs[(1, 1)], outs[(1, 0)]) <= (5e-4 if prec == "bf16x3" else 6e-3)
     for k, v in outs.items():
         _check_net(v, g["recon_bilinear"])
+
+
+@pytest.mark.parametrize("prec", ["mixed", "bf16x3", "fp16"])
+def test_cta_pair_kernel_equals_single_cta(isr, golden, weights, prec):
+    """conv3x3_pair_kernel (tcgen05 cta_group::2, M=256 over two CTAs) computes the same GEMM as the single-CTA kernel:
+    same products, same accumulation order per output element."""
+    from isosurfacesuperresolution_b200 import _lib
+    g = golden("enhancenet_forward")
+    x = cu(g["x"])
+    outs = {}
+    try:
+        for pair in (1, 0):
+            _lib.set_tunable("cta_pair", pair)
+            net = _net(isr, weights)
+            net.precision = prec
+            with torch.no_grad():
+                outs[pair] = net(x)[0].clone()
+    finally:
+        _lib.set_tunable("cta_pair", 1)
+    assert maxabs(outs[1], outs[0]) <= (6e-3 if prec == "mixed" else 1e-4)
+    if prec != "fp16":
+        _check_net(outs[1], g["recon_bilinear"])
