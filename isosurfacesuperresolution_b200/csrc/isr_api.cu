@@ -25,6 +25,7 @@ static std::atomic<uint64_t> g_launches{0};
 static int g_halo_pitch = 10;
 static int g_base_offset_mode = 0;
 static int g_max_ctas = 0;
+static int g_dbg = 0;             // ConvParams::dbg of isr_net_time_conv launches (bench experiments)
 static int g_cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta_group::2, isr_conv_pair.cuh)
 static int g_final_stacked = 1;   // output conv: tap-stacked kernel (isr_conv_final.cuh) when Cout <= 8
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
@@ -511,6 +512,8 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "max_ctas") == 0) {
     if (value < 0) return fail(ISR_ERR_ARG, "max_ctas must be >= 0");
     slot = &g_max_ctas;
+  } else if (key != nullptr && strcmp(key, "dbg") == 0) {
+    slot = &g_dbg;
   } else if (key != nullptr && strcmp(key, "cta_pair") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "cta_pair must be 0 or 1");
     slot = &g_cta_pair;
@@ -733,7 +736,8 @@ int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scal
   int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
   if (rc != ISR_OK) return rc;
   // scale 4: postblock.4 (64->64 at 4h x 4w, the dominant kernel); scale 1: first residual-block conv (h x w)
-  const ConvLaunch &L = pl->convs[scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1)];
+  ConvLaunch L = pl->convs[scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1)];
+  L.p.dbg = g_dbg;
   cudaEvent_t e0, e1;
   ISR_CUDA(cudaEventCreate(&e0));
   ISR_CUDA(cudaEventCreate(&e1));

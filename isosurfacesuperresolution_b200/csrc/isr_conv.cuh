@@ -42,6 +42,8 @@ struct ConvParams {
   int w_row0;            // first row of this launch's weights inside the weight tensor map
   int w_row_stride;      // rows between consecutive (part, tap) blocks
   int num_stages, stage_bytes;
+  int dbg;               // bench experiments only: bit0 = epilogue does not store, bit1 = no MMAs are issued,
+                         // bit2 = epilogue only does the barrier handshake, bit3 = MMA warp does not wait for the epilogue
   int relu;
   const float *bias;     // N floats (zero padded), or nullptr
   const uint16_t *addend;  // [B,H,W,64*add_parts] or nullptr
@@ -121,6 +123,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
     }
     mbar_wait(b_tfull + 8 * acc, acc_ph);
     tc_fence_after();
+    if (p.dbg & 4) return;   // bench experiment: barrier handshake only
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       uint32_t v[32];

@@ -193,7 +193,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int i = 0; i < my_iters; ++i) {
         const uint32_t acc = i & 1;
         const uint32_t acc_ph = (i >> 1) & 1;
-        mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
+        if (!(p.dbg & 8)) mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
         uint32_t first = 1;
@@ -205,7 +205,8 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t a_base = s_stage0 + s * p.stage_bytes;
           const uint64_t a_desc0 = make_smem_desc_sw128(a_base, kPitch * 128, 0);
           if (elect_one()) {
-            if constexpr (STACK) {
+            if (p.dbg & 2) {
+            } else if constexpr (STACK) {
 #pragma unroll
               for (int tap = 0; tap < 9; ++tap) {
                 const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
