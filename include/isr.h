@@ -128,6 +128,26 @@ int isr_net_forward_recurrent_host(isr_net *net, const float *low_host, const fl
                                    float *recon_host, int B, int h, int w, int precision, void *workspace,
                                    size_t workspace_bytes, float *staging_dev, void *stream);
 
+/* ---- pipelined host-buffer sequence API ------------------------------------------------------------------------
+ * The frame recurrence of one batch of sequences with HOST input / output buffers (what a renderer process that owns host
+ * frames calls; inference/loadedmodel.py:70-121 per frame), software-pipelined over three internal streams: the H2D copy of
+ * frame j+1 and the D2H copy of prediction j overlap the kernels of frame j+1.  The recurrent state never leaves the
+ * device.  Host buffers must be pinned for the copies to overlap.  No device memory is allocated: the caller passes the
+ * network workspace, the state tensor (B x c_prev x 4h x 4w) and `depth` staging slots. */
+typedef struct isr_pipe isr_pipe;
+/* floats of device staging needed for `depth` slots of (low + flow + prediction) */
+int isr_pipe_staging_floats(const isr_net *net, int c_low, int B, int h, int w, int depth, size_t *floats);
+int isr_pipe_create(isr_pipe **pipe, isr_net *net, int c_low, int c_prev, int special_mask, int initial_mode, int B, int h,
+                    int w, int precision, void *workspace, size_t workspace_bytes, float *state_dev, float *staging_dev,
+                    size_t staging_floats, int depth);
+/* Enqueues one frame and returns without waiting for it (it blocks only until the slot it reuses has been drained, i.e.
+ * until frame j-depth is in host memory).  flow_host == NULL starts a new sequence: the state is initialised with
+ * initialImage(low, c_prev, initial_mode).  recon_host (B x Cout x 4h x 4w) is complete after isr_pipe_wait(). */
+int isr_pipe_submit(isr_pipe *pipe, const float *low_host, const float *flow_host, float *recon_host);
+/* Blocks until every submitted frame's prediction is in host memory (and the state is final on the device). */
+int isr_pipe_wait(isr_pipe *pipe);
+void isr_pipe_destroy(isr_pipe *pipe);
+
 /* ---- test / bench hooks --------------------------------------------------------------------------------- */
 
 /* One conv3x3(pad 1) 64->cout (cout in {64, <=16}) through the tensor-core kernel, fp32 NCHW in and out, for unit tests:

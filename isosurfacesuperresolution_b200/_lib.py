@@ -47,6 +47,11 @@ SIGNATURES = {
                                        _vp]),
     "isr_net_forward_recurrent_host": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _vp, _sz, _vp,
                                             _vp]),
+    "isr_pipe_staging_floats": (_i, [_vp, _i, _i, _i, _i, _i, _c.POINTER(_sz)]),
+    "isr_pipe_create": (_i, [_c.POINTER(_vp), _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _sz, _i]),
+    "isr_pipe_submit": (_i, [_vp, _vp, _vp, _vp]),
+    "isr_pipe_wait": (_i, [_vp]),
+    "isr_pipe_destroy": (None, [_vp]),
     "isr_debug_conv3x3": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "isr_debug_conv_workspace_bytes": (_i, [_i, _i, _i, _c.POINTER(_sz)]),
     "isr_set_tunable": (_i, [_c.c_char_p, _i]),

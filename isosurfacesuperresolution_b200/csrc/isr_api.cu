@@ -729,6 +729,117 @@ int isr_net_forward_recurrent_host(isr_net *net, const float *low_host, const fl
   return ISR_OK;
 }
 
+}  // extern "C"
+
+struct isr_pipe {
+  isr_net *net = nullptr;
+  int c_low = 0, c_prev = 0, special_mask = 0, initial_mode = 0, B = 0, h = 0, w = 0, precision = 0, depth = 0;
+  void *ws = nullptr;
+  size_t ws_bytes = 0;
+  float *state = nullptr, *staging = nullptr;
+  size_t slot_floats = 0, n_low = 0, n_flow = 0, n_out = 0;
+  cudaStream_t s_in = nullptr, s_comp = nullptr, s_out = nullptr;
+  std::vector<cudaEvent_t> ev_in, ev_comp, ev_out;
+  uint64_t submitted = 0;
+};
+
+extern "C" {
+
+int isr_pipe_staging_floats(const isr_net *net, int c_low, int B, int h, int w, int depth, size_t *floats) {
+  if (net == nullptr || floats == nullptr || c_low <= 0 || B <= 0 || h <= 0 || w <= 0 || depth < 1)
+    return fail(ISR_ERR_ARG, "pipe_staging_floats: bad arguments");
+  const size_t P = static_cast<size_t>(B) * h * w;
+  *floats = static_cast<size_t>(depth) * (P * (c_low + 2) + P * 16 * net->cout);
+  return ISR_OK;
+}
+
+int isr_pipe_create(isr_pipe **out, isr_net *net, int c_low, int c_prev, int special_mask, int initial_mode, int B, int h,
+                    int w, int precision, void *workspace, size_t workspace_bytes, float *state_dev, float *staging_dev,
+                    size_t staging_floats, int depth) {
+  if (out == nullptr || net == nullptr || workspace == nullptr || state_dev == nullptr || staging_dev == nullptr)
+    return fail(ISR_ERR_ARG, "pipe_create: null argument");
+  if (depth < 1 || depth > 8) return fail(ISR_ERR_ARG, "pipe_create: depth must be in [1, 8]");
+  if (c_low + 16 * c_prev != net->cin)
+    return fail(ISR_ERR_ARG, "pipe_create: c_low + 16*c_prev (%d) != input_channels (%d)", c_low + 16 * c_prev, net->cin);
+  if (initial_mode < 0 || initial_mode > 2) return fail(ISR_ERR_ARG, "unknown input mode");
+  size_t need = 0;
+  int rc = isr_pipe_staging_floats(net, c_low, B, h, w, depth, &need);
+  if (rc != ISR_OK) return rc;
+  if (staging_floats < need) return fail(ISR_ERR_WORKSPACE, "pipe_create: staging too small (%zu < %zu floats)", staging_floats, need);
+  Plan *pl = nullptr;
+  if ((rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl)) != ISR_OK) return rc;
+  isr_pipe *p = new isr_pipe();
+  p->net = net; p->c_low = c_low; p->c_prev = c_prev; p->special_mask = special_mask; p->initial_mode = initial_mode;
+  p->B = B; p->h = h; p->w = w; p->precision = precision; p->depth = depth;
+  p->ws = workspace; p->ws_bytes = workspace_bytes; p->state = state_dev; p->staging = staging_dev;
+  const size_t P = static_cast<size_t>(B) * h * w;
+  p->n_low = P * c_low; p->n_flow = P * 2; p->n_out = P * 16 * net->cout;
+  p->slot_floats = p->n_low + p->n_flow + p->n_out;
+  bool ok = cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&p->s_comp, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking) == cudaSuccess;
+  p->ev_in.resize(depth); p->ev_comp.resize(depth); p->ev_out.resize(depth);
+  for (int i = 0; i < depth && ok; ++i)
+    ok = cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&p->ev_comp[i], cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) {
+    isr_pipe_destroy(p);
+    return fail(ISR_ERR_CUDA, "pipe_create: stream / event creation failed");
+  }
+  *out = p;
+  return ISR_OK;
+}
+
+int isr_pipe_submit(isr_pipe *p, const float *low_host, const float *flow_host, float *recon_host) {
+  if (p == nullptr || low_host == nullptr || recon_host == nullptr) return fail(ISR_ERR_ARG, "pipe_submit: null argument");
+  const int k = static_cast<int>(p->submitted % p->depth);
+  // the slot is reused: frame (j - depth) must have left it (its D2H finished => its kernels finished too)
+  if (p->submitted >= static_cast<uint64_t>(p->depth)) ISR_CUDA(cudaEventSynchronize(p->ev_out[k]));
+  float *low_d = p->staging + static_cast<size_t>(k) * p->slot_floats, *flow_d = low_d + p->n_low,
+        *recon_d = flow_d + p->n_flow;
+  ISR_CUDA(cudaMemcpyAsync(low_d, low_host, p->n_low * sizeof(float), cudaMemcpyHostToDevice, p->s_in));
+  if (flow_host != nullptr)
+    ISR_CUDA(cudaMemcpyAsync(flow_d, flow_host, p->n_flow * sizeof(float), cudaMemcpyHostToDevice, p->s_in));
+  ISR_CUDA(cudaEventRecord(p->ev_in[k], p->s_in));
+  ISR_CUDA(cudaStreamWaitEvent(p->s_comp, p->ev_in[k], 0));
+  int rc;
+  if (flow_host == nullptr) {
+    rc = isr_initial_image(low_d, p->state, p->B, p->c_low, p->h, p->w, p->c_prev, p->initial_mode, 0, 4, p->s_comp);
+    if (rc != ISR_OK) return rc;
+  }
+  rc = isr_net_forward_recurrent(p->net, low_d, p->state, flow_host != nullptr ? flow_d : nullptr, p->c_low, p->c_prev,
+                                 p->special_mask, 0, recon_d, nullptr, p->state, p->net->cout == 6, p->B, p->h, p->w,
+                                 p->precision, p->ws, p->ws_bytes, p->s_comp);
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(cudaEventRecord(p->ev_comp[k], p->s_comp));
+  ISR_CUDA(cudaStreamWaitEvent(p->s_out, p->ev_comp[k], 0));
+  ISR_CUDA(cudaMemcpyAsync(recon_host, recon_d, p->n_out * sizeof(float), cudaMemcpyDeviceToHost, p->s_out));
+  ISR_CUDA(cudaEventRecord(p->ev_out[k], p->s_out));
+  ++p->submitted;
+  return ISR_OK;
+}
+
+int isr_pipe_wait(isr_pipe *p) {
+  if (p == nullptr) return fail(ISR_ERR_ARG, "pipe_wait: null argument");
+  ISR_CUDA(cudaStreamSynchronize(p->s_comp));
+  ISR_CUDA(cudaStreamSynchronize(p->s_out));
+  return ISR_OK;
+}
+
+void isr_pipe_destroy(isr_pipe *p) {
+  if (p == nullptr) return;
+  if (p->s_comp) cudaStreamSynchronize(p->s_comp);
+  if (p->s_out) cudaStreamSynchronize(p->s_out);
+  for (cudaEvent_t e : p->ev_in) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : p->ev_comp) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : p->ev_out) if (e) cudaEventDestroy(e);
+  if (p->s_in) cudaStreamDestroy(p->s_in);
+  if (p->s_comp) cudaStreamDestroy(p->s_comp);
+  if (p->s_out) cudaStreamDestroy(p->s_out);
+  delete p;
+}
+
 int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scale, void *workspace,
                       size_t workspace_bytes, int iters, float *ms, void *stream) {
   if (ms == nullptr || iters <= 0 || (scale != 1 && scale != 4)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");

@@ -203,5 +203,59 @@ class NetHandle:
         return float(ms.value)
 
 
-__all__ = ["flatten_high", "warp_upscale", "initial_image", "postprocess", "shade", "debug_conv3x3", "NetHandle",
+class RecurrentPipeline:
+    """Software-pipelined frame recurrence with HOST input / output buffers (include/isr.h ``isr_pipe_*``): the H2D copy
+    of frame j+1 and the D2H copy of prediction j overlap the kernels of frame j+1; the recurrent state stays on the
+    device.  Host tensors should be pinned (``tensor.pin_memory()``), otherwise the copies serialise."""
+
+    def __init__(self, handle, c_low, c_prev, special_mask, initial_mode, B, h, w, precision="mixed", depth=2):
+        if initial_mode not in INITIAL:
+            raise ValueError("unknown input mode: " + str(initial_mode))
+        self.handle, self.B, self.h, self.w, self.c_low = handle, int(B), int(h), int(w), int(c_low)
+        dev = handle.device
+        _, ws_ptr, ws_bytes = handle.workspace(B, h, w, precision)
+        n = ctypes.c_size_t(0)
+        check(lib().isr_pipe_staging_floats(handle._net, c_low, B, h, w, depth, ctypes.byref(n)))
+        self.state = torch.zeros((B, c_prev, 4 * h, 4 * w), device=dev, dtype=torch.float32)
+        self._staging = torch.empty(n.value, device=dev, dtype=torch.float32)
+        self.out_shape = (B, handle.cout, 4 * h, 4 * w)
+        self._pipe = ctypes.c_void_p(0)
+        torch.cuda.synchronize(dev)      # the pipeline runs on its own streams
+        with torch.cuda.device(dev):
+            check(lib().isr_pipe_create(ctypes.byref(self._pipe), handle._net, c_low, c_prev, int(bool(special_mask)),
+                                        INITIAL[initial_mode], B, h, w, PREC[precision], ctypes.c_void_p(ws_ptr), ws_bytes,
+                                        _p(self.state), _p(self._staging), n.value, depth))
+
+    @staticmethod
+    def _host(t, name, shape=None):
+        if not isinstance(t, torch.Tensor) or t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+            raise TypeError(f"{name}: expected a contiguous float32 CPU tensor (pinned for overlap)")
+        if shape is not None and tuple(t.shape) != tuple(shape):
+            raise ValueError(f"{name}: expected shape {tuple(shape)}, got {tuple(t.shape)}")
+        return ctypes.c_void_p(t.data_ptr())
+
+    def submit(self, low_host, flow_host, recon_host):
+        """Enqueue one frame; ``flow_host=None`` starts a new sequence.  ``recon_host`` is valid after ``wait()``."""
+        lo = self._host(low_host, "low_host", (self.B, self.c_low, self.h, self.w))
+        fl = self._host(flow_host, "flow_host", (self.B, 2, self.h, self.w)) if flow_host is not None else ctypes.c_void_p(0)
+        out = self._host(recon_host, "recon_host", self.out_shape)
+        with torch.cuda.device(self.handle.device):
+            check(lib().isr_pipe_submit(self._pipe, lo, fl, out))
+
+    def wait(self):
+        check(lib().isr_pipe_wait(self._pipe))
+
+    def close(self):
+        if self._pipe:
+            lib().isr_pipe_destroy(self._pipe)
+            self._pipe = ctypes.c_void_p(0)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+__all__ = ["RecurrentPipeline", "flatten_high", "warp_upscale", "initial_image", "postprocess", "shade", "debug_conv3x3", "NetHandle",
            "IsrError", "PREC"]

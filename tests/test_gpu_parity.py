@@ -342,3 +342,25 @@ def test_cta_pair_kernel_equals_single_cta(isr, golden, weights, prec):
     assert maxabs(outs[1], outs[0]) <= (6e-3 if prec == "mixed" else 1e-4)
     if prec != "fp16":
         _check_net(outs[1], g["recon_bilinear"])
+
+
+def test_host_pipeline_equals_device_recurrence(isr, weights):
+    """isr_pipe_* (pinned host buffers, three streams, depth-2 staging) produces exactly the frames of the device-resident
+    recurrence: same kernels, only the copies are overlapped."""
+    from isosurfacesuperresolution_b200 import ops
+    net = _net(isr, weights)
+    B, T, h, w = 2, 5, 24, 40
+    low, flow, _ = orc.synthetic_gbuffer(B, h, w, 21, T=T)
+    preds, _, _ = isr.SequenceRunner(net, initial_image="input").run(cu(low), cu(flow))
+    pipe = ops.RecurrentPipeline(net._native(), 5, 6, True, "input", B, h, w, net.precision, depth=2)
+    outs = [torch.empty((B, 6, 4 * h, 4 * w)).pin_memory() for _ in range(T)]
+    lows = [torch.from_numpy(np.ascontiguousarray(low[:, j])).pin_memory() for j in range(T)]
+    flows = [torch.from_numpy(np.ascontiguousarray(flow[:, j])).pin_memory() for j in range(T)]
+    for j in range(T):
+        pipe.submit(lows[j], None if j == 0 else flows[j - 1], outs[j])
+    pipe.wait()
+    for j in range(T):
+        assert torch.equal(outs[j], preds[j].cpu()), f"frame {j}"
+    with pytest.raises(ValueError):
+        pipe.submit(lows[0][:, :4].contiguous(), None, outs[0])
+    pipe.close()
