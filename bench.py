@@ -263,6 +263,55 @@ def run_b200(args, rank, world, local_rank):
         flops = FLOP_PER_OUT_PX_CONV64 * out_px_per_step
         achieved = flops / (conv_ms * 1e-3) / 1e12
 
+        # ---- configs[2]: interactive 1080p frame latency (1 x 270x480 -> 1080x1920), one CUDA graph per frame:
+        # fused warp + space-to-depth + concat, 26 conv launches, 2 upsamples, fused state, composition incl. shading
+        latency = None
+        if world == 1 and not args.no_latency:
+            lh, lw = 270, 480
+            l_low, l_flow, _ = synthetic.synthetic_gbuffer(1, lh, lw, 4321 + 2, T=2)
+            l_low_t, l_flow_t = torch.from_numpy(l_low).to(dev), torch.from_numpy(l_flow).to(dev)
+            render = torch.rand(1, 12, lh, lw, device=dev)
+            render[:, 3:8] = l_low_t[:, 1]
+            render[:, 8:10] = l_flow_t[:, 0]
+            l_inp = l_low_t[:, 1].contiguous()
+            l_flow0 = l_flow_t[:, 0].contiguous()
+            l_state = isr.initialImage(l_low_t[:, 0].contiguous(), 6, "input", False, 4)
+            params = shd.params22()
+
+            def frame():
+                _, _, st = handle.forward_recurrent(l_inp, l_state, l_flow0, True, PRECISION, want_raw=False,
+                                                    want_state=True, out_state=l_state)
+                return ops.compose(render, st, params, True, False, 0.0)
+
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    frame()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                display = frame()
+            for _ in range(20):
+                graph.replay()
+            torch.cuda.synchronize()
+            times = []
+            for _ in range(200):
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                graph.replay()
+                a1.record()
+                a1.synchronize()
+                times.append(a0.elapsed_time(a1))
+            times.sort()
+            latency = {"p50_ms": times[len(times) // 2], "p99_ms": times[int(len(times) * 0.99) - 1], "frames": len(times),
+                       "config": "BASELINE.json configs[2]: 1 x 480x270 -> 1920x1080, per frame: warp+s2d+concat, EnhanceNet, "
+                                 "state post-process, 12-channel composition incl. Phong+AO shading; inputs on the device",
+                       "launch": "one CUDA graph replay per frame", "output_Mpix_per_s_at_p50":
+                           1080 * 1920 / (times[len(times) // 2] * 1e-3) / 1e6,
+                       "display_checksum": float(display.double().abs().mean())}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -290,6 +339,8 @@ def run_b200(args, rank, world, local_rank):
                      "kernel": "conv3x3_pair_kernel<0> (tcgen05 cta_group::2) 64->64 @1024x1024 x16, "
                                "algorithmic 73,728 FLOP/px", "ms_per_launch": conv_ms},
     }
+    if latency is not None:
+        line["latency_1080p"] = latency
     if world == 1 and not args.no_cpu_baseline:
         mpix, cms, cores, sample = cpu_reference_leg(steps=3, warmup=1)
         line["cpu_baseline"] = {"value": mpix, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
@@ -306,6 +357,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -83,6 +83,15 @@ int isr_postprocess(const float *in, float *out, int B, int C, int H, int W, int
  * gbuf: B x C x H x W (C>=5: mask,nx,ny,nz,depth[,ao]), rgb: B x 3 x H x W. */
 int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, int C, int H, int W, void *stream);
 
+/* GUI / video composition (mainGUI.py:603-608,615-636; mainComparisonVideo3.py:540-556): bilinear x4 of the c_low-channel
+ * low-res render (RGB, mask, normal, depth, flow, AO, shadow: c_low >= 12 for the unshaded form, >= 4 otherwise);
+ * unshaded != 0: channels 0:3 = shading(pred), 3:8 = pred[0:5], 10 = pred[5] (pred = post-processed state, c_pred 5|6);
+ * unshaded == 0: channels 0:3 = clamp(pred, 0, 1) (c_pred = 3).  masking != 0: every channel becomes
+ * background0 + (up(low[3]) * 0.5 + 0.5) * (value - background0).  low: B x c_low x h x w; pred: B x c_pred x 4h x 4w;
+ * out: B x c_low x 4h x 4w.  params_host: as isr_shade (ignored when unshaded == 0, may then be NULL). */
+int isr_compose(const float *low, const float *pred, const float *params_host, float *out, int B, int c_low, int c_pred,
+                int h, int w, int unshaded, int masking, float background0, void *stream);
+
 /* ---- EnhanceNet generator (models/enhancenet.py:8-26,92-145) ------------------------------------------- */
 
 typedef struct isr_net isr_net;

@@ -17,7 +17,7 @@ from .enhancenet import EnhanceNet          # noqa: E402
 from .initial_image import initialImage     # noqa: E402
 from .shading import ScreenSpaceShading     # noqa: E402
 from .videotools import VideoTools          # noqa: E402
-from .inference import LoadedModel, SequenceRunner   # noqa: E402
+from .inference import LoadedModel, SequenceRunner, compose_frame   # noqa: E402
 
 
 def createNetwork(name, upscale_factor, input_channels, channel_mask, output_channels, additional_opt):
@@ -30,4 +30,4 @@ def createNetwork(name, upscale_factor, input_channels, channel_mask, output_cha
 
 
 __all__ = ["createNetwork", "EnhanceNet", "VideoTools", "initialImage", "ScreenSpaceShading", "LoadedModel",
-           "SequenceRunner"]
+           "SequenceRunner", "compose_frame"]

@@ -38,6 +38,7 @@ SIGNATURES = {
     "isr_initial_image": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "isr_postprocess": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "isr_shade": (_i, [_vp, _c.POINTER(_c.c_float), _vp, _i, _i, _i, _i, _vp]),
+    "isr_compose": (_i, [_vp, _vp, _c.POINTER(_c.c_float), _vp, _i, _i, _i, _i, _i, _i, _i, _c.c_float, _vp]),
     "isr_net_create": (_i, [_c.POINTER(_vp), _i, _i, _i, _i, _i]),
     "isr_net_destroy": (None, [_vp]),
     "isr_net_load_weights": (_i, [_vp, _c.POINTER(_vp), _i, _vp]),

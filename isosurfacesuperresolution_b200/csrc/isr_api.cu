@@ -582,6 +582,21 @@ int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, in
   return ISR_OK;
 }
 
+int isr_compose(const float *low, const float *pred, const float *params_host, float *out, int B, int c_low, int c_pred,
+                int h, int w, int unshaded, int masking, float background0, void *stream) {
+  if (low == nullptr || pred == nullptr || out == nullptr || B <= 0 || h <= 0 || w <= 0)
+    return fail(ISR_ERR_ARG, "compose: bad arguments");
+  if (unshaded && (c_low < 12 || c_pred < 5 || params_host == nullptr))
+    return fail(ISR_ERR_ARG, "compose: the unshaded form needs a 12-channel render, a 5|6-channel state and shading parameters");
+  if (!unshaded && (c_low < 4 || c_pred != 3)) return fail(ISR_ERR_ARG, "compose: the shaded form needs c_low >= 4 and c_pred == 3");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  float zeros[22] = {0};
+  ISR_CUDA(launch_compose(low, pred, params_host != nullptr ? params_host : zeros, out, B, c_low, c_pred, h, w, unshaded,
+                          masking, background0, S(stream)));
+  return ISR_OK;
+}
+
 int isr_net_create(isr_net **out, int input_channels, int output_channels, int n_mask, int upsample,
                    int recon_residual) {
   if (out == nullptr) return fail(ISR_ERR_ARG, "net_create: null output");

@@ -15,6 +15,8 @@ cudaError_t launch_initial_image(const float *in, float *out, int B, int Cin, in
 cudaError_t launch_postprocess(const float *in, float *out, int B, int C, int H, int W, int unshaded, cudaStream_t s);
 cudaError_t launch_shade(const float *in, const float *params22_host, float *out, int B, int C, int H, int W,
                          cudaStream_t s);
+cudaError_t launch_compose(const float *low, const float *pred, const float *params22_host, float *out, int B, int c_low,
+                           int c_pred, int h, int w, int unshaded, int masking, float bg0, cudaStream_t s);
 cudaError_t launch_pack_recurrent(const float *low, const float *prev, const float *flow, uint16_t *g0, uint16_t *g1,
                                   int B, int c_low, int c_prev, int h, int w, int special_mask, int align_corners,
                                   int nparts, int is_bf16, cudaStream_t s);

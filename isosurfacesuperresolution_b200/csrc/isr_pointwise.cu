@@ -387,6 +387,50 @@ shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams 
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// GUI / video composition (mainGUI.py:603-608,615-636; mainComparisonVideo3.py:540-556), one pass:
+//   image = bilinear x4 of the 12-channel low-res render (RGB, mask, normal, depth, flow, AO, shadow)
+//   unshaded: image[0:3] = shading(state); image[3:8] = state[0:5]; image[10] = state[5]
+//   shaded:   image[0:3] = clamp(pred, 0, 1)
+//   masking:  image = bg0 + (up(mask_low) * 0.5 + 0.5) * (image - bg0)      (all 12 channels, bg0 = background[0])
+__global__ void __launch_bounds__(256)
+compose_kernel(const float *__restrict__ low, const float *__restrict__ pred, float *__restrict__ out, ShadeParams sp,
+               float sf, int B, int c_low, int c_pred, int h, int w, int unshaded, int masking, float bg0) {
+  const int H = 4 * h, W = 4 * w;
+  const size_t plane = static_cast<size_t>(H) * W, lplane = static_cast<size_t>(h) * w;
+  const int y = blockIdx.x % H, b = blockIdx.x / H;
+  int y0, y1;
+  float ly0, ly1;
+  bil_src_pw(y, h, 0.25f, y0, y1, ly0, ly1);
+  const float *lb = low + static_cast<size_t>(b) * c_low * lplane;
+  const float *pb = pred + static_cast<size_t>(b) * c_pred * plane + static_cast<size_t>(y) * W;
+  float *ob = out + static_cast<size_t>(b) * c_low * plane + static_cast<size_t>(y) * W;
+  for (int x = threadIdx.x; x < W; x += blockDim.x) {
+    int x0, x1;
+    float lx0, lx1;
+    bil_src_pw(x, w, 0.25f, x0, x1, lx0, lx1);
+    float m = 1.f;
+    if (masking) m = bil_sample(lb + 3 * lplane, w, y0, y1, x0, x1, ly0, ly1, lx0, lx1, 1.f) * 0.5f + 0.5f;
+    float rgb[3];
+    if (unshaded) {
+      shade_pixel(sp, pb[x], pb[plane + x], pb[2 * plane + x], pb[3 * plane + x], c_pred >= 6 ? pb[5 * plane + x] : 1.f,
+                  c_pred >= 6, sf, rgb);
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) rgb[c] = fminf(fmaxf(pb[c * plane + x], 0.f), 1.f);
+    }
+    for (int c = 0; c < c_low; ++c) {
+      float v;
+      if (c < 3) v = rgb[c];
+      else if (unshaded && c < 8) v = pb[(c - 3) * plane + x];
+      else if (unshaded && c == 10 && c_pred >= 6) v = pb[5 * plane + x];
+      else v = bil_sample(lb + c * lplane, w, y0, y1, x0, x1, ly0, ly1, lx0, lx1, 1.f);
+      if (masking) v = bg0 + m * (v - bg0);
+      ob[c * plane + x] = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // nn.Upsample(scale_factor=2, mode) on NHWC 16-bit 64-channel features (enhancenet.py:40-48,116,119).
 // One thread = one source column j x one 8-channel chunk (16 B), walking down a strip of kUpStrip source rows.  Per
 // source row it loads 3 x 16 B (columns j-1, j, j+1), forms the two horizontal interpolants (output columns 2j, 2j+1) and
@@ -604,6 +648,16 @@ cudaError_t launch_shade(const float *in, const float *params22, float *out, int
     dim3 grid(grid_for(plane, 256), B);
     shade_kernel<1><<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
   }
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_compose(const float *low, const float *pred, const float *params22, float *out, int B, int c_low,
+                           int c_pred, int h, int w, int unshaded, int masking, float bg0, cudaStream_t s) {
+  ShadeParams sp;
+  for (int i = 0; i < 22; ++i) sp.v[i] = params22[i];
+  const int expo = static_cast<int>(params22[19]);
+  const float sf = static_cast<float>((static_cast<double>(expo) + 2.0) / (2.0 * 3.14159265358979323846));
+  compose_kernel<<<B * 4 * h, 256, 0, s>>>(low, pred, out, sp, sf, B, c_low, c_pred, h, w, unshaded, masking, bg0);
   count_launch();
   return cudaGetLastError();
 }

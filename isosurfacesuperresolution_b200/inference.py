@@ -107,6 +107,19 @@ class LoadedModel:
         return prediction
 
 
+def compose_frame(image_low, image_raw, shading=None, masking=False, background=(0.0, 0.0, 0.0)):
+    """The composition step of ``GUI.performSuperresolution`` (mainGUI.py:603-608,615-636; mainComparisonVideo3.py:540-556)
+    as ONE kernel.  ``image_low``: B x 12 x h x w renderer output (mask already in [-1, 1] as the GUI keeps it);
+    ``image_raw``: the post-processed network output B x 6 x 4h x 4w (unshaded networks, needs ``shading``) or the RGB
+    prediction B x 3 x 4h x 4w (shaded networks).  Returns the B x 12 x 4h x 4w display tensor."""
+    from . import ops
+    unshaded = image_raw.shape[1] >= 5
+    if unshaded and shading is None:
+        raise ValueError("compose_frame: unshaded composition needs a ScreenSpaceShading object")
+    return ops.compose(image_low, image_raw, shading.params22() if unshaded else None, unshaded, masking,
+                       float(background[0]))
+
+
 class SequenceRunner:
     """Forward-only frame recurrence over a batch of independent sequences (mainVideoUnshaded.py:417-465).
 
@@ -142,4 +155,4 @@ class SequenceRunner:
         return preds, rgbs, state
 
 
-__all__ = ["LoadedModel", "SequenceRunner", "ScreenSpaceShading"]
+__all__ = ["LoadedModel", "SequenceRunner", "ScreenSpaceShading", "compose_frame"]

@@ -91,6 +91,19 @@ def shade(gbuffer, params22):
     return out
 
 
+def compose(image_low, pred, params22, unshaded=True, masking=False, background0=0.0):
+    """GUI / video composition (mainGUI.py:603-608,615-636): 12-channel bilinear x4 + overwrite + optional mask lerp."""
+    low, pr = _prep(image_low, "image_low"), _prep(pred, "pred")
+    B, c_low, h, w = low.shape
+    assert tuple(pr.shape[2:]) == (4 * h, 4 * w) and pr.shape[0] == B
+    arr = (ctypes.c_float * 22)(*[float(v) for v in params22]) if params22 is not None else None
+    out = torch.empty((B, c_low, 4 * h, 4 * w), device=low.device, dtype=torch.float32)
+    with torch.cuda.device(low.device):
+        check(lib().isr_compose(_p(low), _p(pr), arr, _p(out), B, c_low, pr.shape[1], h, w, int(bool(unshaded)),
+                                int(bool(masking)), float(background0), _stream()))
+    return out
+
+
 def _workspace(device, nbytes):
     # cudaMalloc'd blocks from torch's caching allocator are 512-byte aligned; over-allocate and slice to 1024
     buf = torch.empty(nbytes + 1024, device=device, dtype=torch.uint8)
@@ -257,5 +270,5 @@ class RecurrentPipeline:
             pass
 
 
-__all__ = ["RecurrentPipeline", "flatten_high", "warp_upscale", "initial_image", "postprocess", "shade", "debug_conv3x3", "NetHandle",
+__all__ = ["RecurrentPipeline", "compose", "flatten_high", "warp_upscale", "initial_image", "postprocess", "shade", "debug_conv3x3", "NetHandle",
            "IsrError", "PREC"]

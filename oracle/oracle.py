@@ -232,6 +232,25 @@ def unshaded_sequence(state_dict, low, flow, upsample_mode="bilinear", initial="
 from isosurfacesuperresolution_b200.synthetic import shading_params, synthetic_gbuffer  # noqa: E402,F401
 
 
+# mainGUI.py:603-608,615-636 (GUI.performSuperresolution, composition part; the method itself needs tkinter and cannot be
+# imported, so it is restated op for op with the torch calls it makes)
+def compose_frame(image_low, image_raw, shade_params=None, masking=False, background0=0.0):
+    image = torch.from_numpy(_f32(image_low))
+    raw = torch.from_numpy(_f32(image_raw))
+    image = F.interpolate(image, scale_factor=4, mode="bilinear")                      # mainGUI.py:603 / :627
+    base_mask = image[:, 3:4, :, :].clone()
+    if raw.shape[1] >= 5:                                                              # unshaded, :606-608
+        image[:, 0:3, :, :] = torch.from_numpy(shade(raw.numpy(), shade_params))
+        image[:, 3:8, :, :] = raw[:, 0:-1, :, :]
+        image[:, 10, :, :] = raw[:, -1, :, :]
+    else:                                                                              # shaded, :629
+        image[:, 0:3, :, :] = torch.clamp(raw, 0, 1)
+    if masking:                                                                        # :630-636
+        mask = base_mask * 0.5 + 0.5
+        image = background0 + mask * (image - background0)
+    return image.numpy()
+
+
 def psnr(a, b, epsilon=1e-7):
     """utils/psnr.py:10-15 (unmasked branch): 10*log10(1/(eps + mean((a-b)^2))), peak = 1."""
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)

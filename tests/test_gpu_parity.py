@@ -364,3 +364,24 @@ def test_host_pipeline_equals_device_recurrence(isr, weights):
     with pytest.raises(ValueError):
         pipe.submit(lows[0][:, :4].contiguous(), None, outs[0])
     pipe.close()
+
+
+@pytest.mark.parametrize("masking", [False, True])
+def test_compose_frame_vs_oracle(isr, masking):
+    """a13: GUI composition (12-channel bilinear x4 + shading + overwrite + mask lerp) in one kernel."""
+    rng = np.random.RandomState(3)
+    low, flow, ao = orc.synthetic_gbuffer(1, 54, 96, 8)
+    img = rng.uniform(0, 1, (1, 12, 54, 96)).astype(np.float32)
+    img[:, 3:8] = low[:, 0]
+    raw = orc.postprocess(rng.uniform(-1.2, 1.2, (1, 6, 216, 384)).astype(np.float32), unshaded=True)
+    prm = orc.shading_params(material=(1.0, 0.3, 0.0), ao_strength=0.5, background=(0.2, 0.3, 0.4))
+    shd = _shading_from_params(isr, prm)
+    ref = orc.compose_frame(img, raw, prm, masking=masking, background0=0.2)
+    out = isr.compose_frame(cu(img), cu(raw), shd, masking=masking, background=(0.2, 0.3, 0.4))
+    assert out.shape == (1, 12, 216, 384)
+    assert maxabs(out, ref) <= 1e-5
+    # shaded networks: RGB prediction clamped into channels 0:3, everything else upsampled
+    rgb = rng.uniform(-0.2, 1.2, (1, 3, 216, 384)).astype(np.float32)
+    ref_s = orc.compose_frame(img, rgb, None, masking=masking, background0=1.0)
+    out_s = isr.compose_frame(cu(img), cu(rgb), None, masking=masking, background=(1.0, 1.0, 1.0))
+    assert maxabs(out_s, ref_s) <= 1e-5
