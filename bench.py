@@ -29,7 +29,7 @@ METRIC = "4x-upscaled output Mpix/s"
 UNIT = "Mpix/s"
 B_SEQ, T_FRAMES, H_LOW, W_LOW = 16, 10, 256, 256
 FLOP_PER_OUT_PX_CONV64 = 2 * 64 * 64 * 9            # the dominant kernel: one 64->64 conv3x3 at 4h x 4w
-PRECISION = os.environ.get("ISR_PRECISION", "mixed")
+PRECISION = os.environ.get("ISR_PRECISION", "hybrid")
 
 
 def load_weights():
@@ -320,7 +320,9 @@ def run_b200(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": {"mixed": "bf16x3(trunk)+fp16(tail), fp32 accumulate", "bf16x3": "bf16x3", "bf16": "bf16",
-                  "fp16": "fp16", "fp16x3": "fp16x3", "mixed2": "bf16x3(trunk)+fp16x2(tail)"}[PRECISION],
+                  "fp16": "fp16", "fp16x3": "fp16x3", "mixed2": "bf16x3(trunk)+fp16x2(tail)",
+                  "hybrid": "fp16 (x3 split in preblock + 4 residual blocks, split weights in the other 6, single-pass tail), "
+                            "fp32 accumulate"}.get(PRECISION, PRECISION),
         "data": "synthetic",
         "config": {"workload": "EnhanceNet unshaded 4x frame-recurrent, 256x256->1024x1024, 16 sequences per GPU "
                                "(BASELINE.json configs[1]); step = 1 recurrent frame of the batch incl. warp+s2d, "

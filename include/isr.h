@@ -45,12 +45,18 @@ extern "C" {
  * "x3" = split operands: A=Ahi+Alo, W=Whi+Wlo, three MMAs (hi*hi + hi*lo + lo*hi) per k-step. */
 #define ISR_PREC_BF16 0        /* single-pass bf16 everywhere (fast; misses 1e-2 with random-init weights) */
 #define ISR_PREC_BF16X3 1      /* split-bf16 everywhere (safe) */
-#define ISR_PREC_MIXED 2       /* DEFAULT: split-bf16 in the low-res trunk, single-pass fp16 in the high-res tail (the output
+#define ISR_PREC_MIXED 2       /* split-bf16 in the low-res trunk, single-pass fp16 in the high-res tail (the output
                                 * conv uses split fp16 weights stacked along N, which costs nothing: N=32) */
 #define ISR_PREC_FP16 3        /* single-pass fp16 everywhere */
 #define ISR_PREC_FP16X3 4      /* split-fp16 everywhere */
 #define ISR_PREC_MIXED2 5      /* split-bf16 trunk, fp16 tail with split activations (2 MMAs per k-step) */
 #define ISR_PREC_MIXED3 6      /* split-bf16 trunk, fp16 tail with split WEIGHTS stacked along N (one N=128 MMA per k-step) */
+#define ISR_PREC_MIXED4 7      /* fp16 trunk with split weights stacked along N (one N=128 MMA per k-step), fp16 tail */
+#define ISR_PREC_MIXED5 8      /* MIXED4 + the residual stream stored as hi + lo planes (MMAs read hi, the addend is exact) */
+#define ISR_PREC_HYBRID 10     /* fp16: preblock + first K residual blocks fully split (x3), remaining blocks hi activations x split
+                                * weights (one N=128 MMA per k-step), single-pass fp16 tail; K = tunable trunk_full_blocks (4).  DEFAULT of the
+                                * Python front end and of bench.py */
+#define ISR_PREC_MIXED6 9      /* single-pass fp16 everywhere + hi/lo residual stream */
 
 int isr_version(void);
 const char *isr_last_error(void);

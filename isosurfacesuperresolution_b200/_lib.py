@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libisr.so")
 
-PREC = {"bf16": 0, "bf16x3": 1, "mixed": 2, "fp16": 3, "fp16x3": 4, "mixed2": 5, "mixed3": 6}
+PREC = {"bf16": 0, "bf16x3": 1, "mixed": 2, "fp16": 3, "fp16x3": 4, "mixed2": 5, "mixed3": 6, "mixed4": 7, "mixed5": 8, "mixed6": 9, "hybrid": 10}
 UPSAMPLE = {"nearest": 0, "bilinear": 1}
 INITIAL = {"zero": 0, "unshaded": 1, "input": 2}
 

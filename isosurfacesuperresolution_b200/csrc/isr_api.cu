@@ -29,6 +29,7 @@ static int g_dbg = 0;             // ConvParams::dbg of isr_net_time_conv launch
 static int g_cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta_group::2, isr_conv_pair.cuh)
 static int g_final_stacked = 1;   // output conv: tap-stacked kernel (isr_conv_final.cuh) when Cout <= 8
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
+static int g_trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
@@ -148,7 +149,8 @@ static int setup_kernel_attrs() {
 
 // fills geometry, smem plan and tensor maps of one conv launch; epilogue fields are set by the caller
 static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W, int n_act_parts, const void *wpacked,
-                     int w_rows_total, int w_row0, int w_row_stride, int n_w_parts, int is_bf16) {
+                     int w_rows_total, int w_row0, int w_row_stride, int n_w_parts, int is_bf16, int tensor_parts = 0) {
+  if (tensor_parts < n_act_parts) tensor_parts = n_act_parts;   // planes stored per pixel (>= planes the MMAs read)
   memset(&L->p, 0, sizeof L->p);
   L->n = n;
   ConvParams &p = L->p;
@@ -181,7 +183,7 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
     if (cap < 2) cap = 2;
     L->grid = want < cap ? want : cap;
   }
-  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kPitch, kHaloH, is_bf16);
+  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * tensor_parts, kPitch, kHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
   return make_w_map(&L->tmW, wpacked, w_rows_total, L->pair ? n / 2 : n, is_bf16);
 }
@@ -255,7 +257,10 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
 
 // ---- precision schemes -----------------------------------------------------------------------------------------
 struct Scheme {
-  int bf16, na, nw;  // operand format, activation parts, weight parts
+  int bf16, na, nw;  // operand format, activation parts read by the MMAs, weight parts
+  int fs = 0;        // parts STORED for the residual stream f (0 = na).  fs = 2 with na = 1: the stream keeps hi + lo planes
+                     // (the block's addend and the next block's output are exact to ~22 bits) while the MMAs read hi only
+  int stream_parts() const { return fs > 0 ? fs : na; }
 };
 static bool get_schemes(int precision, Scheme *trunk, Scheme *tail, int *fin_nw = nullptr) {
   int dummy;
@@ -269,6 +274,10 @@ static bool get_schemes(int precision, Scheme *trunk, Scheme *tail, int *fin_nw 
     case ISR_PREC_FP16X3: *trunk = {0, 2, 2}; *tail = {0, 2, 2}; return true;
     case ISR_PREC_MIXED2: *trunk = {1, 2, 2}; *tail = {0, 2, 1}; return true;
     case ISR_PREC_MIXED3: *trunk = {1, 2, 2}; *tail = {0, 1, 2}; return true;
+    case ISR_PREC_MIXED4: *trunk = {0, 1, 2, 1}; *tail = {0, 1, 1}; *fin_nw = 2; return true;
+    case ISR_PREC_MIXED5: *trunk = {0, 1, 2, 2}; *tail = {0, 1, 1}; *fin_nw = 2; return true;
+    case ISR_PREC_MIXED6: *trunk = {0, 1, 1, 2}; *tail = {0, 1, 1}; *fin_nw = 2; return true;
+    case ISR_PREC_HYBRID: *trunk = {0, 2, 2}; *tail = {0, 1, 1}; *fin_nw = 2; return true;   // per block, see build_plan
   }
   return false;
 }
@@ -284,7 +293,8 @@ struct Layer {
 };
 
 struct Plan {
-  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0, fin_stacked = 0, stack_w = 0, cta_pair = 0;
+  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0, fin_stacked = 0, stack_w = 0, cta_pair = 0,
+      full_blocks = 0, f_last_parts = 1;
   void *ws = nullptr;
   Scheme trunk, tail;
   int fin_nw = 0;
@@ -310,7 +320,7 @@ namespace isr {
 static size_t plan_bytes(const isr_net *net, int B, int h, int w, const Scheme &trunk, const Scheme &tail,
                          size_t *offs /* 9 offsets */) {
   const size_t P = static_cast<size_t>(B) * h * w;
-  const size_t lo = align_up(P * 128 * trunk.na, 1024);
+  const size_t lo = align_up(P * 128 * (trunk.stream_parts() > trunk.na ? trunk.stream_parts() : trunk.na), 1024);
   const size_t t2 = align_up(P * 4 * 128 * tail.na, 1024);
   const size_t t4 = align_up(P * 16 * 128 * tail.na, 1024);
   size_t o = 0;
@@ -339,9 +349,10 @@ static void set_store(ConvLaunch *L, const float *bias, int relu, const uint16_t
 }
 
 static int conv_for_layer(ConvLaunch *L, const Layer &ly, int g, const uint16_t *act, int B, int H, int W,
-                          const Scheme &sc) {
+                          const Scheme &sc, int tensor_parts = 0) {
   const uint16_t *wbase = ly.packed + (sc.bf16 ? 0 : ly.per_fmt());
-  return init_conv(L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16);
+  return init_conv(L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16,
+                   tensor_parts);
 }
 
 static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
@@ -355,6 +366,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->B = B; pl->h = h; pl->w = w; pl->precision = precision; pl->ws = ws;
   pl->pitch = g_halo_pitch; pl->bo = g_base_offset_mode; pl->max_ctas = g_max_ctas;
   pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w; pl->cta_pair = g_cta_pair;
+  pl->full_blocks = g_trunk_full_blocks;
   uint8_t *base = static_cast<uint8_t *>(ws);
   auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
   const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
@@ -366,33 +378,45 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->u4 = at(7);
   pl->c4 = at(8);
   const Scheme &T = pl->trunk, &Hs = pl->tail;
+  const int FS = T.stream_parts();   // planes of the residual-stream tensors (partial, f0, f1)
   pl->convs.clear();
   ConvLaunch L;
   int rc;
   // preblock (enhancenet.py:93-95): one launch per 64-channel input group; the second adds the first's partial sums
   if (net->G == 1) {
     if ((rc = conv_for_layer(&L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
-    set_store(&L, net->layers[0].bias, 1, nullptr, 0, f0, T.na);
+    set_store(&L, net->layers[0].bias, 1, nullptr, 0, f0, FS);
     pl->convs.push_back(L);
   } else {
     if ((rc = conv_for_layer(&L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
-    set_store(&L, nullptr, 0, nullptr, 0, partial, T.na);
+    set_store(&L, nullptr, 0, nullptr, 0, partial, FS);
     pl->convs.push_back(L);
     if ((rc = conv_for_layer(&L, net->layers[0], 1, pl->in_g[1], B, h, w, T)) != ISR_OK) return rc;
-    set_store(&L, net->layers[0].bias, 1, partial, T.na, f0, T.na);
+    set_store(&L, net->layers[0].bias, 1, partial, FS, f0, FS);
     pl->convs.push_back(L);
   }
   // 10 residual blocks (enhancenet.py:108-112,140-141): f = f + conv(relu(conv(f)))
+  // ISR_PREC_HYBRID: the first K blocks run fully split (hi*hi + hi*lo + lo*hi), the rest read the hi plane only against
+  // split weights (one N=128 MMA per k-step); rounding errors injected early are amplified by every later block, so the
+  // expensive scheme is spent where it matters.
+  const bool hybrid = precision == ISR_PREC_HYBRID;
+  const int K = hybrid ? pl->full_blocks : 10;
+  const Scheme cheap = {0, 1, 2, 1};
   uint16_t *fc = f0, *fn = f1;
+  int pf = FS;   // planes stored in the current stream tensor
   for (int blk = 0; blk < 10; ++blk) {
-    if ((rc = conv_for_layer(&L, net->layers[1 + 2 * blk], 0, fc, B, h, w, T)) != ISR_OK) return rc;
-    set_store(&L, net->layers[1 + 2 * blk].bias, 1, nullptr, 0, t, T.na);
+    const Scheme &Sb = (hybrid && blk >= K) ? cheap : T;
+    const int pn = hybrid ? ((blk + 1 < K) ? 2 : 1) : FS;
+    if ((rc = conv_for_layer(&L, net->layers[1 + 2 * blk], 0, fc, B, h, w, Sb, pf)) != ISR_OK) return rc;
+    set_store(&L, net->layers[1 + 2 * blk].bias, 1, nullptr, 0, t, Sb.na);
     pl->convs.push_back(L);
-    if ((rc = conv_for_layer(&L, net->layers[2 + 2 * blk], 0, t, B, h, w, T)) != ISR_OK) return rc;
-    set_store(&L, net->layers[2 + 2 * blk].bias, 0, fc, T.na, fn, T.na);
+    if ((rc = conv_for_layer(&L, net->layers[2 + 2 * blk], 0, t, B, h, w, Sb)) != ISR_OK) return rc;
+    set_store(&L, net->layers[2 + 2 * blk].bias, 0, fc, pf, fn, pn);
     pl->convs.push_back(L);
     uint16_t *sw = fc; fc = fn; fn = sw;
+    pf = pn;
   }
+  pl->f_last_parts = pf;
   pl->f_last = fc;
   // postblock (enhancenet.py:115-125): up2 -> conv -> relu -> up2 -> conv -> relu -> conv -> relu -> conv
   pl->idx_post1 = static_cast<int>(pl->convs.size());
@@ -431,7 +455,8 @@ static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision
   for (Plan *pl : net->plans)
     if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
         pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
-        pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair) {
+        pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair &&
+        pl->full_blocks == g_trunk_full_blocks) {
       *out = pl;
       return ISR_OK;
     }
@@ -457,7 +482,7 @@ static int run_plan(isr_net *net, Plan *pl, const float *skip_src, long long ski
   int rc;
   for (int i = 0; i < static_cast<int>(pl->convs.size()); ++i) {
     if (i == pl->idx_post1)
-      ISR_CUDA(launch_upsample2x(pl->f_last, pl->u2, pl->B, pl->h, pl->w, T.na, Hs.na, T.bf16, Hs.bf16,
+      ISR_CUDA(launch_upsample2x(pl->f_last, pl->u2, pl->B, pl->h, pl->w, pl->f_last_parts, Hs.na, T.bf16, Hs.bf16,
                                  net->upsample == ISR_UPSAMPLE_BILINEAR, s));
     if (i == pl->idx_post4)
       ISR_CUDA(launch_upsample2x(pl->c2, pl->u4, pl->B, 2 * pl->h, 2 * pl->w, Hs.na, Hs.na, Hs.bf16, Hs.bf16,
@@ -520,6 +545,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "final_stacked") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "final_stacked must be 0 or 1");
     slot = &g_final_stacked;
+  } else if (key != nullptr && strcmp(key, "trunk_full_blocks") == 0) {
+    if (value < 0 || value > 10) return fail(ISR_ERR_ARG, "trunk_full_blocks must be in [0, 10]");
+    slot = &g_trunk_full_blocks;
   } else if (key != nullptr && strcmp(key, "stack_w") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "stack_w must be 0 or 1");
     slot = &g_stack_w;

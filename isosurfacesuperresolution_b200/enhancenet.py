@@ -25,8 +25,8 @@ STATE_DICT_KEYS = (
 
 
 class EnhanceNet(nn.Module):
-    # tensor-core operand scheme of the CUDA path (include/isr.h); "mixed" meets the 1e-2 / 50 dB parity bar
-    precision = "mixed"
+    # tensor-core operand scheme of the CUDA path (include/isr.h); "hybrid" meets the 1e-2 / 50 dB parity bar
+    precision = "hybrid"
 
     def __init__(self, upscale_factor, input_channels, channel_mask, output_channels, opt):
         super().__init__()

@@ -172,7 +172,7 @@ class NetHandle:
             self._ws[key] = (buf, ptr, n.value)
         return self._ws[key]
 
-    def forward(self, inputs, precision="mixed", want_raw=True, want_state=False, state_unshaded=True):
+    def forward(self, inputs, precision="hybrid", want_raw=True, want_state=False, state_unshaded=True):
         x = _prep(inputs, "inputs")
         B, C, h, w = x.shape
         assert C == self.cin
@@ -186,7 +186,7 @@ class NetHandle:
                                         w, PREC[precision], ctypes.c_void_p(ptr), nbytes, _stream()))
         return recon, raw, state
 
-    def forward_recurrent(self, low, prev, flow, special_mask, precision="mixed", align_corners=False, want_raw=False,
+    def forward_recurrent(self, low, prev, flow, special_mask, precision="hybrid", align_corners=False, want_raw=False,
                           want_state=True, state_unshaded=True, out_state=None):
         low, prev = _prep(low, "low"), _prep(prev, "previous_output")
         flow = _prep(flow, "flow") if flow is not None else None
@@ -207,7 +207,7 @@ class NetHandle:
                                                   ctypes.c_void_p(ptr), nbytes, _stream()))
         return recon, raw, state
 
-    def time_conv(self, B, h, w, precision="mixed", scale=4, iters=10):
+    def time_conv(self, B, h, w, precision="hybrid", scale=4, iters=10):
         _, ptr, nbytes = self.workspace(B, h, w, precision)
         ms = ctypes.c_float(0)
         with torch.cuda.device(self.device):
@@ -221,7 +221,7 @@ class RecurrentPipeline:
     of frame j+1 and the D2H copy of prediction j overlap the kernels of frame j+1; the recurrent state stays on the
     device.  Host tensors should be pinned (``tensor.pin_memory()``), otherwise the copies serialise."""
 
-    def __init__(self, handle, c_low, c_prev, special_mask, initial_mode, B, h, w, precision="mixed", depth=2):
+    def __init__(self, handle, c_low, c_prev, special_mask, initial_mode, B, h, w, precision="hybrid", depth=2):
         if initial_mode not in INITIAL:
             raise ValueError("unknown input mode: " + str(initial_mode))
         self.handle, self.B, self.h, self.w, self.c_low = handle, int(B), int(h), int(w), int(c_low)

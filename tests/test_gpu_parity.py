@@ -165,7 +165,7 @@ def _check_net(out, ref, tol=1e-2, min_psnr=50.0):
 
 
 @pytest.mark.parametrize("ups", ["bilinear", "nearest"])
-@pytest.mark.parametrize("prec", ["mixed", "mixed3", "bf16x3", "fp16x3"])
+@pytest.mark.parametrize("prec", ["hybrid", "mixed", "mixed3", "mixed4", "bf16x3", "fp16x3"])
 def test_enhancenet_forward_golden(isr, golden, weights, ups, prec):
     g = golden("enhancenet_forward")
     net = _net(isr, weights, ups=ups)
@@ -242,7 +242,7 @@ def test_sequence_recurrence_golden(isr, golden, weights):
             _check_net(pred, g[f"pred_{j}"])
             assert maxabs(shd(state), g[f"rgb_{j}"]) <= 2e-2
     # free-running
-    for prec, tol, min_psnr in (("bf16x3", 1e-2, 50.0), ("mixed", 5e-2, 45.0)):
+    for prec, tol, min_psnr in (("bf16x3", 1e-2, 50.0), ("mixed", 5e-2, 45.0), ("hybrid", 5e-2, 45.0)):
         net.precision = prec
         runner = isr.SequenceRunner(net, initial_image="input", shading=shd)
         preds, rgbs, _ = runner.run(low, flow)
@@ -293,7 +293,7 @@ def test_no_cpu_fallback(isr, weights):
         isr.VideoTools.flatten_high(torch.zeros(1, 6, 8, 8), 4)
 
 
-@pytest.mark.parametrize("prec", ["mixed", "bf16x3"])
+@pytest.mark.parametrize("prec", ["hybrid", "mixed", "bf16x3"])
 def test_output_conv_tap_stacked_equals_generic(isr, golden, weights, prec):
     """The tap-stacked output-conv kernel (isr_conv_final.cuh) and the generic N=16 kernel compute the same convolution
     (different fp32 summation order only); same for the N=128 hi/lo weight stacking of the split-precision layers."""
@@ -322,7 +322,7 @@ def test_output_conv_tap_stacked_equals_generic(isr, golden, weights, prec):
         _check_net(v, g["recon_bilinear"])
 
 
-@pytest.mark.parametrize("prec", ["mixed", "bf16x3", "fp16"])
+@pytest.mark.parametrize("prec", ["hybrid", "mixed", "bf16x3", "fp16"])
 def test_cta_pair_kernel_equals_single_cta(isr, golden, weights, prec):
     """conv3x3_pair_kernel (tcgen05 cta_group::2, M=256 over two CTAs) computes the same GEMM as the single-CTA kernel:
     same products, same accumulation order per output element."""
@@ -339,7 +339,7 @@ def test_cta_pair_kernel_equals_single_cta(isr, golden, weights, prec):
                 outs[pair] = net(x)[0].clone()
     finally:
         _lib.set_tunable("cta_pair", 1)
-    assert maxabs(outs[1], outs[0]) <= (6e-3 if prec == "mixed" else 1e-4)
+    assert maxabs(outs[1], outs[0]) <= (6e-3 if prec in ("mixed", "hybrid") else 1e-4)
     if prec != "fp16":
         _check_net(outs[1], g["recon_bilinear"])
 

@@ -44,8 +44,12 @@ seqs = []
 for seed in (11, 12, 13):
     low, flow, _ = isr.synthetic.synthetic_gbuffer(1, 48, 64, seed, T=4)
     seqs.append((low, flow, orc.unshaded_sequence(weights, low, flow, "bilinear", "input", backend="torch")[0]))
-for m in modes:
+for mk in modes:
     r = {}
+    m = mk
+    if ":" in mk:                      # "hybrid:K" = ISR_PREC_HYBRID with K fully split residual blocks
+        m, k = mk.split(":")
+        isr._lib.set_tunable("trunk_full_blocks", int(k))
     with torch.no_grad():
         for ups in ("bilinear", "nearest"):
             n = net_for(ups)
@@ -84,6 +88,6 @@ for m in modes:
         e1.record()
         torch.cuda.synchronize()
         r["ms_forward_16x256"] = e0.elapsed_time(e1) / 5
-    res[m] = r
-    print(m, json.dumps(r), file=sys.stderr, flush=True)
+    res[mk] = r
+    print(mk, json.dumps(r), file=sys.stderr, flush=True)
 print(json.dumps(res, indent=1))
