@@ -239,9 +239,9 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
   }
   const bool stack = L.p.n_w_parts == 2 && g_stack_w;
   if (L.pair && stack)
-    conv3x3_pair_kernel<1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    conv3x3_pair_kernel<1><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   else if (L.pair)
-    conv3x3_pair_kernel<0><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    conv3x3_pair_kernel<0><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   else if (L.n == 64 && stack)
     conv3x3_umma_kernel<64, EPI_STORE16, 1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   else if (L.n == 64)

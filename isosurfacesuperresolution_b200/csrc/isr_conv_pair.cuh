@@ -90,10 +90,19 @@ __device__ __forceinline__ void umma2_commit_multicast(uint32_t bar) {
       : "memory");
 }
 
+// Two epilogue groups of four warps and FOUR accumulator buffers in TMEM: tile i uses buffer i % 4 and is drained by
+// group i % 2 (so a group only ever waits on its own two buffers and observes every phase of their barriers).  With two
+// buffers the epilogue of tile i had to finish within the MMA time of tile i+1 (~1500 cycles) or the issuer stalled;
+// with four it has three tiles' worth of slack while each group still has two tile times per tile.  (Three groups of
+// warps instead -- 448 threads, 128 registers -- spill in the epilogue and run 30 % slower: measured.)
+constexpr int kPairGroups = 2;
+constexpr int kPairBufs = 4;
+constexpr int kPairThreads = (4 * kPairGroups + 2) * 32;
+
 // N = 64 output channels.  Weight rows of one CTA per tap: STACK: 64 (X region: W_hi for the leader, W_lo for the peer)
 // + 32 (Y region: its half of W_hi); otherwise 32 per weight part.
 template <int STACK>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kConvThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const ConvParams p) {
   constexpr int N = 64;
@@ -109,12 +118,14 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t s_wy = s_w + 9 * 2 * kHalfTap;   // STACK: Y region after the X region
   const uint32_t s_stage0 = s_w + ((w_bytes + 1023u) & ~1023u);
   const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
+  constexpr int G = kPairGroups, NB = kPairBufs, kTmaWarp = 4 * G, kMmaWarp = 4 * G + 1;
   const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
-                 b_tempty = s_bar + 152, s_tptr = s_bar + 168;
+                 b_tempty = b_tfull + 8 * NB, s_tptr = b_tempty + 8 * NB;
+  static_assert(136 + 16 * NB + 4 <= 256, "barrier block overflows its 256-byte reservation");
   __shared__ float s_bias[64];
   if (threadIdx.x < 64) s_bias[threadIdx.x] = p.bias != nullptr ? p.bias[threadIdx.x] : 0.f;
 
-  if (warp == 8 && lane == 0) {
+  if (warp == kTmaWarp && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmW);
     for (int s = 0; s < p.num_stages; ++s) {
@@ -122,15 +133,16 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(b_empty + 8 * s, 1);   // per CTA: multicast commit
     }
     mbar_init(b_w, 2);
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < NB; ++a) {
       mbar_init(b_tfull + 8 * a, 1);   // per CTA: multicast commit
       mbar_init(b_tempty + 8 * a, 8);  // leader: 4 epilogue warps x 2 CTAs
     }
     fence_barrier_init();
   }
   constexpr uint32_t kAccCols = STACK ? 2 * N : N;
-  constexpr uint32_t kTmemCols = 2 * kAccCols;
-  if (warp == 9) tmem_alloc2(s_tptr, kTmemCols);
+  constexpr uint32_t kTmemCols = (NB * kAccCols <= 128) ? 128 : ((NB * kAccCols <= 256) ? 256 : 512);
+  static_assert(NB * kAccCols <= 512 && NB % G == 0, "accumulator buffers exceed TMEM");
+  if (warp == kMmaWarp) tmem_alloc2(s_tptr, kTmemCols);
   tc_fence_before();
   cluster_sync_all();   // barriers of both CTAs initialised, TMEM allocated
   tc_fence_after();
@@ -142,7 +154,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int pair_tiles = (p.num_tiles + 1) >> 1;
   const int my_iters = (pair_tiles - pair_id + num_pairs - 1) / num_pairs;
 
-  if (warp == 8) {
+  if (warp == kTmaWarp) {
     // ===================== TMA producer (one per CTA) =====================
     const uint32_t lead_w = mapa_shared(b_w, 0);
     if (elect_one()) {
@@ -181,7 +193,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         __syncwarp();
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == kMmaWarp) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (rank == 0) {
       const uint32_t idesc = make_idesc_f16(256, N, p.is_bf16);
@@ -191,8 +203,8 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_wait(b_w, 0);
       uint32_t it = 0;
       for (int i = 0; i < my_iters; ++i) {
-        const uint32_t acc = i & 1;
-        const uint32_t acc_ph = (i >> 1) & 1;
+        const uint32_t acc = i % NB;
+        const uint32_t acc_ph = (i / NB) & 1;
         if (!(p.dbg & 8)) mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
@@ -235,16 +247,16 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else {
-    // ===================== epilogue warps 0..7: group g = warp/4 drains accumulator buffer g =====================
+    // ===================== epilogue warps: group g = warp/4 drains tiles g, g+G, ... =====================
     const int grp = warp >> 2, q = warp & 3;
-    for (int i = grp; i < my_iters; i += 2) {
+    for (int i = grp; i < my_iters; i += G) {
       const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
       const bool valid = t < p.num_tiles;
       const int tx = t % p.tiles_x;
       const int ty = (t / p.tiles_x) % p.tiles_y;
       const int b = valid ? t / (p.tiles_x * p.tiles_y) : 0;
-      const uint32_t acc = grp;
-      const uint32_t acc_ph = (i >> 1) & 1;
+      const uint32_t acc = i % NB;
+      const uint32_t acc_ph = (i / NB) & 1;
       const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
       epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
       tc_fence_before();
@@ -255,7 +267,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tc_fence_before();
   cluster_sync_all();   // the leader's MMAs read the peer's shared memory: nobody leaves before everything retired
-  if (warp == 9) tmem_dealloc2(tmem_base, kTmemCols);
+  if (warp == kMmaWarp) tmem_dealloc2(tmem_base, kTmemCols);
 }
 
 }  // namespace isr

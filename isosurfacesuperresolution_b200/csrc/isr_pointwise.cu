@@ -45,10 +45,11 @@ __device__ __forceinline__ float lin_m1p1(int i, int n) {
   return fmaf(-step, static_cast<float>(n - 1 - i), 1.f);
 }
 
+// Taps of one grid_sample position.  Out-of-image taps (zeros padding) carry weight 0 and a clamped (always valid)
+// offset, so the gather is branch-free: adding v * 0 leaves the partial sum bit-identical to skipping the tap.
 struct WarpTaps {
   float nw, ne, sw, se;
-  int x0, y0;
-  bool vx0, vx1, vy0, vy1;
+  int o00, o01, o10, o11;   // element offsets inside one H x W plane
 };
 
 // models/videotools.py:65-81: flow*(-2,+2) -> bilinear x r -> + linspace grid -> grid_sample coordinates
@@ -74,31 +75,34 @@ __device__ __forceinline__ WarpTaps warp_taps(const float *__restrict__ flow_b, 
   }
   const float x0f = floorf(ix), y0f = floorf(iy);
   const float x1f = x0f + 1.f, y1f = y0f + 1.f;
-  WarpTaps t;
-  t.nw = (x1f - ix) * (y1f - iy);
-  t.ne = (ix - x0f) * (y1f - iy);
-  t.sw = (x1f - ix) * (iy - y0f);
-  t.se = (ix - x0f) * (iy - y0f);
   const bool okx = (x0f >= -2.f) && (x0f <= static_cast<float>(W) + 1.f);
   const bool oky = (y0f >= -2.f) && (y0f <= static_cast<float>(H) + 1.f);
-  t.x0 = okx ? static_cast<int>(x0f) : -5;
-  t.y0 = oky ? static_cast<int>(y0f) : -5;
-  t.vx0 = t.x0 >= 0 && t.x0 < W;
-  t.vx1 = t.x0 + 1 >= 0 && t.x0 + 1 < W;
-  t.vy0 = t.y0 >= 0 && t.y0 < H;
-  t.vy1 = t.y0 + 1 >= 0 && t.y0 + 1 < H;
+  const int x0 = okx ? static_cast<int>(x0f) : -5;
+  const int y0 = oky ? static_cast<int>(y0f) : -5;
+  const bool vx0 = x0 >= 0 && x0 < W, vx1 = x0 + 1 >= 0 && x0 + 1 < W;
+  const bool vy0 = y0 >= 0 && y0 < H, vy1 = y0 + 1 >= 0 && y0 + 1 < H;
+  WarpTaps t;
+  t.nw = (vy0 && vx0) ? (x1f - ix) * (y1f - iy) : 0.f;
+  t.ne = (vy0 && vx1) ? (ix - x0f) * (y1f - iy) : 0.f;
+  t.sw = (vy1 && vx0) ? (x1f - ix) * (iy - y0f) : 0.f;
+  t.se = (vy1 && vx1) ? (ix - x0f) * (iy - y0f) : 0.f;
+  const int cx0 = min(max(x0, 0), W - 1), cx1 = min(max(x0 + 1, 0), W - 1);
+  const int cy0 = min(max(y0, 0), H - 1) * W, cy1 = min(max(y0 + 1, 0), H - 1) * W;
+  t.o00 = cy0 + cx0; t.o01 = cy0 + cx1; t.o10 = cy1 + cx0; t.o11 = cy1 + cx1;
   return t;
 }
 
 // grid_sample (bilinear, zeros padding) of one channel plane; special mask remap of videotools.py:77-85
 __device__ __forceinline__ float warp_gather(const float *__restrict__ p, int W, const WarpTaps &t, bool sm) {
+  float v00 = __ldg(p + t.o00), v01 = __ldg(p + t.o01), v10 = __ldg(p + t.o10), v11 = __ldg(p + t.o11);
+  if (sm) {
+    v00 = v00 * 0.5f + 0.5f; v01 = v01 * 0.5f + 0.5f; v10 = v10 * 0.5f + 0.5f; v11 = v11 * 0.5f + 0.5f;
+  }
   float acc = 0.f;
-  const float *r0 = p + static_cast<size_t>(t.y0) * W + t.x0;
-  const float *r1 = r0 + W;
-  if (t.vy0 && t.vx0) { float v = __ldg(r0); if (sm) v = v * 0.5f + 0.5f; acc += v * t.nw; }
-  if (t.vy0 && t.vx1) { float v = __ldg(r0 + 1); if (sm) v = v * 0.5f + 0.5f; acc += v * t.ne; }
-  if (t.vy1 && t.vx0) { float v = __ldg(r1); if (sm) v = v * 0.5f + 0.5f; acc += v * t.sw; }
-  if (t.vy1 && t.vx1) { float v = __ldg(r1 + 1); if (sm) v = v * 0.5f + 0.5f; acc += v * t.se; }
+  acc += v00 * t.nw;
+  acc += v01 * t.ne;
+  acc += v10 * t.sw;
+  acc += v11 * t.se;
   if (sm) acc = acc * 2.f - 1.f;
   return acc;
 }
@@ -193,8 +197,31 @@ pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ p
       const int lp = hx >> 2, dx = hx & 3;
       if (flow != nullptr) {
         const WarpTaps t = warp_taps(flow + static_cast<size_t>(b) * 2 * h * w, h, w, 4, Y, X, align_corners);
-        for (int c = 0; c < c_prev; ++c)
-          tile[lp][c_low + c * 16 + dy * 4 + dx] = warp_gather(pb + c * plane, W, t, special_mask && c == 0);
+        // all taps of up to 6 channels are requested before the first use (24 loads in flight per thread): the pass is
+        // bound by gather latency, not by issue slots
+        for (int c0 = 0; c0 < c_prev; c0 += 6) {
+          float v[6][4];
+#pragma unroll
+          for (int c = 0; c < 6; ++c) {
+            const float *pc = pb + static_cast<size_t>(min(c0 + c, c_prev - 1)) * plane;
+            v[c][0] = __ldg(pc + t.o00); v[c][1] = __ldg(pc + t.o01); v[c][2] = __ldg(pc + t.o10); v[c][3] = __ldg(pc + t.o11);
+          }
+#pragma unroll
+          for (int c = 0; c < 6; ++c) {
+            if (c0 + c < c_prev) {
+              const bool sm = special_mask && (c0 + c == 0);
+              float a0 = v[c][0], a1 = v[c][1], a2 = v[c][2], a3 = v[c][3];
+              if (sm) { a0 = a0 * 0.5f + 0.5f; a1 = a1 * 0.5f + 0.5f; a2 = a2 * 0.5f + 0.5f; a3 = a3 * 0.5f + 0.5f; }
+              float acc = 0.f;
+              acc += a0 * t.nw;
+              acc += a1 * t.ne;
+              acc += a2 * t.sw;
+              acc += a3 * t.se;
+              if (sm) acc = acc * 2.f - 1.f;
+              tile[lp][c_low + (c0 + c) * 16 + dy * 4 + dx] = acc;
+            }
+          }
+        }
       } else {
         for (int c = 0; c < c_prev; ++c)
           tile[lp][c_low + c * 16 + dy * 4 + dx] = __ldg(pb + c * plane + static_cast<size_t>(Y) * W + X);
