@@ -172,6 +172,9 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   const size_t avail = kSmemLimit - kStaticSmem - 1024 - w_bytes - 256;
   int stages = static_cast<int>(avail / p.stage_bytes);
   if (stages > 8) stages = 8;
+  // two issuing warps alternate tiles: a stage (and its barriers) must always be consumed by the same warp, or that
+  // warp would skip barrier phases and its parity waits would alias
+  if (L->pair) stages -= stages % (kPairIssuers * n_act_parts);
   if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "conv smem plan: fewer than 2 halo stages fit");
   p.num_stages = stages;
   L->smem = 1024 + w_bytes + static_cast<size_t>(stages) * p.stage_bytes + 256;
@@ -892,6 +895,12 @@ int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scal
   // scale 4: postblock.4 (64->64 at 4h x 4w, the dominant kernel); scale 1: first residual-block conv (h x w)
   ConvLaunch L = pl->convs[scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1)];
   L.p.dbg = g_dbg;
+  unsigned long long *cyc = nullptr;
+  if (g_dbg & 32) {   // bench experiment: cycles of the MMA issue loop (clock64 in the issuing warp)
+    ISR_CUDA(cudaMalloc(&cyc, 256 * sizeof(unsigned long long)));
+    ISR_CUDA(cudaMemset(cyc, 0, 256 * sizeof(unsigned long long)));
+    L.p.dbg_cycles = cyc;
+  }
   cudaEvent_t e0, e1;
   ISR_CUDA(cudaEventCreate(&e0));
   ISR_CUDA(cudaEventCreate(&e1));
@@ -906,6 +915,17 @@ int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scal
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   *ms = t / iters;
+  if (cyc != nullptr) {
+    unsigned long long hc[256];
+    ISR_CUDA(cudaMemcpy(hc, cyc, sizeof hc, cudaMemcpyDeviceToHost));
+    cudaFree(cyc);
+    unsigned long long mx = 0, sum = 0; int n = 0;
+    for (int i = 0; i < 128; ++i) if (hc[i]) { mx = hc[i] > mx ? hc[i] : mx; sum += hc[i]; ++n; }
+    const double mmas = static_cast<double>((L.p.num_tiles + 1) / 2) / (L.grid / 2) * 36.0 * (L.p.n_act_parts == 2 ? 2.0 : 1.0);
+    fprintf(stderr, "[isr dbg] MMA loop cycles: max %llu avg %.0f over %d pairs; %.1f cycles per k64-tap MMA group/4 (=per MMA) ; kernel %.1f us => %.0f MHz\n",
+            mx, n ? static_cast<double>(sum) / n : 0.0, n, n ? static_cast<double>(sum) / n / mmas : 0.0, t / iters * 1e3,
+            mx / (t / iters * 1e3));
+  }
   return ISR_OK;
 }
 

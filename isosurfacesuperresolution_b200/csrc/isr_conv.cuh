@@ -43,7 +43,9 @@ struct ConvParams {
   int w_row_stride;      // rows between consecutive (part, tap) blocks
   int num_stages, stage_bytes;
   int dbg;               // bench experiments only: bit0 = epilogue does not store, bit1 = no MMAs are issued,
-                         // bit2 = epilogue only does the barrier handshake, bit3 = MMA warp does not wait for the epilogue
+                         // bit2 = epilogue only does the barrier handshake, bit3 = MMA warp does not wait for the epilogue,
+                         // bit4 = the TMA producer fills each halo stage once and only signals afterwards (pair kernel)
+  unsigned long long *dbg_cycles;   // bench experiment (dbg bit5): cycles spent in the MMA issue loop, per CTA pair
   int relu;
   const float *bias;     // N floats (zero padded), or nullptr
   const uint16_t *addend;  // [B,H,W,64*add_parts] or nullptr
@@ -121,7 +123,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
         }
       }
     }
-    mbar_wait(b_tfull + 8 * acc, acc_ph);
+    mbar_wait_parked(b_tfull + 8 * acc, acc_ph);
     tc_fence_after();
     if (p.dbg & 4) return;   // bench experiment: barrier handshake only
 #pragma unroll

@@ -97,7 +97,8 @@ __device__ __forceinline__ void umma2_commit_multicast(uint32_t bar) {
 // warps instead -- 448 threads, 128 registers -- spill in the epilogue and run 30 % slower: measured.)
 constexpr int kPairGroups = 2;
 constexpr int kPairBufs = 4;
-constexpr int kPairThreads = (4 * kPairGroups + 2) * 32;
+constexpr int kPairIssuers = 2;   // MMA-issuing warps (leader CTA), see the issuer section of the kernel
+constexpr int kPairThreads = (4 * kPairGroups + 1 + kPairIssuers) * 32;
 
 // N = 64 output channels.  Weight rows of one CTA per tap: STACK: 64 (X region: W_hi for the leader, W_lo for the peer)
 // + 32 (Y region: its half of W_hi); otherwise 32 per weight part.
@@ -184,32 +185,44 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
         const uint32_t s = it % p.num_stages;
         const uint32_t ph = (it / p.num_stages) & 1;
-        mbar_wait(b_empty + 8 * s, ph ^ 1);
+        mbar_wait_parked(b_empty + 8 * s, ph ^ 1);
         if (elect_one()) {
           const uint32_t lead_full = mapa_shared(b_full + 8 * s, 0);
-          mbar_arrive_expect_tx_cluster(lead_full, kPitch * kHaloH * 128);
-          tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA, lead_full, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
+          if ((p.dbg & 16) && it >= static_cast<uint32_t>(p.num_stages)) {   // bench experiment: stages are filled once
+            mbar_arrive_cluster(lead_full);
+          } else {
+            mbar_arrive_expect_tx_cluster(lead_full, kPitch * kHaloH * 128);
+            tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA, lead_full, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
+          }
         }
         __syncwarp();
       }
     }
-  } else if (warp == kMmaWarp) {
-    // ===================== MMA issuer (leader CTA only) =====================
+  } else if (warp >= kMmaWarp) {
+    // ===================== MMA issuers (leader CTA only): TWO warps, warp m issues tiles m, m+2, ... =================
+    // The tcgen05.mma queue is shallow: whatever the issuing thread does between the last MMA of a tile and the first of
+    // the next (barrier waits, commits, index arithmetic) is a tensor-pipe bubble -- measured 49.8 cycles per MMA in this
+    // loop against 43.0 for back-to-back issue (tools/probe_mma3.cu), and moving the waits into the middle of a tile made
+    // it worse (58.8).  With two issuing warps one of them always has MMAs to feed while the other does its per-tile
+    // bookkeeping; tiles alternate, accumulators and halo stages are barrier-protected per tile, and a tcgen05.commit
+    // tracks the MMAs of the issuing thread, i.e. of that warp's own tile.
     if (rank == 0) {
+      const int mw = warp - kMmaWarp;
       const uint32_t idesc = make_idesc_f16(256, N, p.is_bf16);
       const uint32_t idesc2 = make_idesc_f16(256, 2 * N, p.is_bf16);
       const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
       const uint64_t by_desc_base = make_smem_desc_sw128(s_wy, 1024, 0);
       mbar_wait(b_w, 0);
-      uint32_t it = 0;
-      for (int i = 0; i < my_iters; ++i) {
+      const long long c_start = clock64();
+      for (int i = mw; i < my_iters; i += kPairIssuers) {
         const uint32_t acc = i % NB;
         const uint32_t acc_ph = (i / NB) & 1;
         if (!(p.dbg & 8)) mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
         uint32_t first = 1;
-        for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+        for (int ap = 0; ap < p.n_act_parts; ++ap) {
+          const uint32_t it = static_cast<uint32_t>(i) * p.n_act_parts + ap;
           const uint32_t s = it % p.num_stages;
           const uint32_t ph = (it / p.num_stages) & 1;
           mbar_wait(b_full + 8 * s, ph);
@@ -244,6 +257,12 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           __syncwarp();
           first = 0;
         }
+      }
+      if (p.dbg_cycles != nullptr && lane == 0 && my_iters > 0) {
+        // wait for this warp's last accumulator so the count covers the execution of its MMAs
+        const int last = ((my_iters - 1 - mw) / kPairIssuers) * kPairIssuers + mw;
+        if (last >= 0 && last < my_iters) mbar_wait(b_tfull + 8 * (last % NB), (last / NB) & 1);
+        p.dbg_cycles[pair_id + 128 * mw] = static_cast<unsigned long long>(clock64() - c_start);
       }
     }
   } else {

@@ -54,6 +54,25 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   __trap();
 }
 
+// Wait of a warp that is NOT on the MMA-issue critical path (epilogue, TMA producer).  The N <= 64 MMAs are bound by
+// shared-memory operand reads, and every failed try_wait is a shared-memory access that takes a slot from them
+// (measured: 49.8 instead of 43.0 cycles per MMA with nine warps polling).  The suspend-time hint parks the warp in
+// hardware until the phase completes instead of re-polling.
+__device__ __forceinline__ void mbar_wait_parked(uint32_t bar, uint32_t parity) {
+  for (uint32_t spin = 0; spin < (1u << 20); ++spin) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(4000u)
+        : "memory");
+    if (ok) return;
+  }
+  __trap();
+}
+
 // ---- TMA --------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const void *tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
