@@ -104,7 +104,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
     for (int j = 0; j < 16; ++j) bias_r[j] = s_bias[16 * m + j];
     // residual addend (the block's skip): fetched BEFORE waiting for the accumulator, so its HBM latency hides
     // behind the tile's MMAs.  ad[pixel j = 2*half+hh][part][2 x 16 B]
-    uint4 ad[4][2][2];
+    uint32_t ad[4][2][8];
     const bool has_add = p.addend != nullptr;
     if (has_add) {
 #pragma unroll
@@ -114,12 +114,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
         const size_t pix = (static_cast<size_t>(b) * p.H + (ok ? y : 0)) * p.W + (ok ? x : 0);
 #pragma unroll
         for (int ap = 0; ap < 2; ++ap) {
-          if (ap < p.add_parts) {
-            const uint4 *src =
-                reinterpret_cast<const uint4 *>(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m);
-            ad[j][ap][0] = __ldg(src);
-            ad[j][ap][1] = __ldg(src + 1);
-          }
+          if (ap < p.add_parts) ldg_v8(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m, ad[j][ap]);
         }
       }
     }
@@ -154,8 +149,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
 #pragma unroll
             for (int ap = 0; ap < 2; ++ap) {
               if (ap < p.add_parts) {
-                const uint4 q0 = ad[2 * half + hh][ap][0], q1 = ad[2 * half + hh][ap][1];
-                const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+                const uint32_t *w = ad[2 * half + hh][ap];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                   const float2 a = unpack2(w[j], p.is_bf16);
@@ -172,9 +166,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
           uint32_t hi[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
-          uint4 *dst = reinterpret_cast<uint4 *>(p.out16 + pix * (64 * p.out_parts) + 16 * m);
-          dst[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-          dst[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+          st_global_v8(p.out16 + pix * (64 * p.out_parts) + 16 * m, hi);
           if (p.out_parts == 2) {
             uint32_t lo[8];
 #pragma unroll
@@ -182,9 +174,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
               const float2 h = unpack2(hi[j], p.is_bf16);
               lo[j] = pack2(f[2 * j] - h.x, f[2 * j + 1] - h.y, p.is_bf16);
             }
-            uint4 *dl = reinterpret_cast<uint4 *>(p.out16 + pix * 128 + 64 + 16 * m);
-            dl[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-            dl[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            st_global_v8(p.out16 + pix * 128 + 64 + 16 * m, lo);
           }
         }
       }

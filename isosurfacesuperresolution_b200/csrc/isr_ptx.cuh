@@ -73,6 +73,19 @@ __device__ __forceinline__ void mbar_wait_parked(uint32_t bar, uint32_t parity) 
   __trap();
 }
 
+// ---- 256-bit global accesses (sm_100: LDG/STG.256) ---------------------------------------------------------
+// One instruction per 32-byte sector: the NHWC epilogues leave 16 consecutive 16-bit channels (32 B) in a thread.
+__device__ __forceinline__ void st_global_v8(void *dst, const uint32_t *v) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "r"(v[0]), "r"(v[1]), "r"(v[2]),
+               "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+__device__ __forceinline__ void ldg_v8(const void *src, uint32_t *v) {
+  asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "l"(src));
+}
+
 // ---- TMA --------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void tma_prefetch_desc(const void *tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
