@@ -27,7 +27,8 @@ static int g_base_offset_mode = 0;
 static int g_max_ctas = 0;
 static int g_dbg = 0;             // ConvParams::dbg of isr_net_time_conv launches (bench experiments)
 static int g_cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta_group::2, isr_conv_pair.cuh)
-static int g_final_stacked = 1;   // output conv: tap-stacked kernel (isr_conv_final.cuh) when Cout <= 8
+static int g_final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (measured slower: 1.24 vs 0.92 ms), 1 = tap-stacked kernel (isr_conv_final.cuh, Cout <= 8),
+                                  // 0 = generic single-CTA N=16 kernel
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
 static int g_trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
 
@@ -137,6 +138,10 @@ static int setup_kernel_attrs() {
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0, 16, EPI_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<1, 16, EPI_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -163,7 +168,7 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   p.is_bf16 = is_bf16;
   p.w_row0 = w_row0;
   p.w_row_stride = w_row_stride;
-  L->pair = (n == 64 && g_cta_pair) ? 1 : 0;
+  L->pair = ((n == 64 && g_cta_pair) || (n == 16 && g_final_stacked == 2)) ? 1 : 0;
   const bool stack = n_w_parts == 2 && g_stack_w;
   // weight bytes per CTA: the pair kernel keeps half of the B operand per CTA (+ its half of W_hi when stacked)
   size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * 9 * n * 128, 1024);
@@ -241,7 +246,11 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     return ISR_OK;
   }
   const bool stack = L.p.n_w_parts == 2 && g_stack_w;
-  if (L.pair && stack)
+  if (L.pair && L.n == 16 && stack)
+    conv3x3_pair_kernel<1, 16, EPI_FINAL><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+  else if (L.pair && L.n == 16)
+    conv3x3_pair_kernel<0, 16, EPI_FINAL><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
+  else if (L.pair && stack)
     conv3x3_pair_kernel<1><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   else if (L.pair)
     conv3x3_pair_kernel<0><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
@@ -436,7 +445,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->idx_final = static_cast<int>(pl->convs.size());
   Scheme Fs = Hs;
   if (pl->fin_nw > 0) Fs.nw = pl->fin_nw;
-  if (net->layers[24].packed_fin != nullptr && g_final_stacked) {
+  if (net->layers[24].packed_fin != nullptr && g_final_stacked == 1) {
     const int cp = final_cp(net->cout), nrows = final_rows(cp);
     const uint16_t *wb = net->layers[24].packed_fin + (Fs.bf16 ? 0 : static_cast<size_t>(2) * nrows * 64);
     if ((rc = init_conv_final(&L, cp, pl->u4, B, 4 * h, 4 * w, Fs.na, wb, Fs.nw, Fs.bf16)) != ISR_OK) return rc;
@@ -546,7 +555,7 @@ int isr_set_tunable(const char *key, int value) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "cta_pair must be 0 or 1");
     slot = &g_cta_pair;
   } else if (key != nullptr && strcmp(key, "final_stacked") == 0) {
-    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "final_stacked must be 0 or 1");
+    if (value < 0 || value > 2) return fail(ISR_ERR_ARG, "final_stacked must be 0 (generic), 1 (tap-stacked) or 2 (CTA pair)");
     slot = &g_final_stacked;
   } else if (key != nullptr && strcmp(key, "trunk_full_blocks") == 0) {
     if (value < 0 || value > 10) return fail(ISR_ERR_ARG, "trunk_full_blocks must be in [0, 10]");

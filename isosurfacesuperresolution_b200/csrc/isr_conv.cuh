@@ -181,6 +181,105 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
     }
 }
 
+// Epilogue of the output conv (Cout <= 16) for one 8x16 tile: raw = acc + bias; recon = raw + upsampled skip
+// (enhancenet.py:51-90); optional recurrent state (mainVideoUnshaded.py:460-465).  thread = GEMM row (32x32b load):
+// pixel (py, px) = (row/8, row%8); NCHW fp32 planes, 8 px = one 32 B sector.  Shared by the single-CTA and the CTA-pair
+// kernel.
+template <int N, int STACK>
+__device__ __forceinline__ void epilogue_final(const ConvParams &p, const float *s_bias, uint32_t taddr, int q, int lane,
+                                               int b, int ty, int tx, bool tile_valid, uint32_t bar_tfull,
+                                               uint32_t acc_ph) {
+  const int row = q * 32 + lane;
+  const int y = ty * kTileH + (row >> 3), x = tx * kTileW + (row & 7);
+  const bool inb = tile_valid && (y < p.H) && (x < p.W);
+  // the skip taps do not depend on the accumulator: fetch them before waiting for the MMAs
+  constexpr int kSkipPrefetch = 8;
+  float sk[kSkipPrefetch];
+#pragma unroll
+  for (int c = 0; c < kSkipPrefetch; ++c) sk[c] = 0.f;
+  if (inb && p.recon_residual) {
+    int x0, x1, y0, y1;
+    float lx0, lx1, ly0, ly1;
+    if (p.upsample == 1) {
+      bil_src(x, p.w_low, 0.25f, x0, x1, lx0, lx1);
+      bil_src(y, p.h_low, 0.25f, y0, y1, ly0, ly1);
+    } else {
+      x0 = x1 = x >> 2;
+      y0 = y1 = y >> 2;
+      lx0 = ly0 = 1.f;
+      lx1 = ly1 = 0.f;
+    }
+    // all taps of all channels are issued before the first use (no per-channel branch)
+    const int o00 = y0 * p.w_low + x0, o01 = y0 * p.w_low + x1, o10 = y1 * p.w_low + x0, o11 = y1 * p.w_low + x1;
+    const int nm = p.n_mask > 0 ? p.n_mask : 1;
+    float t00[kSkipPrefetch], t01[kSkipPrefetch], t10[kSkipPrefetch], t11[kSkipPrefetch];
+#pragma unroll
+    for (int c = 0; c < kSkipPrefetch; ++c) {
+      const int cc = c < nm ? c : nm - 1;
+      const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(cc) * p.h_low * p.w_low;
+      t00[c] = __ldg(sp + o00);
+      t01[c] = __ldg(sp + o01);
+      t10[c] = __ldg(sp + o10);
+      t11[c] = __ldg(sp + o11);
+    }
+#pragma unroll
+    for (int c = 0; c < kSkipPrefetch; ++c) {
+      const float r0 = fmaf(lx0, t00[c], lx1 * t01[c]);
+      const float r1 = fmaf(lx0, t10[c], lx1 * t11[c]);
+      const float v = p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00[c];
+      sk[c] = c < p.n_mask ? v : 0.f;
+    }
+  }
+  mbar_wait_parked(bar_tfull, acc_ph);
+  tc_fence_after();
+  uint32_t v[16];
+  tmem_ld16(taddr, v);
+  if constexpr (STACK) {   // columns 16..31 hold A x W_lo^T
+    uint32_t v2[16];
+    tmem_ld16(taddr + N, v2);
+    tmem_ld_wait();
+#pragma unroll
+    for (int c = 0; c < 16; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
+  } else {
+    tmem_ld_wait();
+  }
+  if (inb) {
+    const size_t plane = static_cast<size_t>(p.H) * p.W;
+    const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;
+    float rec[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      rec[c] = 0.f;
+      if (c < p.cout) {
+        const float raw = __uint_as_float(v[c]) + s_bias[c];
+        if (p.out_raw != nullptr) p.out_raw[o0 + c * plane] = raw;
+        float r = raw;
+        if (p.recon_residual && c < p.n_mask && c < kSkipPrefetch) r = sk[c < kSkipPrefetch ? c : 0] + raw;
+        rec[c] = r;
+        if (p.out_recon != nullptr) p.out_recon[o0 + c * plane] = r;
+      }
+    }
+    if (p.out_state != nullptr) {
+      if (p.state_unshaded && p.cout >= 5) {
+        // mainVideoUnshaded.py:460-465: clamp mask, normalise normal (shading.py:193-207), clamp depth / ao
+        p.out_state[o0] = fminf(fmaxf(rec[0], -1.f), 1.f);
+        float len = sqrtf(rec[1] * rec[1] + rec[2] * rec[2] + rec[3] * rec[3]);
+        len = fmaxf(len, 1e-7f);
+        p.out_state[o0 + plane] = rec[1] / len;
+        p.out_state[o0 + 2 * plane] = rec[2] / len;
+        p.out_state[o0 + 3 * plane] = rec[3] / len;
+#pragma unroll
+        for (int c = 4; c < 16; ++c)
+          if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+          if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+      }
+    }
+  }
+}
+
 // STACK = 1 (split precision, N = 64 only): the hi and lo weight planes of a tap sit back to back in shared memory and
 // are ONE N=128 B operand, so A_hi*W_hi^T and A_hi*W_lo^T are a single M128xN128 MMA (67.7 cycles measured) instead of two
 // N=64 MMAs (2 x 53.9, profiles/r01_probe_mma_cycles.json); the epilogue adds accumulator columns c and 64+c.
@@ -323,97 +422,7 @@ conv3x3_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if constexpr (EPI == EPI_STORE16) {
         epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, true, b_tfull + 8 * acc, acc_ph);
       } else {
-        // final conv: raw = acc + bias; recon = raw + upsampled skip (enhancenet.py:51-90); optional recurrent state.
-        // thread = GEMM row (32x32b load): pixel (py, px) = (row/8, row%8); NCHW fp32 planes, 8 px = one 32 B sector.
-        const int row = q * 32 + lane;
-        const int y = ty * kTileH + (row >> 3), x = tx * kTileW + (row & 7);
-        const bool inb = (y < p.H) && (x < p.W);
-        // the skip taps do not depend on the accumulator: fetch them before waiting for the MMAs
-        constexpr int kSkipPrefetch = 8;
-        float sk[kSkipPrefetch];
-#pragma unroll
-        for (int c = 0; c < kSkipPrefetch; ++c) sk[c] = 0.f;
-        if (inb && p.recon_residual) {
-          int x0, x1, y0, y1;
-          float lx0, lx1, ly0, ly1;
-          if (p.upsample == 1) {
-            bil_src(x, p.w_low, 0.25f, x0, x1, lx0, lx1);
-            bil_src(y, p.h_low, 0.25f, y0, y1, ly0, ly1);
-          } else {
-            x0 = x1 = x >> 2;
-            y0 = y1 = y >> 2;
-            lx0 = ly0 = 1.f;
-            lx1 = ly1 = 0.f;
-          }
-          // all taps of all channels are issued before the first use (no per-channel branch)
-          const int o00 = y0 * p.w_low + x0, o01 = y0 * p.w_low + x1, o10 = y1 * p.w_low + x0, o11 = y1 * p.w_low + x1;
-          const int nm = p.n_mask > 0 ? p.n_mask : 1;
-          float t00[kSkipPrefetch], t01[kSkipPrefetch], t10[kSkipPrefetch], t11[kSkipPrefetch];
-#pragma unroll
-          for (int c = 0; c < kSkipPrefetch; ++c) {
-            const int cc = c < nm ? c : nm - 1;
-            const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(cc) * p.h_low * p.w_low;
-            t00[c] = __ldg(sp + o00);
-            t01[c] = __ldg(sp + o01);
-            t10[c] = __ldg(sp + o10);
-            t11[c] = __ldg(sp + o11);
-          }
-#pragma unroll
-          for (int c = 0; c < kSkipPrefetch; ++c) {
-            const float r0 = fmaf(lx0, t00[c], lx1 * t01[c]);
-            const float r1 = fmaf(lx0, t10[c], lx1 * t11[c]);
-            const float v = p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00[c];
-            sk[c] = c < p.n_mask ? v : 0.f;
-          }
-        }
-        mbar_wait(b_tfull + 8 * acc, acc_ph);
-        tc_fence_after();
-        uint32_t v[16];
-        tmem_ld16(taddr, v);
-        if constexpr (STACK) {   // columns 16..31 hold A x W_lo^T
-          uint32_t v2[16];
-          tmem_ld16(taddr + N, v2);
-          tmem_ld_wait();
-#pragma unroll
-          for (int c = 0; c < 16; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + __uint_as_float(v2[c]));
-        } else {
-          tmem_ld_wait();
-        }
-        if (inb) {
-          const size_t plane = static_cast<size_t>(p.H) * p.W;
-          const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;
-          float rec[16];
-#pragma unroll
-          for (int c = 0; c < 16; ++c) {
-            rec[c] = 0.f;
-            if (c < p.cout) {
-              const float raw = __uint_as_float(v[c]) + s_bias[c];
-              if (p.out_raw != nullptr) p.out_raw[o0 + c * plane] = raw;
-              float r = raw;
-              if (p.recon_residual && c < p.n_mask && c < kSkipPrefetch) r = sk[c < kSkipPrefetch ? c : 0] + raw;
-              rec[c] = r;
-              if (p.out_recon != nullptr) p.out_recon[o0 + c * plane] = r;
-            }
-          }
-          if (p.out_state != nullptr) {
-            if (p.state_unshaded && p.cout >= 5) {
-              // mainVideoUnshaded.py:460-465: clamp mask, normalise normal (shading.py:193-207), clamp depth / ao
-              p.out_state[o0] = fminf(fmaxf(rec[0], -1.f), 1.f);
-              float len = sqrtf(rec[1] * rec[1] + rec[2] * rec[2] + rec[3] * rec[3]);
-              len = fmaxf(len, 1e-7f);
-              p.out_state[o0 + plane] = rec[1] / len;
-              p.out_state[o0 + 2 * plane] = rec[2] / len;
-              p.out_state[o0 + 3 * plane] = rec[3] / len;
-#pragma unroll
-              for (int c = 4; c < 16; ++c)
-                if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
-            } else {
-#pragma unroll
-              for (int c = 0; c < 16; ++c)
-                if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
-            }
-          }
-        }
+        epilogue_final<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, true, b_tfull + 8 * acc, acc_ph);
       }
       tc_fence_before();
       __syncwarp();

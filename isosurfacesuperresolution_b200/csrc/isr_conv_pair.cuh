@@ -102,11 +102,13 @@ constexpr int kPairThreads = (4 * kPairGroups + 1 + kPairIssuers) * 32;
 
 // N = 64 output channels.  Weight rows of one CTA per tap: STACK: 64 (X region: W_hi for the leader, W_lo for the peer)
 // + 32 (Y region: its half of W_hi); otherwise 32 per weight part.
-template <int STACK>
+// N = 16 with EPI_FINAL: the network's output conv (Cout <= 16) with its fused skip / state epilogue; an N = 16 pair-MMA
+// costs 39 cycles, and the epilogue is a plain TMEM row load (no shared-memory gather as in isr_conv_final.cuh).
+template <int STACK, int N = 64, int EPI = EPI_STORE16>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const ConvParams p) {
-  constexpr int N = 64;
+  static_assert(N == 64 || N == 16, "N = 64 (hidden layers) or 16 (output conv)");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5;
@@ -124,7 +126,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                  b_tempty = b_tfull + 8 * NB, s_tptr = b_tempty + 8 * NB;
   static_assert(136 + 16 * NB + 4 <= 256, "barrier block overflows its 256-byte reservation");
   __shared__ float s_bias[64];
-  if (threadIdx.x < 64) s_bias[threadIdx.x] = p.bias != nullptr ? p.bias[threadIdx.x] : 0.f;
+  if (threadIdx.x < 64) s_bias[threadIdx.x] = (p.bias != nullptr && threadIdx.x < N) ? p.bias[threadIdx.x] : 0.f;
 
   if (warp == kTmaWarp && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -141,7 +143,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_barrier_init();
   }
   constexpr uint32_t kAccCols = STACK ? 2 * N : N;
-  constexpr uint32_t kTmemCols = (NB * kAccCols <= 128) ? 128 : ((NB * kAccCols <= 256) ? 256 : 512);
+  constexpr uint32_t kTmemCols = (NB * kAccCols <= 64) ? 64 : (NB * kAccCols <= 128) ? 128 : ((NB * kAccCols <= 256) ? 256 : 512);
   static_assert(NB * kAccCols <= 512 && NB % G == 0, "accumulator buffers exceed TMEM");
   if (warp == kMmaWarp) tmem_alloc2(s_tptr, kTmemCols);
   tc_fence_before();
@@ -277,7 +279,10 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t acc = i % NB;
       const uint32_t acc_ph = (i / NB) & 1;
       const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
-      epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
+      if constexpr (EPI == EPI_STORE16)
+        epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
+      else
+        epilogue_final<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_shared(b_tempty + 8 * acc, 0));

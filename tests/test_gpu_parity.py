@@ -302,7 +302,7 @@ def test_output_conv_tap_stacked_equals_generic(isr, golden, weights, prec):
     x = cu(g["x"])
     outs = {}
     try:
-        for fin, stk in ((1, 1), (0, 1), (1, 0), (0, 0)):
+        for fin, stk in ((2, 1), (2, 0), (1, 1), (0, 1), (1, 0), (0, 0)):
             _lib.set_tunable("final_stacked", fin)
             _lib.set_tunable("stack_w", stk)
             net = _net(isr, weights)
@@ -314,6 +314,8 @@ def test_output_conv_tap_stacked_equals_generic(isr, golden, weights, prec):
         _lib.set_tunable("stack_w", 1)
     # tap-stacked vs generic output conv: same products, different fp32 summation order
     assert maxabs(outs[(1, 1)], outs[(0, 1)]) <= 5e-5 and maxabs(outs[(1, 0)], outs[(0, 0)]) <= 5e-5
+    # CTA-pair output conv (tunable final_stacked=2) vs the generic single-CTA kernel
+    assert maxabs(outs[(2, 1)], outs[(0, 1)]) <= 5e-5 and maxabs(outs[(2, 0)], outs[(0, 0)]) <= 5e-5
     # hi/lo weight stacking moves the small hi*lo products into their own accumulator columns; the tensor core's fp32
     # accumulation is not order-independent at the 1e-4 level (measured 1.2e-4 in bf16x3, the stacked form being the
     # closer one to the fp32 reference), and in `mixed` the fp16 tail re-quantises that difference to its own noise level
