@@ -11,7 +11,9 @@ $(CSRC)/isr_api.o: $(CSRC)/isr_api.cu $(CSRC)/isr_conv.cuh $(CSRC)/isr_conv_fina
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(CSRC)/isr_pointwise.o: $(CSRC)/isr_pointwise.cu $(CSRC)/isr_internal.h
 	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
-$(LIB): $(CSRC)/isr_api.o $(CSRC)/isr_pointwise.o
+$(CSRC)/isr_ingest.o: $(CSRC)/isr_ingest.cu $(CSRC)/isr_internal.h
+	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
+$(LIB): $(CSRC)/isr_api.o $(CSRC)/isr_pointwise.o $(CSRC)/isr_ingest.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart static
 oracle:
 	$(MAKE) -C oracle -s

@@ -98,6 +98,33 @@ int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, in
 int isr_compose(const float *low, const float *pred, const float *params_host, float *out, int B, int c_low, int c_pred,
                 int h, int w, int unshaded, int masking, float background0, void *stream);
 
+/* ---- in front of the network on the interactive path ---------------------------- */
+
+/* G-buffer ingest.  render: the renderer's frame, interleaved != 0: B x h x w x c_render (the wire format of
+ * GPURendererDirect/render_kernel.cu:254-265: RGB, mask, nx, ny, nz, depth, flow_x, flow_y, AO, shadow; c_render = 12),
+ * interleaved == 0: planar B x c_render x h x w (the tensor inference/loadedmodel.py:70 receives).  One pass writes
+ *   low     B x c_low x h x w: the network input slice of loadedmodel.py:84-105.  variant 0 (unshaded): mask*2-1,
+ *           normal, depth (5); 1: RGB, mask (4); 2: + depth (5); 3: + normal (7); 4: clamp(channels 0:8, 0, 1) (8);
+ *   flow    B x 2 x h x w: channels 8:10 (raw, holes not filled);
+ *   hole    B x h x w bytes: 1 where mask == 0 (the in-painting mask of loadedmodel.py:80);
+ *   image12 B x 12 x h x w planar copy with the mask moved to [-1, 1] (mainGUI.py:713-716).
+ * Any output may be NULL. */
+int isr_ingest_gbuffer(const float *render, int interleaved, int B, int c_render, int h, int w, int variant, float *low,
+                       float *flow, unsigned char *hole, float *image12, void *stream);
+/* channels of `low` for a variant (5, 4, 5, 7, 8), or ISR_ERR_ARG */
+int isr_ingest_low_channels(int variant);
+
+/* Flow in-painting on the device, replacing cv.inpaint(flow, mask == 0, 3, INPAINT_NS) of loadedmodel.py:77-82 (no
+ * GPU -> CPU -> GPU round trip).  Push-pull pyramid: valid pixels keep their value exactly; a hole takes the bilinear
+ * sample of the next coarser level, whose pixels are the means of their valid children.  Not OpenCV's algorithm: the
+ * fill is an average of valid neighbours at the scale of the hole: identical to OpenCV's on constant fields, inside
+ * the range of the valid flow always, and within 10 % of the flow range of OpenCV's for silhouette-sized holes
+ * (tests/test_ingest_oracle.py); arithmetic restated in oracle/oracle.py::inpaint_flow_pushpull.
+ * flow, out: B x 2 x h x w; hole: B x h x w bytes; workspace: isr_inpaint_workspace_bytes, 16-byte aligned. */
+int isr_inpaint_workspace_bytes(int B, int h, int w, size_t *bytes);
+int isr_inpaint_flow(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, void *workspace,
+                     size_t workspace_bytes, void *stream);
+
 /* ---- EnhanceNet generator (models/enhancenet.py:8-26,92-145) ------------------------------------------- */
 
 typedef struct isr_net isr_net;

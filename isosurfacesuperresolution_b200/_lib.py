@@ -39,6 +39,10 @@ SIGNATURES = {
     "isr_postprocess": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "isr_shade": (_i, [_vp, _c.POINTER(_c.c_float), _vp, _i, _i, _i, _i, _vp]),
     "isr_compose": (_i, [_vp, _vp, _c.POINTER(_c.c_float), _vp, _i, _i, _i, _i, _i, _i, _i, _c.c_float, _vp]),
+    "isr_ingest_gbuffer": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "isr_ingest_low_channels": (_i, [_i]),
+    "isr_inpaint_workspace_bytes": (_i, [_i, _i, _i, _c.POINTER(_sz)]),
+    "isr_inpaint_flow": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "isr_net_create": (_i, [_c.POINTER(_vp), _i, _i, _i, _i, _i]),
     "isr_net_destroy": (None, [_vp]),
     "isr_net_load_weights": (_i, [_vp, _c.POINTER(_vp), _i, _vp]),

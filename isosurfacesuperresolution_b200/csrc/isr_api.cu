@@ -637,6 +637,41 @@ int isr_compose(const float *low, const float *pred, const float *params_host, f
   return ISR_OK;
 }
 
+int isr_ingest_low_channels(int variant) {
+  if (variant < 0 || variant > 4) return fail(ISR_ERR_ARG, "ingest: unknown variant %d", variant);
+  return ingest_low_channels(variant);
+}
+
+int isr_ingest_gbuffer(const float *render, int interleaved, int B, int c_render, int h, int w, int variant, float *low,
+                       float *flow, unsigned char *hole, float *image12, void *stream) {
+  if (render == nullptr || B <= 0 || h <= 0 || w <= 0) return fail(ISR_ERR_ARG, "ingest: bad arguments");
+  if (variant < 0 || variant > 4) return fail(ISR_ERR_ARG, "ingest: unknown variant %d", variant);
+  if (c_render < 10 || (image12 != nullptr && c_render < 12))
+    return fail(ISR_ERR_ARG, "ingest: the render needs >= 10 channels (RGB, mask, normal, depth, flow), 12 for image12");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_ingest(render, interleaved, c_render, low, flow, hole, image12, B, h, w, variant, S(stream)));
+  return ISR_OK;
+}
+
+int isr_inpaint_workspace_bytes(int B, int h, int w, size_t *bytes) {
+  if (bytes == nullptr || B <= 0 || h <= 0 || w <= 0) return fail(ISR_ERR_ARG, "inpaint workspace: bad arguments");
+  *bytes = inpaint_workspace_floats(B, h, w) * sizeof(float);
+  return ISR_OK;
+}
+
+int isr_inpaint_flow(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, void *workspace,
+                     size_t workspace_bytes, void *stream) {
+  if (flow == nullptr || hole == nullptr || out == nullptr || workspace == nullptr || B <= 0 || h <= 0 || w <= 0)
+    return fail(ISR_ERR_ARG, "inpaint_flow: bad arguments");
+  const size_t need = inpaint_workspace_floats(B, h, w) * sizeof(float);
+  if (workspace_bytes < need) return fail(ISR_ERR_WORKSPACE, "inpaint_flow: workspace too small (%zu < %zu)", workspace_bytes, need);
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_inpaint_flow(flow, hole, out, B, h, w, static_cast<float *>(workspace), S(stream)));
+  return ISR_OK;
+}
+
 int isr_net_create(isr_net **out, int input_channels, int output_channels, int n_mask, int upsample,
                    int recon_residual) {
   if (out == nullptr) return fail(ISR_ERR_ARG, "net_create: null output");

@@ -31,4 +31,12 @@ cudaError_t launch_pack_weights(const float *w, uint16_t *out, int cout, int cin
 // tap-stacked output-conv weights: [fmt 2][part 2][nrows (n = tap*cp + co)][64]
 cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s);
 
+// isr_ingest.cu
+int ingest_low_channels(int variant);
+cudaError_t launch_ingest(const float *render, int interleaved, int c_render, float *low, float *flow,
+                          unsigned char *hole, float *image12, int B, int h, int w, int variant, cudaStream_t s);
+size_t inpaint_workspace_floats(int B, int h, int w);
+cudaError_t launch_inpaint_flow(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, float *ws,
+                                cudaStream_t s);
+
 }  // namespace isr

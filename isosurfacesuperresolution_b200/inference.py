@@ -68,7 +68,7 @@ class LoadedModel:
     @staticmethod
     def _inpaint_flow(current_low):
         """loadedmodel.py:77-82: Navier-Stokes in-painting of the flow where mask == 0, on the host (OpenCV), as the
-        reference does.  (A GPU in-painter is SURVEY.md section 8f rank 1 -- not built yet.)"""
+        reference does.  The device replacement is ops.inpaint_flow (inference(..., inpaint="gpu"))."""
         import cv2 as cv
         cpu = current_low.detach().cpu().numpy()
         out = np.empty((cpu.shape[0], 2) + cpu.shape[2:], np.float32)
@@ -78,28 +78,48 @@ class LoadedModel:
             out[b, 1] = cv.inpaint(cpu[b, 9], hole, 3, cv.INPAINT_NS)
         return torch.from_numpy(out).to(current_low.device)
 
-    def inference(self, current_low, prev_high, inpaint_flow=True):
-        """current_low: B x >=10 x h x w renderer output (RGB, mask, normal, depth, flow, ...) on the GPU;
-        prev_high: previous high-res result or None.  Returns the prediction B x Cout x 4h x 4w."""
+    def _variant(self):
+        if self.unshaded:
+            return "unshaded"
+        if self.has_normal and self.has_depth:
+            return "shaded_normal_depth"
+        if self.has_normal:
+            return "shaded_normal"
+        if self.has_depth:
+            return "shaded_depth"
+        return "shaded"
+
+    def inference(self, current_low, prev_high, inpaint_flow=True, inpaint=None):
+        """current_low: B x >=10 x h x w renderer output (RGB, mask, normal, depth, flow, ...) on the GPU -- or the
+        renderer's own interleaved B x h x w x 12 / h x w x 12 frame; prev_high: previous high-res result or None.
+        Returns the prediction B x Cout x 4h x 4w.
+
+        ``inpaint``: "opencv" (the reference's host-side cv.inpaint, loadedmodel.py:77-82; default, needs a device
+        synchronisation and a CPU round trip per frame) or "gpu" (push-pull fill on the device, ops.inpaint_flow:
+        nothing leaves the GPU).  ``self.inpaint`` sets the default.  Channel slicing / mask remap / clamps
+        (loadedmodel.py:84-105) are one ingest kernel either way."""
+        from . import ops
+        mode = inpaint or getattr(self, "inpaint", "opencv")
+        if mode not in ("opencv", "gpu"):
+            raise ValueError("unknown inpaint mode: " + str(mode))
         with torch.no_grad():
             current_low = current_low.to(self.device)
-            flow = self._inpaint_flow(current_low) if inpaint_flow else current_low[:, 8:10].contiguous()
+            interleaved = current_low.dim() == 3 or (current_low.shape[-1] in (10, 12) and current_low.shape[1] not in (10, 12))
+            inp, flow, hole, _ = ops.ingest_gbuffer(current_low, self._variant(), interleaved=interleaved)
+            if inpaint_flow:
+                if mode == "gpu":
+                    flow = ops.inpaint_flow(flow, hole)
+                else:
+                    planar = current_low if not interleaved else (
+                        current_low if current_low.dim() == 4 else current_low.unsqueeze(0)).permute(0, 3, 1, 2)
+                    flow = self._inpaint_flow(planar)
             if self.unshaded:
-                inp = torch.cat((current_low[:, 3:4] * 2 - 1, current_low[:, 4:8]), dim=1)
                 if prev_high is None:
                     prev = initialImage(inp, 6, self.initial_image_mode, self.inverse_ao, self.upscale_factor)
                     prediction, _ = self.model(inp, prev, None)
                 else:
                     prediction, _ = self.model(inp, prev_high.to(self.device), flow, special_mask=True)
             else:
-                if self.has_normal and self.has_depth:
-                    inp = torch.clamp(current_low[:, 0:8], 0, 1)
-                elif self.has_normal:
-                    inp = current_low[:, 0:7]
-                elif self.has_depth:
-                    inp = torch.cat((current_low[:, 0:4], current_low[:, 7:8]), dim=1)
-                else:
-                    inp = current_low[:, 0:4]
                 if prev_high is None:
                     # loadedmodel.py:110 passes upscale_factor as aoInverted (harmless for 'zero'); reproduced
                     prev_high = initialImage(inp, 3, self.initial_image_mode, self.upscale_factor)

@@ -104,6 +104,56 @@ def compose(image_low, pred, params22, unshaded=True, masking=False, background0
     return out
 
 
+INGEST_VARIANTS = {"unshaded": 0, "shaded": 1, "shaded_depth": 2, "shaded_normal": 3, "shaded_normal_depth": 4}
+
+
+def ingest_gbuffer(render, variant="unshaded", interleaved=None, want_flow=True, want_hole=True, want_image12=False):
+    """One-pass G-buffer ingest (include/isr.h isr_ingest_gbuffer).  ``render``: the renderer's frame, H x W x 12 or
+    B x H x W x 12 interleaved (GPURendererDirect wire format; ``interleaved=True``) or planar B x C x h x w (the tensor
+    LoadedModel.inference receives).  ``interleaved=None`` guesses: last dimension 12 and second dimension != 12.
+    Returns (low, flow, hole, image12); entries not asked for are None."""
+    x = _prep(render, "render")
+    if x.dim() == 3:
+        x = x.unsqueeze(0)
+    if interleaved is None:
+        interleaved = x.shape[-1] in (10, 12) and x.shape[1] not in (10, 12)
+    if interleaved:
+        B, h, w, c = x.shape
+    else:
+        B, c, h, w = x.shape
+    v = INGEST_VARIANTS[variant] if isinstance(variant, str) else int(variant)
+    c_low = check(lib().isr_ingest_low_channels(v))
+    dev = x.device
+    low = torch.empty((B, c_low, h, w), device=dev, dtype=torch.float32)
+    flow = torch.empty((B, 2, h, w), device=dev, dtype=torch.float32) if want_flow else None
+    hole = torch.empty((B, h, w), device=dev, dtype=torch.uint8) if want_hole else None
+    img = torch.empty((B, 12, h, w), device=dev, dtype=torch.float32) if want_image12 else None
+    with torch.cuda.device(dev):
+        check(lib().isr_ingest_gbuffer(_p(x), int(bool(interleaved)), B, c, h, w, v, _p(low), _p(flow), _p(hole), _p(img),
+                                       _stream()))
+    return low, flow, hole, img
+
+
+def inpaint_flow(flow, hole):
+    """Device flow in-painting (push-pull pyramid), the replacement of cv.inpaint(..., 3, INPAINT_NS) in
+    loadedmodel.py:77-82.  flow: B x 2 x h x w, hole: B x h x w (non-zero = to be filled)."""
+    f = _prep(flow, "flow")
+    if not isinstance(hole, torch.Tensor) or not hole.is_cuda:
+        raise RuntimeError("hole: the B200 path needs a CUDA tensor; there is no CPU fallback")
+    hm = (hole != 0).to(torch.uint8).contiguous()
+    B, two, h, w = f.shape
+    assert two == 2 and tuple(hm.shape) == (B, h, w)
+    nbytes = _lib._sz(0)
+    check(lib().isr_inpaint_workspace_bytes(B, h, w, ctypes.byref(nbytes)))
+    ws = torch.empty(nbytes.value + 16, device=f.device, dtype=torch.uint8)
+    off = (-ws.data_ptr()) % 16
+    out = torch.empty_like(f)
+    with torch.cuda.device(f.device):
+        check(lib().isr_inpaint_flow(_p(f), _p(hm), _p(out), B, h, w, ctypes.c_void_p(ws.data_ptr() + off), nbytes.value,
+                                     _stream()))
+    return out
+
+
 def _workspace(device, nbytes):
     # cudaMalloc'd blocks from torch's caching allocator are 512-byte aligned; over-allocate and slice to 1024
     buf = torch.empty(nbytes + 1024, device=device, dtype=torch.uint8)

@@ -255,3 +255,85 @@ def psnr(a, b, epsilon=1e-7):
     """utils/psnr.py:10-15 (unmasked branch): 10*log10(1/(eps + mean((a-b)^2))), peak = 1."""
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     return float(10.0 * np.log10(1.0 / (epsilon + np.mean((a - b) ** 2))))
+
+
+# ---- in front of the network: G-buffer ingest and flow in-painting (SURVEY.md 8f ranks 1, 2) ------------------------
+INGEST_CHANNELS = {0: 5, 1: 4, 2: 5, 3: 7, 4: 8}
+
+
+def ingest_gbuffer(render, variant=0, interleaved=True):
+    """Channel slicing of inference/loadedmodel.py:84-105 (+ mainGUI.py:713-716 for image12) applied to the renderer's
+    frame (GPURendererDirect/render_kernel.cu:254-265: RGB, mask, normal, depth, flow, AO, shadow).
+    render: B x h x w x C interleaved or B x C x h x w.  Returns (low, flow, hole, image12)."""
+    r = _f32(render)
+    x = np.ascontiguousarray(r.transpose(0, 3, 1, 2)) if interleaved else r
+    if variant == 0:
+        low = np.concatenate([x[:, 3:4] * np.float32(2) - np.float32(1), x[:, 4:8]], axis=1)
+    elif variant == 4:
+        low = np.clip(x[:, 0:8], 0, 1)
+    elif variant == 3:
+        low = x[:, 0:7]
+    elif variant == 2:
+        low = np.concatenate([x[:, 0:4], x[:, 7:8]], axis=1)
+    else:
+        low = x[:, 0:4]
+    hole = (x[:, 3] == 0).astype(np.uint8)
+    image12 = None
+    if x.shape[1] >= 12:
+        image12 = x[:, :12].copy()
+        image12[:, 3] = x[:, 3] * np.float32(2) - np.float32(1)
+    return _f32(low), _f32(x[:, 8:10]), hole, image12
+
+
+def _half_src(n_out, n_in):
+    d = np.arange(n_out, dtype=np.float32)
+    src = np.float32(0.5) * (d + np.float32(0.5)) - np.float32(0.5)
+    src = np.maximum(src, np.float32(0))
+    a = np.minimum(src.astype(np.int32), n_in - 1)
+    i1 = np.where(a < n_in - 1, a + 1, a)
+    l1 = np.clip(src - a.astype(np.float32), np.float32(0), np.float32(1)).astype(np.float32)
+    return a, i1, (np.float32(1) - l1).astype(np.float32), l1
+
+
+def inpaint_flow_pushpull(flow, hole):
+    """CPU restatement of isr_inpaint_flow (isosurfacesuperresolution_b200/csrc/isr_ingest.cu), the device replacement of
+    cv.inpaint(flow, mask == 0, 3, cv.INPAINT_NS) at inference/loadedmodel.py:77-82.  Not OpenCV's algorithm (push-pull
+    pyramid instead of fast marching): parity with OpenCV is unpinned; this function pins the CUDA kernel's arithmetic,
+    operation for operation, in fp32.  flow: B x 2 x h x w, hole: B x h x w (non-zero = fill)."""
+    f = _f32(flow)
+    B, _, h, w = f.shape
+    wgt = (np.asarray(hole) == 0).astype(np.float32)
+    vals = [np.where(wgt[:, None] > 0, f, np.float32(0)).astype(np.float32)]
+    wts = [wgt]
+    while vals[-1].shape[2] > 1 or vals[-1].shape[3] > 1:     # pull
+        sv, sw = vals[-1], wts[-1]
+        sh, swd = sv.shape[2:]
+        dh, dwd = (sh + 1) // 2, (swd + 1) // 2
+        W = np.zeros((B, dh, dwd), np.float32)
+        V = np.zeros((B, 2, dh, dwd), np.float32)
+        for dy in (0, 1):
+            for dx in (0, 1):
+                cw = np.zeros((B, dh, dwd), np.float32)
+                cv_ = np.zeros((B, 2, dh, dwd), np.float32)
+                ys, xs = sw[:, dy::2, dx::2].shape[1:]
+                cw[:, :ys, :xs] = sw[:, dy::2, dx::2]
+                cv_[:, :, :ys, :xs] = sv[:, :, dy::2, dx::2]
+                W = (W + cw).astype(np.float32)
+                V = (V + (cw[:, None] * cv_).astype(np.float32)).astype(np.float32)
+        any_ = W > 0
+        with np.errstate(divide="ignore", invalid="ignore"):
+            dv = np.where(any_[:, None], (V / W[:, None]).astype(np.float32), np.float32(0)).astype(np.float32)
+        vals.append(dv)
+        wts.append(any_.astype(np.float32))
+    for l in range(len(vals) - 2, -1, -1):                    # push
+        cvv, fv, fw = vals[l + 1], vals[l], wts[l]
+        fh, fwd = fv.shape[2:]
+        y0, y1, ly0, ly1 = _half_src(fh, cvv.shape[2])
+        x0, x1, lx0, lx1 = _half_src(fwd, cvv.shape[3])
+        top, bot = cvv[:, :, y0], cvv[:, :, y1]
+        r0 = ((lx0 * top[:, :, :, x0]).astype(np.float32) + (lx1 * top[:, :, :, x1]).astype(np.float32)).astype(np.float32)
+        r1 = ((lx0 * bot[:, :, :, x0]).astype(np.float32) + (lx1 * bot[:, :, :, x1]).astype(np.float32)).astype(np.float32)
+        fill = ((ly0[:, None] * r0).astype(np.float32) + (ly1[:, None] * r1).astype(np.float32)).astype(np.float32)
+        vals[l] = np.where(fw[:, None] != 0, fv, fill).astype(np.float32)
+        wts[l] = np.ones_like(fw)
+    return vals[0]
