@@ -18,6 +18,7 @@ from .initial_image import initialImage     # noqa: E402
 from .shading import ScreenSpaceShading     # noqa: E402
 from .videotools import VideoTools          # noqa: E402
 from .inference import LoadedModel, SequenceRunner, compose_frame   # noqa: E402
+from .dataset import SequenceDataset, evaluate, masked_psnr           # noqa: E402
 
 
 def createNetwork(name, upscale_factor, input_channels, channel_mask, output_channels, additional_opt):
@@ -30,4 +31,4 @@ def createNetwork(name, upscale_factor, input_channels, channel_mask, output_cha
 
 
 __all__ = ["createNetwork", "EnhanceNet", "VideoTools", "initialImage", "ScreenSpaceShading", "LoadedModel",
-           "SequenceRunner", "compose_frame"]
+           "SequenceRunner", "compose_frame", "SequenceDataset", "evaluate", "masked_psnr"]

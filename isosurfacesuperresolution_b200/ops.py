@@ -140,7 +140,7 @@ def inpaint_flow(flow, hole):
     f = _prep(flow, "flow")
     if not isinstance(hole, torch.Tensor) or not hole.is_cuda:
         raise RuntimeError("hole: the B200 path needs a CUDA tensor; there is no CPU fallback")
-    hm = (hole != 0).to(torch.uint8).contiguous()
+    hm = hole.contiguous() if hole.dtype == torch.uint8 else (hole != 0).to(torch.uint8).contiguous()
     B, two, h, w = f.shape
     assert two == 2 and tuple(hm.shape) == (B, h, w)
     nbytes = _lib._sz(0)

@@ -466,3 +466,24 @@ def test_loaded_model_gpu_inpaint_and_interleaved(isr, weights):
     assert maxabs(cvf, ops.inpaint_flow(fl, hole)) <= float(fl.max() - fl.min())      # both fills stay inside the flow range
     with pytest.raises(ValueError):
         lm.inference(cu(frame), p0, inpaint="bogus")
+
+
+def test_dataset_evaluate_on_npy_sequences(isr, weights, tmp_path):
+    """sequences in the reference's .npy format through the fused recurrent path.  `high` holds the CPU
+    oracle's own (post-processed) predictions, so every PSNR must be at the operand-rounding noise level (>= 45 dB free-running)."""
+    import os
+    net = _net(isr, weights)
+    for i, seed in enumerate((21, 22, 23)):
+        low, flow, _ = orc.synthetic_gbuffer(1, 24, 32, seed, T=3)
+        preds = orc.unshaded_sequence(weights, low, flow, "bilinear", "input", backend="torch")[0]
+        # frame j is warped from frame j-1 with flow[:, j-1] (mainVideoUnshaded.py:429-433), as SequenceRunner does
+        np.save(os.path.join(tmp_path, "low_%05d.npy" % i), low[0])
+        np.save(os.path.join(tmp_path, "flow_%05d.npy" % i), flow[0])
+        np.save(os.path.join(tmp_path, "high_%05d.npy" % i),
+                np.concatenate([orc.postprocess(p, unshaded=True) for p in preds], axis=0))
+    ds = isr.SequenceDataset(str(tmp_path))
+    assert len(ds) == 3 and ds.num_frames == 3 and ds.upscale_factor == 4
+    res = isr.evaluate(net, ds, batch_size=2, initial_image="input")
+    assert res["frames"] == 9
+    for k in ("psnr_mask", "psnr_normal", "psnr_depth", "psnr_ao"):
+        assert res[k] >= 45.0, (k, res)
