@@ -30,6 +30,7 @@ static int g_cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta
 static int g_final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (measured slower: 1.24 vs 0.92 ms), 1 = tap-stacked kernel (isr_conv_final.cuh, Cout <= 8),
                                   // 0 = generic single-CTA N=16 kernel
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
+static int g_pdl = 1;   // CTA-pair convs are launched with programmatic stream serialization (prologue overlaps the previous tail)
 static int g_trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
@@ -246,15 +247,25 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     return ISR_OK;
   }
   const bool stack = L.p.n_w_parts == 2 && g_stack_w;
-  if (L.pair && L.n == 16 && stack)
-    conv3x3_pair_kernel<1, 16, EPI_FINAL><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
-  else if (L.pair && L.n == 16)
-    conv3x3_pair_kernel<0, 16, EPI_FINAL><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
-  else if (L.pair && stack)
-    conv3x3_pair_kernel<1><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
-  else if (L.pair)
-    conv3x3_pair_kernel<0><<<L.grid, kPairThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
-  else if (L.n == 64 && stack)
+  if (L.pair) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(L.grid);
+    cfg.blockDim = dim3(kPairThreads);
+    cfg.dynamicSmemBytes = L.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_pdl ? 1 : 0;
+    if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
+    else if (L.n == 16) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
+    else if (stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16>, L.tmA, L.tmW, L.p));
+    else ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16>, L.tmA, L.tmW, L.p));
+    count_launch();
+    return ISR_OK;
+  }
+  if (L.n == 64 && stack)
     conv3x3_umma_kernel<64, EPI_STORE16, 1><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
   else if (L.n == 64)
     conv3x3_umma_kernel<64, EPI_STORE16, 0><<<L.grid, kConvThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
@@ -560,6 +571,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "trunk_full_blocks") == 0) {
     if (value < 0 || value > 10) return fail(ISR_ERR_ARG, "trunk_full_blocks must be in [0, 10]");
     slot = &g_trunk_full_blocks;
+  } else if (key != nullptr && strcmp(key, "pdl") == 0) {
+    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "pdl must be 0 or 1");
+    slot = &g_pdl;
   } else if (key != nullptr && strcmp(key, "stack_w") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "stack_w must be 0 or 1");
     slot = &g_stack_w;

@@ -152,6 +152,9 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(s_tptr));
 
+  // Programmatic dependent launch: everything above (barriers, TMEM, tensor-map prefetch) and the weight load below do
+  // not depend on the previous kernel; the warps that touch activations call pdl_wait() first.
+  pdl_launch_dependents();
   const int num_pairs = static_cast<int>(gridDim.x) >> 1;
   const int pair_id = static_cast<int>(blockIdx.x) >> 1;
   const int pair_tiles = (p.num_tiles + 1) >> 1;
@@ -177,6 +180,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
     __syncwarp();
+    pdl_wait();   // the activations are the previous kernel's output
     uint32_t it = 0;
     for (int i = 0; i < my_iters; ++i) {
       const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
@@ -270,6 +274,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else {
     // ===================== epilogue warps: group g = warp/4 drains tiles g, g+G, ... =====================
     const int grp = warp >> 2, q = warp & 3;
+    pdl_wait();   // addend reads / output writes must not overtake the previous kernel
     for (int i = grp; i < my_iters; i += G) {
       const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
       const bool valid = t < p.num_tiles;

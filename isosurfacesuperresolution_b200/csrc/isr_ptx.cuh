@@ -73,6 +73,11 @@ __device__ __forceinline__ void mbar_wait_parked(uint32_t bar, uint32_t parity) 
   __trap();
 }
 
+// ---- programmatic dependent launch (the next kernel's prologue overlaps this kernel's tail) ---------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// blocks until every prerequisite grid has completed and its memory is visible; a no-op for ordinary launches
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- 256-bit global accesses (sm_100: LDG/STG.256) ---------------------------------------------------------
 // One instruction per 32-byte sector: the NHWC epilogues leave 16 consecutive 16-bit channels (32 B) in a thread.
 __device__ __forceinline__ void st_global_v8(void *dst, const uint32_t *v) {
