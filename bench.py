@@ -380,7 +380,12 @@ def run_b200(args, rank, world, local_rank):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": achieved / peak_tf, "traffic": None, "peak_source": which + " bf16_tflops (burst)",
+                     "frac": achieved / peak_tf,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of this launch, one `ncu --set full` capture
+                     # (profiles/r01_ncu_conv_full_v8_two_issuers.json: 2.233 GB + 2.101 GB); algorithmic: 2 x 2.147 GB
+                     "traffic": 4.334e9 if (B, h, w) == (16, 256, 256) else None,
+                     "traffic_unit": "bytes per launch (ncu)", "algorithmic_bytes": 2 * 128 * out_px_per_step,
+                     "peak_source": which + " bf16_tflops (burst)",
                      "kernel": "conv3x3_pair_kernel<0> (tcgen05 cta_group::2) 64->64 @1024x1024 x16, "
                                "algorithmic 73,728 FLOP/px", "ms_per_launch": conv_ms},
     }

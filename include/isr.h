@@ -125,6 +125,20 @@ int isr_inpaint_workspace_bytes(int B, int h, int w, size_t *bytes);
 int isr_inpaint_flow(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, void *workspace,
                      size_t workspace_bytes, void *stream);
 
+/* Screen-space ambient occlusion of the renderer's post-pass on the device:
+ * ShadowFX::screenSpaceAmbientOcclusion, GPURenderer/ShadowFX.cpp:23-134, same argument list and meaning (strided
+ * addressing: value(channel, x, y) = buf[channel + entry_stride * (x + row_stride * y)]; the reference calls it in place
+ * on the 12-channel frame with normal = 4..6, depth = 7, output = 10, 64 samples, GPURenderer.cpp:716-723).  input and
+ * output are DEVICE pointers and may alias when the channels differ.  samples <= 128, noise_samples <= 8.
+ * The hemisphere kernel and rotation noise are drawn on the host from std::default_random_engine(42) with the reference's
+ * call sequence (ShadowFX.cpp:35-66); isr_ssao_tables returns them (kernel: 3*samples floats, noise: 3*noise_samples^2
+ * floats, x-major) for inspection. */
+int isr_ssao(int width, int height, const float *input, int input_entry_stride, int input_row_stride, int normal_x_index,
+             int normal_y_index, int normal_z_index, int depth_index, float *output, int output_entry_stride,
+             int output_row_stride, int output_index, int samples, float sample_radius, float bias, int noise_samples,
+             void *stream);
+int isr_ssao_tables(int samples, int noise_samples, float *kernel_host, float *noise_host);
+
 /* ---- EnhanceNet generator (models/enhancenet.py:8-26,92-145) ------------------------------------------- */
 
 typedef struct isr_net isr_net;

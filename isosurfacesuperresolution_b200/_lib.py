@@ -43,6 +43,8 @@ SIGNATURES = {
     "isr_ingest_low_channels": (_i, [_i]),
     "isr_inpaint_workspace_bytes": (_i, [_i, _i, _i, _c.POINTER(_sz)]),
     "isr_inpaint_flow": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
+    "isr_ssao": (_i, [_i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _c.c_float, _c.c_float, _i, _vp]),
+    "isr_ssao_tables": (_i, [_i, _i, _vp, _vp]),
     "isr_net_create": (_i, [_c.POINTER(_vp), _i, _i, _i, _i, _i]),
     "isr_net_destroy": (None, [_vp]),
     "isr_net_load_weights": (_i, [_vp, _c.POINTER(_vp), _i, _vp]),

@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <random>
 #include <string>
 #include <vector>
 
@@ -648,6 +649,70 @@ int isr_compose(const float *low, const float *pred, const float *params_host, f
   float zeros[22] = {0};
   ISR_CUDA(launch_compose(low, pred, params_host != nullptr ? params_host : zeros, out, B, c_low, c_pred, h, w, unshaded,
                           masking, background0, S(stream)));
+  return ISR_OK;
+}
+
+// ShadowFX.cpp:35-66: sample hemisphere and kernel rotations from std::default_random_engine(42); expressions keep the
+// reference's float / double mix (2.0, 1.0 and 64.0 are double literals, Vec3<float> stores the rounded result)
+static void ssao_fill_tables(int samples, int ns, SsaoTables *t) {
+  std::uniform_real_distribution<float> randomFloats(0.0, 1.0);
+  std::default_random_engine generator(42);
+  for (int i = 0; i < samples; ++i) {
+    // constructor arguments in the reference: evaluated right to left by MSVC and g++ (z, y, x)
+    float sz = static_cast<float>(randomFloats(generator) * 2.0 - 1.0);
+    float sy = randomFloats(generator);
+    float sx = static_cast<float>(randomFloats(generator) * 2.0 - 1.0);
+    const float d = sqrtf(sx * sx + sy * sy + sz * sz);   // Vec3::normalize()
+    if (!(fabsf(d) <= 1.0e-7f)) {
+      const float inv = 1.0f / d;
+      sx *= inv; sy *= inv; sz *= inv;
+    }
+    const float r = randomFloats(generator);
+    sx *= r; sy *= r; sz *= r;
+    float scale = static_cast<float>(static_cast<float>(i) / 64.0);
+    scale = 0.1f + scale * scale * (1.0f - 0.1f);
+    t->kernel[3 * i] = sx * scale; t->kernel[3 * i + 1] = sy * scale; t->kernel[3 * i + 2] = sz * scale;
+  }
+  for (int x = 0; x < ns; ++x)
+    for (int y = 0; y < ns; ++y) {
+      const float nz = static_cast<float>(randomFloats(generator) * 2.0 - 1.0);   // right to left
+      const float nx = static_cast<float>(randomFloats(generator) * 2.0 - 1.0);
+      t->noise[(x * ns + y) * 3] = nx; t->noise[(x * ns + y) * 3 + 1] = 0.0f; t->noise[(x * ns + y) * 3 + 2] = nz;
+    }
+}
+
+int isr_ssao_tables(int samples, int noise_samples, float *kernel_host, float *noise_host) {
+  if (samples <= 0 || samples > 128 || noise_samples <= 0 || noise_samples > 8)
+    return fail(ISR_ERR_UNSUPPORTED, "ssao: samples must be in [1,128] and noise_samples in [1,8]");
+  SsaoTables t;
+  memset(&t, 0, sizeof t);
+  ssao_fill_tables(samples, noise_samples, &t);
+  if (kernel_host != nullptr) memcpy(kernel_host, t.kernel, sizeof(float) * 3 * samples);
+  if (noise_host != nullptr) memcpy(noise_host, t.noise, sizeof(float) * 3 * noise_samples * noise_samples);
+  return ISR_OK;
+}
+
+int isr_ssao(int width, int height, const float *input, int input_entry_stride, int input_row_stride, int normal_x_index,
+             int normal_y_index, int normal_z_index, int depth_index, float *output, int output_entry_stride,
+             int output_row_stride, int output_index, int samples, float sample_radius, float bias, int noise_samples,
+             void *stream) {
+  if (input == nullptr || output == nullptr || width <= 0 || height <= 0 || input_entry_stride <= 0 ||
+      output_entry_stride <= 0 || input_row_stride < width || output_row_stride < width)
+    return fail(ISR_ERR_ARG, "ssao: bad arguments");
+  if (samples <= 0 || samples > 128 || noise_samples <= 0 || noise_samples > 8)
+    return fail(ISR_ERR_UNSUPPORTED, "ssao: samples must be in [1,128] and noise_samples in [1,8]");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  static thread_local SsaoTables tab;
+  static thread_local int tab_samples = -1, tab_ns = -1;
+  if (tab_samples != samples || tab_ns != noise_samples) {
+    memset(&tab, 0, sizeof tab);
+    ssao_fill_tables(samples, noise_samples, &tab);
+    tab_samples = samples; tab_ns = noise_samples;
+  }
+  ISR_CUDA(launch_ssao(input, input_entry_stride, input_row_stride, normal_x_index, normal_y_index, normal_z_index,
+                       depth_index, output, output_entry_stride, output_row_stride, output_index, width, height, samples,
+                       sample_radius, bias, noise_samples, tab, S(stream)));
   return ISR_OK;
 }
 

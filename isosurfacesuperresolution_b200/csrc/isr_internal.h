@@ -39,4 +39,13 @@ size_t inpaint_workspace_floats(int B, int h, int w);
 cudaError_t launch_inpaint_flow(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, float *ws,
                                 cudaStream_t s);
 
+// isr_ssao.cu: hemisphere kernel (<= 128 samples) and rotation noise (<= 8 x 8), passed by value to the kernel
+struct SsaoTables {
+  float kernel[3 * 128];
+  float noise[3 * 64];
+};
+cudaError_t launch_ssao(const float *input, int es, int rs, int inx, int iny, int inz, int idepth, float *output, int oes,
+                        int ors, int oidx, int width, int height, int samples, float radius, float bias, int ns,
+                        const SsaoTables &tab, cudaStream_t s);
+
 }  // namespace isr

@@ -154,6 +154,22 @@ def inpaint_flow(flow, hole):
     return out
 
 
+def ssao(frame, samples=64, sample_radius=0.1, bias=0.025, noise_samples=4, normal_index=4, depth_index=7,
+         output_index=10):
+    """ShadowFX::screenSpaceAmbientOcclusion (GPURenderer/ShadowFX.cpp:23-134) on the device, IN PLACE on the renderer's
+    interleaved frame (H x W x C or B x H x W x C CUDA tensor; channel layout of GPURenderer.cpp:716-723).  Returns it."""
+    if not isinstance(frame, torch.Tensor) or not frame.is_cuda or frame.dtype != torch.float32 or not frame.is_contiguous():
+        raise RuntimeError("frame: a contiguous CUDA float32 tensor is required; there is no CPU fallback")
+    views = [frame] if frame.dim() == 3 else list(frame.unbind(0))
+    with torch.cuda.device(frame.device):
+        for f in views:
+            H, W, C = f.shape
+            check(lib().isr_ssao(W, H, _p(f), C, W, normal_index, normal_index + 1, normal_index + 2, depth_index, _p(f),
+                                 C, W, output_index, int(samples), float(sample_radius), float(bias), int(noise_samples),
+                                 _stream()))
+    return frame
+
+
 def _workspace(device, nbytes):
     # cudaMalloc'd blocks from torch's caching allocator are 512-byte aligned; over-allocate and slice to 1024
     buf = torch.empty(nbytes + 1024, device=device, dtype=torch.uint8)

@@ -337,3 +337,57 @@ def inpaint_flow_pushpull(flow, hole):
         vals[l] = np.where(fw[:, None] != 0, fv, fill).astype(np.float32)
         wts[l] = np.ones_like(fw)
     return vals[0]
+
+
+# ---- screen-space ambient occlusion ---------------------------------------------------------
+_SSAO = None
+_SSAO_REF = None
+_SSAO_ARGS = [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+              ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+              ctypes.c_float, ctypes.c_float, ctypes.c_int]
+
+
+def _ssao_lib():
+    global _SSAO
+    if _SSAO is None:
+        so = os.path.join(_HERE, "libisr_oracle_ssao.so")
+        src = os.path.join(_HERE, "ssao_oracle.cpp")
+        if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+            subprocess.check_call(["make", "-C", _HERE, "-s", "libisr_oracle_ssao.so"])
+        _SSAO = ctypes.CDLL(so)
+        _SSAO.orc_ssao.argtypes = _SSAO_ARGS
+        _SSAO.orc_ssao.restype = None
+    return _SSAO
+
+
+def ssao_ref_available():
+    return os.path.exists(os.path.join(_HERE, "_ref", "libshadowfx_ref.so"))
+
+
+def ssao_tables(samples=64, noise_samples=4):
+    k = np.zeros(3 * samples, np.float32)
+    n = np.zeros(3 * noise_samples * noise_samples, np.float32)
+    _ssao_lib().orc_ssao_tables(samples, noise_samples, _p(k), _p(n))
+    return k, n
+
+
+def ssao(frame, samples=64, sample_radius=0.1, bias=0.025, noise_samples=4, normal_index=4, depth_index=7,
+         output_index=10, use_reference_build=False):
+    """ShadowFX::screenSpaceAmbientOcclusion (GPURenderer/ShadowFX.cpp:23-134) on one interleaved H x W x C frame, in the
+    channel layout of its call site (GPURenderer.cpp:716-723: normal 4..6, depth 7, AO -> 10).  Returns a copy of the frame
+    with the AO channel written.  ``use_reference_build``: run the reference's own ShadowFX.cpp compiled in place
+    (oracle/_ref, only where /root/reference was present at build time) instead of the restatement."""
+    global _SSAO_REF
+    f = _f32(frame).copy()
+    H, W, C = f.shape
+    args = (W, H, _p(f), C, W, normal_index, normal_index + 1, normal_index + 2, depth_index, _p(f), C, W, output_index,
+            samples, sample_radius, bias, noise_samples)
+    if use_reference_build:
+        if _SSAO_REF is None:
+            _SSAO_REF = ctypes.CDLL(os.path.join(_HERE, "_ref", "libshadowfx_ref.so"))
+            _SSAO_REF.ref_ssao.argtypes = _SSAO_ARGS
+            _SSAO_REF.ref_ssao.restype = None
+        _SSAO_REF.ref_ssao(*args)
+    else:
+        _ssao_lib().orc_ssao(*args)
+    return f

@@ -487,3 +487,27 @@ def test_dataset_evaluate_on_npy_sequences(isr, weights, tmp_path):
     assert res["frames"] == 9
     for k in ("psnr_mask", "psnr_normal", "psnr_depth", "psnr_ao"):
         assert res[k] >= 45.0, (k, res)
+
+
+# ---- screen-space ambient occlusion ----------------------------------------------------------
+@pytest.mark.parametrize("cfg", [dict(), dict(samples=32, sample_radius=0.05), dict(noise_samples=2, bias=0.0)])
+def test_ssao_equals_oracle(isr, cfg):
+    """isr_ssao against the CPU restatement of ShadowFX::screenSpaceAmbientOcclusion (bit-exact: same fp32 / fp64
+    operations in the same order) and, where it was built, against the reference's own ShadowFX.cpp (oracle/_ref)."""
+    from isosurfacesuperresolution_b200 import ops
+    from test_ssao_oracle import ssao_frame
+    for shape in ((48, 64), (67, 45)):
+        f = ssao_frame(*shape)
+        ref = orc.ssao(f, **cfg)
+        out = ops.ssao(cu(f), **cfg).cpu().numpy()
+        assert np.array_equal(out[..., :10], f[..., :10]) and np.array_equal(out[..., 11], f[..., 11])   # in place, AO only
+        assert np.array_equal(out[..., 10], ref[..., 10])
+        if orc.ssao_ref_available():
+            assert np.array_equal(out, orc.ssao(f, use_reference_build=True, **cfg))
+    # batched interleaved frames and argument checks
+    fb = np.stack([ssao_frame(32, 40, seed=s) for s in (1, 2)])
+    ob = ops.ssao(cu(fb)).cpu().numpy()
+    for i in range(2):
+        assert np.array_equal(ob[i], orc.ssao(fb[i]))
+    with pytest.raises(Exception):
+        ops.ssao(cu(fb), samples=129)
