@@ -511,3 +511,42 @@ def test_ssao_equals_oracle(isr, cfg):
         assert np.array_equal(ob[i], orc.ssao(fb[i]))
     with pytest.raises(Exception):
         ops.ssao(cu(fb), samples=129)
+
+
+# ---- full BASELINE.json sizes through a size-independent property ---------------------------------------------------
+@pytest.mark.parametrize("cfg", ["C2", "C3", "C4"])
+def test_full_size_crop_parity(isr, weights, cfg):
+    """The network is translation-covariant with a finite receptive field (21 low-res convs + the three high-res ones and
+    the bilinear steps: < 28 low-res pixels), so far enough from a crop's border the output of the FULL-size problem must
+    equal the fp32 CPU oracle run on the crop alone.  This carries the 1e-2 / 50 dB bar to the sizes of
+    BASELINE.json configs[1] (16 x 256^2), configs[2] (1 x 270x480, ragged tiles) and configs[3] (shaded 56 -> 3,
+    4 x 540x960 -> 2160x3840), where the oracle itself would take minutes.  Also: a sequence's result does not depend on
+    the rest of its batch (bit-exact)."""
+    M, S = 28, 84                                                    # margin, crop side (low-res)
+    if cfg == "C4":
+        torch.manual_seed(1234)
+        net = _net(isr, None, cin=56, cout=3, mask=(0, 1, 2))
+        wts = {k: v.detach().cpu().numpy() for k, v in net.state_dict().items()}
+        B, h, w, cin, nm = 4, 540, 960, 56, 3
+    else:
+        net, wts, cin, nm = _net(isr, weights), weights, 101, 5
+        B, h, w = (16, 256, 256) if cfg == "C2" else (1, 270, 480)
+    g = torch.Generator(device="cuda").manual_seed(77)
+    x = torch.rand(B, cin, h, w, device="cuda", generator=g) * 2 - 1
+    with torch.no_grad():
+        recon, raw = net(x)
+    assert recon.shape == (B, nm if cfg == "C4" else 6, 4 * h, 4 * w)
+    for b, y0, x0 in ((B - 1, h - S, w - S), (0, 0, 0), (B // 2, (h - S) // 2 + 3, (w - S) // 2 + 5)):
+        crop = x[b:b + 1, :, y0:y0 + S, x0:x0 + S].cpu().numpy()
+        ref_recon, ref_raw = orc.enhancenet_forward(wts, crop, "bilinear", "residual", nm, backend="torch")
+        # interior of the crop, except where the crop border IS the image border (same zero padding on both sides)
+        ya, yb = (0 if y0 == 0 else M), (S if y0 + S == h else S - M)
+        xa, xb = (0 if x0 == 0 else M), (S if x0 + S == w else S - M)
+        sl = (slice(None), slice(None), slice(4 * ya, 4 * yb), slice(4 * xa, 4 * xb))
+        full = (slice(b, b + 1), slice(None), slice(4 * (y0 + ya), 4 * (y0 + yb)), slice(4 * (x0 + xa), 4 * (x0 + xb)))
+        _check_net(raw[full], ref_raw[sl])
+        _check_net(recon[full], ref_recon[sl])
+    if B > 1:                                                       # batch independence, bit for bit
+        with torch.no_grad():
+            alone, _ = net(x[B - 1:B].contiguous())
+        assert torch.equal(alone, recon[B - 1:B])
