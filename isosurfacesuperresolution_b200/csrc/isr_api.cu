@@ -31,6 +31,7 @@ static int g_cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta
 static int g_final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (measured slower: 1.24 vs 0.92 ms), 1 = tap-stacked kernel (isr_conv_final.cuh, Cout <= 8),
                                   // 0 = generic single-CTA N=16 kernel
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
+static int g_fuse_up = 1;   // bilinear nets: the 4x upsample + first 4x conv run as one phase-decomposed kernel (isr_up2.cu)
 static int g_pdl = 1;   // CTA-pair convs are launched with programmatic stream serialization (prologue overlaps the previous tail)
 static int g_trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
 
@@ -108,6 +109,7 @@ struct ConvLaunch {
   int n;  // 64 (EPI_STORE16) or 16 (EPI_FINAL)
   int cp = 0;  // > 0: tap-stacked output conv (conv3x3_final_kernel<cp>)
   int pair = 0;  // 1: CTA-pair kernel (conv3x3_pair_kernel)
+  int ph = 1;    // 4: fused upsample + conv (four output phases per low-res tile)
   size_t smem;
   int grid;
 };
@@ -139,6 +141,8 @@ static int setup_kernel_attrs() {
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(kSmemLimit - kStaticSmem)));
+  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
   ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0, 16, EPI_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(kSmemLimit - kStaticSmem)));
@@ -196,6 +200,35 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   int rc = make_act_map(&L->tmA, act, B, H, W, 64 * tensor_parts, kPitch, kHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
   return make_w_map(&L->tmW, wpacked, w_rows_total, L->pair ? n / 2 : n, is_bf16);
+}
+
+// fused bilinear-2x-upsample + conv (64 -> 64): act = LOW-res input [B][hl][wl][64 * tensor_parts], wpacked = composite
+// weights of the chosen format [phase 4][tap 9][64][64]; the launch writes the (2 hl) x (2 wl) output
+static int init_conv_up2(ConvLaunch *L, const void *act, int B, int hl, int wl, int tensor_parts, const void *wpacked,
+                         int is_bf16) {
+  memset(&L->p, 0, sizeof L->p);
+  L->n = 64; L->cp = 0; L->pair = 1; L->ph = 4;
+  ConvParams &p = L->p;
+  p.B = B; p.H = hl; p.W = wl;
+  p.tiles_x = (wl + kTileW - 1) / kTileW;
+  p.tiles_y = (hl + kTileH - 1) / kTileH;
+  p.num_tiles = p.tiles_x * p.tiles_y * B;
+  p.n_act_parts = 1; p.n_w_parts = 1; p.is_bf16 = is_bf16;
+  p.w_row0 = 0; p.w_row_stride = 64;
+  const size_t w_bytes = static_cast<size_t>(36) * 32 * 128;   // per CTA: 4 phases x 9 taps x 32 rows
+  p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kPitch) * kHaloH * 128, 1024));
+  int stages = static_cast<int>((kSmemLimit - kStaticSmem - 1024 - w_bytes - 512) / p.stage_bytes);
+  if (stages > 4) stages = 4;
+  if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "up2 conv smem plan: fewer than 2 halo stages fit");
+  p.num_stages = stages;
+  L->smem = 1024 + w_bytes + static_cast<size_t>(stages) * p.stage_bytes + 512;   // 8 accumulator barriers: 512 B block
+  int cap = (g_max_ctas > 0 ? g_max_ctas : num_sms()) & ~1;
+  if (cap < 2) cap = 2;
+  const int want = 2 * ((p.num_tiles + 1) / 2);
+  L->grid = want < cap ? want : cap;
+  int rc = make_act_map(&L->tmA, act, B, hl, wl, 64 * tensor_parts, kPitch, kHaloH, is_bf16);
+  if (rc != ISR_OK) return rc;
+  return make_w_map(&L->tmW, wpacked, 36 * 64, 32, is_bf16);
 }
 
 static int final_cp(int cout) { return cout <= 4 ? 4 : (cout <= 6 ? 6 : 8); }
@@ -259,7 +292,8 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = g_pdl ? 1 : 0;
-    if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
+    if (L.ph == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, L.tmA, L.tmW, L.p));
+    else if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
     else if (L.n == 16) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
     else if (stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16>, L.tmA, L.tmW, L.p));
     else ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16>, L.tmA, L.tmW, L.p));
@@ -312,6 +346,7 @@ struct Layer {
   uint16_t *packed = nullptr;  // [fmt 2][part 2][tap 9][G][npad][64]
   float *bias = nullptr;       // npad floats, zero padded
   uint16_t *packed_fin = nullptr;  // output conv only: tap-stacked [fmt 2][part 2][nrows][64]
+  uint16_t *packed_up = nullptr;   // layer 22 only: composite weights of the fused upsample + conv [fmt 2][phase 4][tap 9][64][64]
   size_t per_fmt() const { return static_cast<size_t>(2) * 9 * G * npad * 64; }
   int rows() const { return 2 * 9 * G * npad; }
 };
@@ -327,6 +362,10 @@ struct Plan {
   // pointwise steps interleaved with convs: up2 after conv index up_after[0], up4 after up_after[1]
   uint16_t *f_last = nullptr, *u2 = nullptr, *c2 = nullptr, *u4 = nullptr, *c4 = nullptr;
   int idx_post1 = 0, idx_post4 = 0, idx_final = 0;
+  // fused 4x upsample + conv (isr_up2.cu): the phase kernel, the two band convs and their buffers
+  int fuse4 = 0, fuse_up = 0;
+  ConvLaunch up4, band_r, band_c;
+  uint16_t *rows_in = nullptr, *cols_in = nullptr, *rows_out = nullptr, *cols_out = nullptr;
 };
 
 }  // namespace isr
@@ -342,13 +381,13 @@ struct isr_net {
 namespace isr {
 
 static size_t plan_bytes(const isr_net *net, int B, int h, int w, const Scheme &trunk, const Scheme &tail,
-                         size_t *offs /* 9 offsets */) {
+                         size_t *offs /* 13 offsets */) {
   const size_t P = static_cast<size_t>(B) * h * w;
   const size_t lo = align_up(P * 128 * (trunk.stream_parts() > trunk.na ? trunk.stream_parts() : trunk.na), 1024);
   const size_t t2 = align_up(P * 4 * 128 * tail.na, 1024);
   const size_t t4 = align_up(P * 16 * 128 * tail.na, 1024);
   size_t o = 0;
-  size_t tmp[9];
+  size_t tmp[13];
   if (offs == nullptr) offs = tmp;
   offs[0] = o; o += lo;                       // in_g0
   offs[1] = o; o += (net->G == 2 ? lo : 0);   // in_g1
@@ -359,6 +398,13 @@ static size_t plan_bytes(const isr_net *net, int B, int h, int w, const Scheme &
   offs[6] = o; o += 2 * t2;                   // u2, c2
   offs[7] = o; o += t4;                       // u4
   offs[8] = o; o += t4;                       // c4
+  // bands of the fused 4x upsample + conv (isr_up2.cu): 3 rows / 3 columns on each side, input and output
+  const size_t rb = align_up(static_cast<size_t>(B) * 6 * 4 * w * 128 * tail.na, 1024);
+  const size_t cb = align_up(static_cast<size_t>(B) * 6 * 4 * h * 128 * tail.na, 1024);
+  offs[9] = o; o += rb;                       // rows_in
+  offs[10] = o; o += cb;                      // cols_in
+  offs[11] = o; o += rb;                      // rows_out
+  offs[12] = o; o += cb;                      // cols_out
   return o;
 }
 
@@ -382,7 +428,7 @@ static int conv_for_layer(ConvLaunch *L, const Layer &ly, int g, const uint16_t 
 static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
   if (!get_schemes(precision, &pl->trunk, &pl->tail, &pl->fin_nw))
     return fail(ISR_ERR_ARG, "unknown precision %d", precision);
-  size_t offs[9];
+  size_t offs[13];
   const size_t need = plan_bytes(net, B, h, w, pl->trunk, pl->tail, offs);
   if (ws == nullptr || ws_bytes < need)
     return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, need);
@@ -391,6 +437,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->pitch = g_halo_pitch; pl->bo = g_base_offset_mode; pl->max_ctas = g_max_ctas;
   pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w; pl->cta_pair = g_cta_pair;
   pl->full_blocks = g_trunk_full_blocks;
+  pl->fuse_up = g_fuse_up;
   uint8_t *base = static_cast<uint8_t *>(ws);
   auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
   const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
@@ -451,6 +498,20 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   if ((rc = conv_for_layer(&L, net->layers[22], 0, pl->u4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
   set_store(&L, net->layers[22].bias, 1, nullptr, 0, pl->c4, Hs.na);
   pl->convs.push_back(L);
+  // fused form of (upsample 2x -> layers[22]): phase-decomposed kernel on c2 + the plain conv on four border bands
+  pl->fuse4 = 0;
+  if (g_fuse_up && g_cta_pair && net->upsample == ISR_UPSAMPLE_BILINEAR && Hs.na == 1 && Hs.nw == 1 && net->layers[22].packed_up != nullptr &&
+      2 * h >= 4 && 2 * w >= 4) {
+    const uint16_t *wu = net->layers[22].packed_up + (Hs.bf16 ? 0 : static_cast<size_t>(36) * 4096);
+    if ((rc = init_conv_up2(&pl->up4, pl->c2, B, 2 * h, 2 * w, Hs.na, wu, Hs.bf16)) != ISR_OK) return rc;
+    set_store(&pl->up4, net->layers[22].bias, 1, nullptr, 0, pl->c4, Hs.na);
+    pl->rows_in = at(9); pl->cols_in = at(10); pl->rows_out = at(11); pl->cols_out = at(12);
+    if ((rc = conv_for_layer(&pl->band_r, net->layers[22], 0, pl->rows_in, 2 * B, 3, 4 * w, Hs)) != ISR_OK) return rc;
+    set_store(&pl->band_r, net->layers[22].bias, 1, nullptr, 0, pl->rows_out, Hs.na);
+    if ((rc = conv_for_layer(&pl->band_c, net->layers[22], 0, pl->cols_in, 2 * B, 4 * h, 3, Hs)) != ISR_OK) return rc;
+    set_store(&pl->band_c, net->layers[22].bias, 1, nullptr, 0, pl->cols_out, Hs.na);
+    pl->fuse4 = 1;
+  }
   if ((rc = conv_for_layer(&L, net->layers[23], 0, pl->c4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
   set_store(&L, net->layers[23].bias, 1, nullptr, 0, pl->u4, Hs.na);
   pl->convs.push_back(L);
@@ -480,7 +541,7 @@ static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision
     if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
         pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
         pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair &&
-        pl->full_blocks == g_trunk_full_blocks) {
+        pl->full_blocks == g_trunk_full_blocks && pl->fuse_up == g_fuse_up) {
       *out = pl;
       return ISR_OK;
     }
@@ -508,6 +569,15 @@ static int run_plan(isr_net *net, Plan *pl, const float *skip_src, long long ski
     if (i == pl->idx_post1)
       ISR_CUDA(launch_upsample2x(pl->f_last, pl->u2, pl->B, pl->h, pl->w, pl->f_last_parts, Hs.na, T.bf16, Hs.bf16,
                                  net->upsample == ISR_UPSAMPLE_BILINEAR, s));
+    if (i == pl->idx_post4 && pl->fuse4) {
+      // conv3x3(bilinear_up2(c2)) without the upsampled tensor; then the 2-px border ring from the four bands
+      if ((rc = run_conv(pl->up4, s)) != ISR_OK) return rc;
+      ISR_CUDA(launch_band_upsample(pl->c2, pl->rows_in, pl->cols_in, pl->B, 2 * pl->h, 2 * pl->w, Hs.na, Hs.bf16, s));
+      if ((rc = run_conv(pl->band_r, s)) != ISR_OK) return rc;
+      if ((rc = run_conv(pl->band_c, s)) != ISR_OK) return rc;
+      ISR_CUDA(launch_band_scatter(pl->rows_out, pl->cols_out, pl->c4, pl->B, 4 * pl->h, 4 * pl->w, Hs.na, s));
+      continue;
+    }
     if (i == pl->idx_post4)
       ISR_CUDA(launch_upsample2x(pl->c2, pl->u4, pl->B, 2 * pl->h, 2 * pl->w, Hs.na, Hs.na, Hs.bf16, Hs.bf16,
                                  net->upsample == ISR_UPSAMPLE_BILINEAR, s));
@@ -572,6 +642,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "trunk_full_blocks") == 0) {
     if (value < 0 || value > 10) return fail(ISR_ERR_ARG, "trunk_full_blocks must be in [0, 10]");
     slot = &g_trunk_full_blocks;
+  } else if (key != nullptr && strcmp(key, "fuse_up") == 0) {
+    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "fuse_up must be 0 or 1");
+    slot = &g_fuse_up;
   } else if (key != nullptr && strcmp(key, "pdl") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "pdl must be 0 or 1");
     slot = &g_pdl;
@@ -785,6 +858,10 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
       return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
     }
   }
+  if (cudaMalloc(&net->layers[22].packed_up, static_cast<size_t>(2) * 36 * 4096 * sizeof(uint16_t)) != cudaSuccess) {
+    isr_net_destroy(net);
+    return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
+  }
   if (output_channels <= 8) {
     const int nrows = final_rows(final_cp(output_channels));
     if (cudaMalloc(&net->layers[24].packed_fin, static_cast<size_t>(4) * nrows * 64 * sizeof(uint16_t)) != cudaSuccess) {
@@ -803,6 +880,7 @@ void isr_net_destroy(isr_net *net) {
     if (net->layers[i].packed) cudaFree(net->layers[i].packed);
     if (net->layers[i].bias) cudaFree(net->layers[i].bias);
     if (net->layers[i].packed_fin) cudaFree(net->layers[i].packed_fin);
+    if (net->layers[i].packed_up) cudaFree(net->layers[i].packed_up);
   }
   delete net;
 }
@@ -814,6 +892,7 @@ int isr_net_load_weights(isr_net *net, const float *const *params, int n_params,
     Layer &ly = net->layers[i];
     if (params[2 * i] == nullptr || params[2 * i + 1] == nullptr) return fail(ISR_ERR_ARG, "load_weights: null tensor");
     ISR_CUDA(launch_pack_weights(params[2 * i], ly.packed, ly.cout, ly.cin, ly.npad, ly.G, S(stream)));
+    if (ly.packed_up != nullptr) ISR_CUDA(launch_pack_weights_up2(params[2 * i], ly.packed_up, S(stream)));
     if (ly.packed_fin != nullptr)
       ISR_CUDA(launch_pack_weights_final(params[2 * i], ly.packed_fin, ly.cout, final_cp(ly.cout),
                                          final_rows(final_cp(ly.cout)), S(stream)));

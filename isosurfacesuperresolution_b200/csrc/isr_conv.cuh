@@ -93,7 +93,9 @@ __device__ __forceinline__ void bil_src(int dst, int n_in, float inv_scale, int 
 template <int N, int STACK>
 __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const float *s_bias, uint32_t taddr, int q, int lane,
                                                  int b, int ty, int tx, bool tile_valid, uint32_t bar_tfull,
-                                                 uint32_t acc_ph) {
+                                                 uint32_t acc_ph, int omul = 1, int oyadd = 0, int oxadd = 0) {
+  // omul / oyadd / oxadd: tile pixel (y, x) is stored at output pixel (omul * y + oyadd, omul * x + oxadd) of an
+  // (omul * H) x (omul * W) tensor -- the phase interleave of the fused upsample + conv layer (omul = 2)
   const uint32_t b_tfull = bar_tfull;
   constexpr uint32_t acc = 0;   // bar_tfull already addresses this tile's accumulator barrier
     // thread (m = lane%4, rr = lane/4): pixel column rr of image rows 4q..4q+3 of the tile, channels 16m..16m+15
@@ -138,7 +140,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
       for (int hh = 0; hh < 2; ++hh) {
         const int y = ty * kTileH + 4 * q + 2 * half + hh;
         if (tile_valid && y < p.H && x < p.W) {
-          const size_t pix = (static_cast<size_t>(b) * p.H + y) * p.W + x;
+          const size_t pix = (static_cast<size_t>(b) * (p.H * omul) + (y * omul + oyadd)) * (p.W * omul) + (x * omul + oxadd);
           float f[16];
 #pragma unroll
           for (int rep = 0; rep < 8; ++rep) {

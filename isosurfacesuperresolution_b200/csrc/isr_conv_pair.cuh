@@ -104,11 +104,15 @@ constexpr int kPairThreads = (4 * kPairGroups + 1 + kPairIssuers) * 32;
 // + 32 (Y region: its half of W_hi); otherwise 32 per weight part.
 // N = 16 with EPI_FINAL: the network's output conv (Cout <= 16) with its fused skip / state epilogue; an N = 16 pair-MMA
 // costs 39 cycles, and the epilogue is a plain TMEM row load (no shared-memory gather as in isr_conv_final.cuh).
-template <int STACK, int N = 64, int EPI = EPI_STORE16>
+// PH = 4: fused bilinear-2x-upsample + conv (isr_up2.cu): every low-res tile is convolved four times, once per output
+// phase (py, px), with that phase's composite weights; the four results are four "virtual tiles" v = 4*i + phase that
+// share the tile's halo stage, each with its own accumulator buffer (8 buffers) and its own strided output pixels.
+template <int STACK, int N = 64, int EPI = EPI_STORE16, int PH = 1>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const ConvParams p) {
   static_assert(N == 64 || N == 16, "N = 64 (hidden layers) or 16 (output conv)");
+  static_assert(PH == 1 || (PH == 4 && STACK == 0 && N == 64 && EPI == EPI_STORE16), "PH = 4: single-pass 64-wide layers only");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5;
@@ -116,15 +120,15 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t rank = cluster_ctarank();
 
   constexpr uint32_t kHalfTap = (N / 2) * 128;   // 32 weight rows = 4 KB
-  const uint32_t w_bytes = STACK ? 9 * 3 * kHalfTap : p.n_w_parts * 9 * kHalfTap;   // per CTA
+  const uint32_t w_bytes = STACK ? 9 * 3 * kHalfTap : (PH == 4 ? 36 : p.n_w_parts * 9) * kHalfTap;   // per CTA
   const uint32_t s_w = smem_base;
   const uint32_t s_wy = s_w + 9 * 2 * kHalfTap;   // STACK: Y region after the X region
   const uint32_t s_stage0 = s_w + ((w_bytes + 1023u) & ~1023u);
   const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
-  constexpr int G = kPairGroups, NB = kPairBufs, kTmaWarp = 4 * G, kMmaWarp = 4 * G + 1;
+  constexpr int G = kPairGroups, NB = (PH == 4 ? 8 : kPairBufs), kTmaWarp = 4 * G, kMmaWarp = 4 * G + 1;
   const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
                  b_tempty = b_tfull + 8 * NB, s_tptr = b_tempty + 8 * NB;
-  static_assert(136 + 16 * NB + 4 <= 256, "barrier block overflows its 256-byte reservation");
+  static_assert(136 + 16 * NB + 4 <= (PH == 4 ? 512 : 256), "barrier block overflows its reservation (256 B; 512 B for PH = 4)");
   __shared__ float s_bias[64];
   if (threadIdx.x < 64) s_bias[threadIdx.x] = (p.bias != nullptr && threadIdx.x < N) ? p.bias[threadIdx.x] : 0.f;
 
@@ -133,7 +137,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmW);
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(b_full + 8 * s, 2);    // used in the leader: one arrive.expect_tx per CTA
-      mbar_init(b_empty + 8 * s, 1);   // per CTA: multicast commit
+      mbar_init(b_empty + 8 * s, PH == 4 ? 2 : 1);   // per CTA: multicast commit (PH = 4: one per issuing warp)
     }
     mbar_init(b_w, 2);
     for (int a = 0; a < NB; ++a) {
@@ -173,10 +177,9 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tma2_load_2d(s_wy + tap * kHalfTap, &tmW, lead_w, 0, p.w_row0 + tap * p.w_row_stride + static_cast<int>(rank) * (N / 2));
         }
       } else {
-        for (int wp = 0; wp < p.n_w_parts; ++wp)
-          for (int tap = 0; tap < 9; ++tap)
-            tma2_load_2d(s_w + (wp * 9 + tap) * kHalfTap, &tmW, lead_w, 0,
-                         p.w_row0 + (wp * 9 + tap) * p.w_row_stride + static_cast<int>(rank) * (N / 2));
+        const int nblk = PH == 4 ? 36 : p.n_w_parts * 9;   // (part | phase, tap) blocks of N rows
+        for (int j = 0; j < nblk; ++j)
+          tma2_load_2d(s_w + j * kHalfTap, &tmW, lead_w, 0, p.w_row0 + j * p.w_row_stride + static_cast<int>(rank) * (N / 2));
       }
     }
     __syncwarp();
@@ -220,9 +223,10 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint64_t by_desc_base = make_smem_desc_sw128(s_wy, 1024, 0);
       mbar_wait(b_w, 0);
       const long long c_start = clock64();
-      for (int i = mw; i < my_iters; i += kPairIssuers) {
-        const uint32_t acc = i % NB;
-        const uint32_t acc_ph = (i / NB) & 1;
+      for (int v = mw; v < my_iters * PH; v += kPairIssuers) {   // virtual tile v = PH * i + phase
+        const int i = v / PH, phase = v % PH;
+        const uint32_t acc = v % NB;
+        const uint32_t acc_ph = (v / NB) & 1;
         if (!(p.dbg & 8)) mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * kAccCols;
@@ -251,13 +255,14 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                 for (int tap = 0; tap < 9; ++tap) {
                   const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
-                  const uint64_t bdesc = b_desc_base + static_cast<uint64_t>(((wp * 9 + tap) * kHalfTap) >> 4);
+                  const uint64_t bdesc = b_desc_base + static_cast<uint64_t>((((PH == 4 ? phase : wp) * 9 + tap) * kHalfTap) >> 4);
                   umma2_f16_k64(d_tmem, adesc, bdesc, idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
                 }
                 first = 0;
               }
             }
-            umma2_commit_multicast(b_empty + 8 * s);  // frees this halo stage in both CTAs
+            // frees this halo stage in both CTAs (PH = 4: after this warp's last phase of the tile; both warps commit)
+            if (PH == 1 || phase >= PH - kPairIssuers) umma2_commit_multicast(b_empty + 8 * s);
             if (ap == p.n_act_parts - 1) umma2_commit_multicast(b_tfull + 8 * acc);
           }
           __syncwarp();
@@ -266,8 +271,9 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       if (p.dbg_cycles != nullptr && lane == 0 && my_iters > 0) {
         // wait for this warp's last accumulator so the count covers the execution of its MMAs
-        const int last = ((my_iters - 1 - mw) / kPairIssuers) * kPairIssuers + mw;
-        if (last >= 0 && last < my_iters) mbar_wait(b_tfull + 8 * (last % NB), (last / NB) & 1);
+        const int nv = my_iters * PH;
+        const int last = ((nv - 1 - mw) / kPairIssuers) * kPairIssuers + mw;
+        if (last >= 0 && last < nv) mbar_wait(b_tfull + 8 * (last % NB), (last / NB) & 1);
         p.dbg_cycles[pair_id + 128 * mw] = static_cast<unsigned long long>(clock64() - c_start);
       }
     }
@@ -275,17 +281,19 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ===================== epilogue warps: group g = warp/4 drains tiles g, g+G, ... =====================
     const int grp = warp >> 2, q = warp & 3;
     pdl_wait();   // addend reads / output writes must not overtake the previous kernel
-    for (int i = grp; i < my_iters; i += G) {
+    for (int v = grp; v < my_iters * PH; v += G) {
+      const int i = v / PH, phase = v % PH;
       const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
       const bool valid = t < p.num_tiles;
       const int tx = t % p.tiles_x;
       const int ty = (t / p.tiles_x) % p.tiles_y;
       const int b = valid ? t / (p.tiles_x * p.tiles_y) : 0;
-      const uint32_t acc = i % NB;
-      const uint32_t acc_ph = (i / NB) & 1;
+      const uint32_t acc = v % NB;
+      const uint32_t acc_ph = (v / NB) & 1;
       const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
       if constexpr (EPI == EPI_STORE16)
-        epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
+        epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph,
+                                   PH == 4 ? 2 : 1, PH == 4 ? (phase >> 1) : 0, PH == 4 ? (phase & 1) : 0);
       else
         epilogue_final<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
       tc_fence_before();

@@ -39,6 +39,14 @@ size_t inpaint_workspace_floats(int B, int h, int w);
 cudaError_t launch_inpaint_flow(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, float *ws,
                                 cudaStream_t s);
 
+// isr_up2.cu: fused bilinear-2x-upsample + conv support
+// out: [fmt 2 (bf16, fp16)][phase 4][tap 9][n 64][k 64] composite weights of a 64 -> 64 layer
+cudaError_t launch_pack_weights_up2(const float *w, uint16_t *out, cudaStream_t s);
+cudaError_t launch_band_upsample(const uint16_t *in, uint16_t *rows, uint16_t *cols, int B, int hl, int wl, int in_parts,
+                                 int is_bf16, cudaStream_t s);
+cudaError_t launch_band_scatter(const uint16_t *rows, const uint16_t *cols, uint16_t *out, int B, int H2, int W2, int parts,
+                                cudaStream_t s);
+
 // isr_ssao.cu: hemisphere kernel (<= 128 samples) and rotation noise (<= 8 x 8), passed by value to the kernel
 struct SsaoTables {
   float kernel[3 * 128];

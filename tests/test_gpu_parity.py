@@ -333,6 +333,7 @@ def test_cta_pair_kernel_equals_single_cta(isr, golden, weights, prec):
     x = cu(g["x"])
     outs = {}
     try:
+        _lib.set_tunable("fuse_up", 0)          # like for like: the fused upsample + conv exists in pair form only
         for pair in (1, 0):
             _lib.set_tunable("cta_pair", pair)
             net = _net(isr, weights)
@@ -341,6 +342,7 @@ def test_cta_pair_kernel_equals_single_cta(isr, golden, weights, prec):
                 outs[pair] = net(x)[0].clone()
     finally:
         _lib.set_tunable("cta_pair", 1)
+        _lib.set_tunable("fuse_up", 1)
     assert maxabs(outs[1], outs[0]) <= (6e-3 if prec in ("mixed", "hybrid") else 1e-4)
     if prec != "fp16":
         _check_net(outs[1], g["recon_bilinear"])
@@ -550,3 +552,34 @@ def test_full_size_crop_parity(isr, weights, cfg):
         with torch.no_grad():
             alone, _ = net(x[B - 1:B].contiguous())
         assert torch.equal(alone, recon[B - 1:B])
+
+
+@pytest.mark.parametrize("shape", [(1, 32, 48), (2, 19, 27), (1, 270, 480)])
+def test_fused_upsample_conv_equals_unfused(isr, weights, shape):
+    """conv3x3(bilinear_up2(x)) as four phase convolutions on the low-res tensor with composite weights + the four
+    border bands (isr_up2.cu, tunable fuse_up=1, default) against the materialised upsample + conv (fuse_up=0): same
+    layer up to operand rounding (the composite weights are rounded once, the unfused path rounds the upsampled
+    activations), everywhere including the 2-px border ring and ragged tiles; both meet the oracle bar."""
+    from isosurfacesuperresolution_b200 import _lib
+    B, h, w = shape
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.rand(B, 101, h, w, device="cuda", generator=g) * 2 - 1
+    outs = {}
+    try:
+        for fuse in (1, 0):
+            _lib.set_tunable("fuse_up", fuse)
+            net = _net(isr, weights)
+            with torch.no_grad():
+                outs[fuse] = net(x)[0].clone()
+    finally:
+        _lib.set_tunable("fuse_up", 1)
+    d = (outs[1] - outs[0]).abs()
+    assert float(d.max()) <= 6e-3
+    ring = torch.ones_like(d, dtype=torch.bool)
+    ring[:, :, 8:-8, 8:-8] = False
+    # the border is not worse than the interior (a wrong ring would be off by O(0.1))
+    assert float(d[ring].max()) <= 6e-3 and float(d[ring].mean()) <= 2 * float(d[~ring].mean()) + 1e-5
+    if h * w <= 2000:
+        ref, _ = orc.enhancenet_forward(weights, x.cpu().numpy(), "bilinear", "residual", 5, backend="torch")
+        _check_net(outs[1], ref)
+        _check_net(outs[0], ref)
