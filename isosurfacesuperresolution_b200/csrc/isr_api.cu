@@ -346,7 +346,7 @@ struct Layer {
   uint16_t *packed = nullptr;  // [fmt 2][part 2][tap 9][G][npad][64]
   float *bias = nullptr;       // npad floats, zero padded
   uint16_t *packed_fin = nullptr;  // output conv only: tap-stacked [fmt 2][part 2][nrows][64]
-  uint16_t *packed_up = nullptr;   // layer 22 only: composite weights of the fused upsample + conv [fmt 2][phase 4][tap 9][64][64]
+  uint16_t *packed_up = nullptr;   // layers 21, 22: composite weights of the fused upsample + conv [fmt 2][phase 4][tap 9][64][64]
   size_t per_fmt() const { return static_cast<size_t>(2) * 9 * G * npad * 64; }
   int rows() const { return 2 * 9 * G * npad; }
 };
@@ -363,9 +363,14 @@ struct Plan {
   uint16_t *f_last = nullptr, *u2 = nullptr, *c2 = nullptr, *u4 = nullptr, *c4 = nullptr;
   int idx_post1 = 0, idx_post4 = 0, idx_final = 0;
   // fused 4x upsample + conv (isr_up2.cu): the phase kernel, the two band convs and their buffers
-  int fuse4 = 0, fuse_up = 0;
-  ConvLaunch up4, band_r, band_c;
-  uint16_t *rows_in = nullptr, *cols_in = nullptr, *rows_out = nullptr, *cols_out = nullptr;
+  int fuse_up = 0;
+  struct Fused {
+    int on = 0, hl = 0, wl = 0, in_parts = 1;   // low-res size and stored planes of the input
+    const uint16_t *src = nullptr;
+    uint16_t *dst = nullptr;
+    ConvLaunch up, band_r, band_c;
+  } fuse2, fuse4;   // (upsample -> layers[21]) at 2x, (upsample -> layers[22]) at 4x
+  uint16_t *rows_in = nullptr, *cols_in = nullptr, *rows_out = nullptr, *cols_out = nullptr;   // shared by both
 };
 
 }  // namespace isr
@@ -498,20 +503,28 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   if ((rc = conv_for_layer(&L, net->layers[22], 0, pl->u4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
   set_store(&L, net->layers[22].bias, 1, nullptr, 0, pl->c4, Hs.na);
   pl->convs.push_back(L);
-  // fused form of (upsample 2x -> layers[22]): phase-decomposed kernel on c2 + the plain conv on four border bands
-  pl->fuse4 = 0;
-  if (g_fuse_up && g_cta_pair && net->upsample == ISR_UPSAMPLE_BILINEAR && Hs.na == 1 && Hs.nw == 1 && net->layers[22].packed_up != nullptr &&
-      2 * h >= 4 && 2 * w >= 4) {
-    const uint16_t *wu = net->layers[22].packed_up + (Hs.bf16 ? 0 : static_cast<size_t>(36) * 4096);
-    if ((rc = init_conv_up2(&pl->up4, pl->c2, B, 2 * h, 2 * w, Hs.na, wu, Hs.bf16)) != ISR_OK) return rc;
-    set_store(&pl->up4, net->layers[22].bias, 1, nullptr, 0, pl->c4, Hs.na);
-    pl->rows_in = at(9); pl->cols_in = at(10); pl->rows_out = at(11); pl->cols_out = at(12);
-    if ((rc = conv_for_layer(&pl->band_r, net->layers[22], 0, pl->rows_in, 2 * B, 3, 4 * w, Hs)) != ISR_OK) return rc;
-    set_store(&pl->band_r, net->layers[22].bias, 1, nullptr, 0, pl->rows_out, Hs.na);
-    if ((rc = conv_for_layer(&pl->band_c, net->layers[22], 0, pl->cols_in, 2 * B, 4 * h, 3, Hs)) != ISR_OK) return rc;
-    set_store(&pl->band_c, net->layers[22].bias, 1, nullptr, 0, pl->cols_out, Hs.na);
-    pl->fuse4 = 1;
-  }
+  // fused form of (upsample 2x -> conv): phase-decomposed kernel on the low-res tensor + the plain conv on four border
+  // bands.  At 2x the input is the trunk's last stream tensor: fused only when it is a single plane in the tail's format.
+  pl->fuse2.on = pl->fuse4.on = 0;
+  pl->rows_in = at(9); pl->cols_in = at(10); pl->rows_out = at(11); pl->cols_out = at(12);
+  auto build_fused = [&](Plan::Fused *f, const Layer &ly, const uint16_t *src, int in_parts, int hl, int wl,
+                         uint16_t *dst) -> int {
+    const uint16_t *wu = ly.packed_up + (Hs.bf16 ? 0 : static_cast<size_t>(36) * 4096);
+    int r;
+    if ((r = init_conv_up2(&f->up, src, B, hl, wl, in_parts, wu, Hs.bf16)) != ISR_OK) return r;
+    set_store(&f->up, ly.bias, 1, nullptr, 0, dst, Hs.na);
+    if ((r = conv_for_layer(&f->band_r, ly, 0, pl->rows_in, 2 * B, 3, 2 * wl, Hs)) != ISR_OK) return r;
+    set_store(&f->band_r, ly.bias, 1, nullptr, 0, pl->rows_out, Hs.na);
+    if ((r = conv_for_layer(&f->band_c, ly, 0, pl->cols_in, 2 * B, 2 * hl, 3, Hs)) != ISR_OK) return r;
+    set_store(&f->band_c, ly.bias, 1, nullptr, 0, pl->cols_out, Hs.na);
+    f->src = src; f->dst = dst; f->hl = hl; f->wl = wl; f->in_parts = in_parts; f->on = 1;
+    return ISR_OK;
+  };
+  const bool can_fuse = g_fuse_up && g_cta_pair && net->upsample == ISR_UPSAMPLE_BILINEAR && Hs.na == 1 && Hs.nw == 1;
+  if (can_fuse && net->layers[22].packed_up != nullptr && 2 * h >= 4 && 2 * w >= 4)
+    if ((rc = build_fused(&pl->fuse4, net->layers[22], pl->c2, Hs.na, 2 * h, 2 * w, pl->c4)) != ISR_OK) return rc;
+  if (can_fuse && net->layers[21].packed_up != nullptr && h >= 4 && w >= 4 && pl->f_last_parts == 1 && T.bf16 == Hs.bf16)
+    if ((rc = build_fused(&pl->fuse2, net->layers[21], pl->f_last, 1, h, w, pl->c2)) != ISR_OK) return rc;
   if ((rc = conv_for_layer(&L, net->layers[23], 0, pl->c4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
   set_store(&L, net->layers[23].bias, 1, nullptr, 0, pl->u4, Hs.na);
   pl->convs.push_back(L);
@@ -566,16 +579,17 @@ static int run_plan(isr_net *net, Plan *pl, const float *skip_src, long long ski
   const Scheme &T = pl->trunk, &Hs = pl->tail;
   int rc;
   for (int i = 0; i < static_cast<int>(pl->convs.size()); ++i) {
-    if (i == pl->idx_post1)
+    if (i == pl->idx_post1 && !pl->fuse2.on)
       ISR_CUDA(launch_upsample2x(pl->f_last, pl->u2, pl->B, pl->h, pl->w, pl->f_last_parts, Hs.na, T.bf16, Hs.bf16,
                                  net->upsample == ISR_UPSAMPLE_BILINEAR, s));
-    if (i == pl->idx_post4 && pl->fuse4) {
-      // conv3x3(bilinear_up2(c2)) without the upsampled tensor; then the 2-px border ring from the four bands
-      if ((rc = run_conv(pl->up4, s)) != ISR_OK) return rc;
-      ISR_CUDA(launch_band_upsample(pl->c2, pl->rows_in, pl->cols_in, pl->B, 2 * pl->h, 2 * pl->w, Hs.na, Hs.bf16, s));
-      if ((rc = run_conv(pl->band_r, s)) != ISR_OK) return rc;
-      if ((rc = run_conv(pl->band_c, s)) != ISR_OK) return rc;
-      ISR_CUDA(launch_band_scatter(pl->rows_out, pl->cols_out, pl->c4, pl->B, 4 * pl->h, 4 * pl->w, Hs.na, s));
+    if ((i == pl->idx_post1 && pl->fuse2.on) || (i == pl->idx_post4 && pl->fuse4.on)) {
+      // conv3x3(bilinear_up2(x)) without the upsampled tensor; then the 2-px border ring from the four bands
+      const Plan::Fused &f = i == pl->idx_post1 ? pl->fuse2 : pl->fuse4;
+      if ((rc = run_conv(f.up, s)) != ISR_OK) return rc;
+      ISR_CUDA(launch_band_upsample(f.src, pl->rows_in, pl->cols_in, pl->B, f.hl, f.wl, f.in_parts, Hs.bf16, s));
+      if ((rc = run_conv(f.band_r, s)) != ISR_OK) return rc;
+      if ((rc = run_conv(f.band_c, s)) != ISR_OK) return rc;
+      ISR_CUDA(launch_band_scatter(pl->rows_out, pl->cols_out, f.dst, pl->B, 2 * f.hl, 2 * f.wl, Hs.na, s));
       continue;
     }
     if (i == pl->idx_post4)
@@ -858,10 +872,11 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
       return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
     }
   }
-  if (cudaMalloc(&net->layers[22].packed_up, static_cast<size_t>(2) * 36 * 4096 * sizeof(uint16_t)) != cudaSuccess) {
-    isr_net_destroy(net);
-    return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
-  }
+  for (int i = 21; i <= 22; ++i)
+    if (cudaMalloc(&net->layers[i].packed_up, static_cast<size_t>(2) * 36 * 4096 * sizeof(uint16_t)) != cudaSuccess) {
+      isr_net_destroy(net);
+      return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
+    }
   if (output_channels <= 8) {
     const int nrows = final_rows(final_cp(output_channels));
     if (cudaMalloc(&net->layers[24].packed_fin, static_cast<size_t>(4) * nrows * 64 * sizeof(uint16_t)) != cudaSuccess) {
