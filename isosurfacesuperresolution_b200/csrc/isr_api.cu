@@ -32,6 +32,7 @@ static int g_final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (meas
                                   // 0 = generic single-CTA N=16 kernel
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
 static int g_fuse_up = 1;   // bilinear nets: the 4x upsample + first 4x conv run as one phase-decomposed kernel (isr_up2.cu)
+static int g_final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
 static int g_pdl = 1;   // CTA-pair convs are launched with programmatic stream serialization (prologue overlaps the previous tail)
 static int g_trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
 
@@ -236,7 +237,7 @@ static int final_rows(int cp) { return (9 * cp + 15) / 16 * 16; }
 static size_t final_pbytes(int cp) {
   const int ld = (9 * cp + 7) / 8 * 8;
   const int pitch4 = ((ld / 4) % 2 == 0) ? ld / 4 + 1 : ld / 4;
-  return align_up(static_cast<size_t>(kPitch) * kHaloH * pitch4 * 16, 1024);
+  return align_up(static_cast<size_t>(kPitch) * kHaloH * pitch4 * 16 + 6 * 4 * 8 * 4, 1024);   // gather buffer + skip patch
 }
 
 // tap-stacked output conv: wpacked = [part 2][nrows][64] of the chosen format
@@ -262,6 +263,11 @@ static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H,
   int stages = static_cast<int>((kSmemLimit - kStaticSmem - fixed) / p.stage_bytes);
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "final conv smem plan: fewer than 2 halo stages fit");
+  p.issuers = 1;
+  if (g_final_issuers == 3 && stages >= kFinalIssuers * n_act_parts) {   // three issuing warps need every stage to belong to one of them
+    stages -= stages % (kFinalIssuers * n_act_parts);
+    p.issuers = kFinalIssuers;
+  }
   p.num_stages = stages;
   L->smem = fixed + static_cast<size_t>(stages) * p.stage_bytes;
   int cap = g_max_ctas > 0 ? g_max_ctas : num_sms();
@@ -363,7 +369,7 @@ struct Plan {
   uint16_t *f_last = nullptr, *u2 = nullptr, *c2 = nullptr, *u4 = nullptr, *c4 = nullptr;
   int idx_post1 = 0, idx_post4 = 0, idx_final = 0;
   // fused 4x upsample + conv (isr_up2.cu): the phase kernel, the two band convs and their buffers
-  int fuse_up = 0;
+  int fuse_up = 0, fin_issuers = 0;
   struct Fused {
     int on = 0, hl = 0, wl = 0, in_parts = 1;   // low-res size and stored planes of the input
     const uint16_t *src = nullptr;
@@ -443,6 +449,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w; pl->cta_pair = g_cta_pair;
   pl->full_blocks = g_trunk_full_blocks;
   pl->fuse_up = g_fuse_up;
+  pl->fin_issuers = g_final_issuers;
   uint8_t *base = static_cast<uint8_t *>(ws);
   auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
   const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
@@ -554,7 +561,7 @@ static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision
     if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
         pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
         pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair &&
-        pl->full_blocks == g_trunk_full_blocks && pl->fuse_up == g_fuse_up) {
+        pl->full_blocks == g_trunk_full_blocks && pl->fuse_up == g_fuse_up && pl->fin_issuers == g_final_issuers) {
       *out = pl;
       return ISR_OK;
     }
@@ -659,6 +666,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "fuse_up") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "fuse_up must be 0 or 1");
     slot = &g_fuse_up;
+  } else if (key != nullptr && strcmp(key, "final_issuers") == 0) {
+    if (value != 1 && value != 3) return fail(ISR_ERR_ARG, "final_issuers must be 1 or 3");
+    slot = &g_final_issuers;
   } else if (key != nullptr && strcmp(key, "pdl") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "pdl must be 0 or 1");
     slot = &g_pdl;
@@ -1105,12 +1115,21 @@ void isr_pipe_destroy(isr_pipe *p) {
 
 int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scale, void *workspace,
                       size_t workspace_bytes, int iters, float *ms, void *stream) {
-  if (ms == nullptr || iters <= 0 || (scale != 1 && scale != 4)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");
+  if (ms == nullptr || iters <= 0 || (scale != 1 && scale != 4 && scale != 5)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");
   Plan *pl = nullptr;
   int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
   if (rc != ISR_OK) return rc;
   // scale 4: postblock.4 (64->64 at 4h x 4w, the dominant kernel); scale 1: first residual-block conv (h x w)
-  ConvLaunch L = pl->convs[scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1)];
+  // scale 5: the output conv, writing into scratch (c4) with the packed-input buffer standing in for the skip source
+  ConvLaunch L = pl->convs[scale == 5 ? pl->idx_final : (scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1))];
+  if (scale == 5) {
+    const size_t n_out = static_cast<size_t>(B) * net->cout * 16 * h * w;
+    L.p.out_recon = reinterpret_cast<float *>(pl->c4);
+    L.p.out_state = reinterpret_cast<float *>(pl->c4) + n_out;
+    L.p.state_unshaded = net->cout == 6;
+    L.p.skip_src = reinterpret_cast<const float *>(pl->in_g[0]);
+    L.p.skip_bstride = static_cast<long long>(net->n_mask > 0 ? net->n_mask : 1) * h * w;
+  }
   L.p.dbg = g_dbg;
   unsigned long long *cyc = nullptr;
   if (g_dbg & 32) {   // bench experiment: cycles of the MMA issue loop (clock64 in the issuing warp)

@@ -42,6 +42,7 @@ struct ConvParams {
   int w_row0;            // first row of this launch's weights inside the weight tensor map
   int w_row_stride;      // rows between consecutive (part, tap) blocks
   int num_stages, stage_bytes;
+  int issuers;           // conv3x3_final_kernel: MMA-issuing warps in use (1 | 3)
   int dbg;               // bench experiments only: bit0 = epilogue does not store, bit1 = no MMAs are issued,
                          // bit2 = epilogue only does the barrier handshake, bit3 = MMA warp does not wait for the epilogue,
                          // bit4 = the TMA producer fills each halo stage once and only signals afterwards (pair kernel)

@@ -18,7 +18,8 @@
 namespace isr {
 
 constexpr int kFinalGroups = 3;                                   // epilogue groups of four warps
-constexpr int kFinalThreads = (4 * kFinalGroups + 2) * 32;        // + TMA producer warp + MMA issuer warp
+constexpr int kFinalIssuers = kFinalGroups;                       // MMA-issuing warps: warp m issues tiles m, m+G, ... into buffer m
+constexpr int kFinalThreads = (4 * kFinalGroups + 1 + kFinalIssuers) * 32;   // + TMA producer warp + MMA issuer warps
 
 template <int CP>
 struct FinalCfg {
@@ -27,7 +28,9 @@ struct FinalCfg {
   static constexpr int kLd = (kCols + 7) / 8 * 8;            // columns fetched from TMEM (x8 loads)
   static constexpr int kPitch4 = ((kLd / 4) % 2 == 0) ? kLd / 4 + 1 : kLd / 4;   // odd number of 16 B units: conflict-free
   static constexpr int kPPitch = kPitch4 * 4;                // floats per halo row in the gather buffer
-  static constexpr int kPBytes = ((kPitch * kHaloH * kPPitch * 4) + 1023) / 1024 * 1024;
+  static constexpr int kSkipFloats = 6 * 4 * 8;              // low-res skip patch of a tile: 6 rows x 4 cols x <= 8 channels
+  static constexpr int kPFloats = kPitch * kHaloH * kPPitch;  // gather buffer proper; the skip patch follows it
+  static constexpr int kPBytes = ((kPFloats + kSkipFloats) * 4 + 1023) / 1024 * 1024;
   static constexpr uint32_t kTmemCols = (2 * kFinalGroups * kN <= 256) ? 256 : 512;   // one accumulator pair per group
 };
 
@@ -117,20 +120,23 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         __syncwarp();
       }
     }
-  } else if (warp == kMmaWarp) {
-    // ===================== MMA issuer =====================
+  } else if (warp >= kMmaWarp) {
+    // ===================== MMA issuers: one warp per accumulator buffer (p.issuers = 3), so the per-tile bookkeeping of
+    // one warp (barrier waits, commits) hides behind the MMAs of the others -- see isr_conv_pair.cuh.  p.issuers = 1 when
+    // the stage count is not a multiple of 3 * n_act_parts (a stage must always be consumed by the same warp).
+    const int mw = warp - kMmaWarp;
     const uint32_t idesc = make_idesc_f16(128, N, p.is_bf16);
     const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
     mbar_wait(b_w, 0);
-    uint32_t it = 0;
-    for (int i = 0; i < my_tiles; ++i) {
+    for (int i = mw; i < my_tiles && mw < p.issuers; i += p.issuers) {
       const uint32_t acc = i % kFinalGroups;
       const uint32_t acc_ph = (i / kFinalGroups) & 1;
       mbar_wait(b_tempty + 8 * acc, acc_ph ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * (2 * N);
       uint32_t first = 1;
-      for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+      for (int ap = 0; ap < p.n_act_parts; ++ap) {
+        const uint32_t it = static_cast<uint32_t>(i) * p.n_act_parts + ap;
         const uint32_t s = it % p.num_stages;
         const uint32_t ph = (it / p.num_stages) & 1;
         mbar_wait(b_full + 8 * s, ph);
@@ -171,32 +177,41 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const int py = row >> 3, px = row & 7;
       const int y = ty * kTileH + py, x = tx * kTileW + px;
       const bool inb = (y < p.H) && (x < p.W);
-      // skip taps do not depend on the accumulator: fetch them before waiting for the MMAs
-      // only the LOADS are issued here; the interpolation happens after the gather, so their latency hides behind it
+      // Skip connection (_recon_image, enhancenet.py:67-71): the 4x bilinear / nearest upsample of the low-res input.
+      // A tile's 8 x 16 pixels read a 4 x 6 low-res patch per channel: the group stages it in shared memory (one or two
+      // loads per thread, issued before the accumulator wait; visible after the barrier between phases A and B) instead
+      // of 24 scattered global loads per thread.  Patch origin: (4 ty - 1, 2 tx - 1), indices clamped like bil_src.
       float lx0 = 1.f, lx1 = 0.f, ly0 = 1.f, ly1 = 0.f;
-      float t00[CP], t01[CP], t10[CP], t11[CP];
+      int pr0 = 0, pr1 = 0, pc0 = 0, pc1 = 0;   // patch rows / columns of this pixel's taps
+      float *S = P + C::kPFloats;
+      float sv[2] = {0.f, 0.f};
+      int n_skip = 0;
+      const bool want_skip = p.recon_residual && !(p.dbg & 128);   // dbg bit7: bench experiment without the skip
+      if (want_skip) {
+        const int by = 4 * ty - 1, bx = 2 * tx - 1;
+        const int nm = p.n_mask > 0 ? (p.n_mask < 8 ? p.n_mask : 8) : 1;
+        n_skip = nm * 24;
+        // the loads go to REGISTERS here and to shared memory only after phase A: a store to S right away would make the
+        // warp wait for the load (queued behind the previous tile's output stores) before it can start draining TMEM
 #pragma unroll
-      for (int c = 0; c < CP; ++c) t00[c] = t01[c] = t10[c] = t11[c] = 0.f;
-      if (inb && p.recon_residual) {
+        for (int k = 0; k < 2; ++k) {
+          const int e = row + 128 * k;
+          if (e < nm * 24) {
+            const int c = e / 24, r = (e % 24) >> 2, cc = e & 3;
+            const int yy = min(max(by + r, 0), p.h_low - 1), xx = min(max(bx + cc, 0), p.w_low - 1);
+            sv[k] = __ldg(p.skip_src + b * p.skip_bstride + (static_cast<size_t>(c) * p.h_low + yy) * p.w_low + xx);
+          }
+        }
         int x0, x1, y0, y1;
         if (p.upsample == 1) {
           bil_src(x, p.w_low, 0.25f, x0, x1, lx0, lx1);
           bil_src(y, p.h_low, 0.25f, y0, y1, ly0, ly1);
         } else {
-          x0 = x1 = x >> 2;
-          y0 = y1 = y >> 2;
+          x0 = x1 = min(x >> 2, p.w_low - 1);
+          y0 = y1 = min(y >> 2, p.h_low - 1);
         }
-        const int o00 = y0 * p.w_low + x0, o01 = y0 * p.w_low + x1, o10 = y1 * p.w_low + x0, o11 = y1 * p.w_low + x1;
-        const int nm = p.n_mask > 0 ? p.n_mask : 1;
-#pragma unroll
-        for (int c = 0; c < CP; ++c) {
-          const int cc = c < nm ? c : nm - 1;
-          const float *sp = p.skip_src + b * p.skip_bstride + static_cast<size_t>(cc) * p.h_low * p.w_low;
-          t00[c] = __ldg(sp + o00);
-          t01[c] = __ldg(sp + o01);
-          t10[c] = __ldg(sp + o10);
-          t11[c] = __ldg(sp + o11);
-        }
+        pr0 = min(max(y0 - by, 0), 5); pr1 = min(max(y1 - by, 0), 5);
+        pc0 = min(max(x0 - bx, 0), 3); pc1 = min(max(x1 - bx, 0), 3);
       }
       mbar_wait(b_tfull + 8 * acc, acc_ph);
       tc_fence_after();
@@ -225,6 +240,8 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           }
         }
       }
+      if (row < n_skip) S[row] = sv[0];
+      if (row + 128 < n_skip) S[row + 128] = sv[1];
       // the accumulator buffer is free as soon as it is in shared memory
       tc_fence_before();
       __syncwarp();
@@ -244,41 +261,43 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           rec[2 * c2 + 1] += f.y;
         }
       }
-      if (inb) {
+      if (inb && !((p.dbg & 64) && rec[0] != 12345.678f)) {   // dbg bit6: bench experiment without the global stores
         const size_t plane = static_cast<size_t>(p.H) * p.W;
         const size_t o0 = static_cast<size_t>(b) * p.cout * plane + static_cast<size_t>(y) * p.W + x;
 #pragma unroll
         for (int c = 0; c < CP; ++c) {
           if (c < p.cout) {
             const float raw = rec[c];
-            if (p.out_raw != nullptr) p.out_raw[o0 + c * plane] = raw;
-            if (p.recon_residual && c < p.n_mask) {
+            if (p.out_raw != nullptr) __stcs(p.out_raw + o0 + c * plane, raw);
+            if (want_skip && c < p.n_mask) {
               // _recon_image (enhancenet.py:67-71): bilinear (x first, then y) or nearest 4x skip + raw
-              const float r0 = fmaf(lx0, t00[c], lx1 * t01[c]);
-              const float r1 = fmaf(lx0, t10[c], lx1 * t11[c]);
-              rec[c] = (p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00[c]) + raw;
+              const float *sc = S + c * 24;
+              const float t00 = sc[pr0 * 4 + pc0], t01 = sc[pr0 * 4 + pc1], t10 = sc[pr1 * 4 + pc0], t11 = sc[pr1 * 4 + pc1];
+              const float r0 = fmaf(lx0, t00, lx1 * t01);
+              const float r1 = fmaf(lx0, t10, lx1 * t11);
+              rec[c] = (p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00) + raw;
             }
-            if (p.out_recon != nullptr) p.out_recon[o0 + c * plane] = rec[c];
+            if (p.out_recon != nullptr) __stcs(p.out_recon + o0 + c * plane, rec[c]);
           }
         }
         if (p.out_state != nullptr) {
           if (p.state_unshaded && p.cout >= 5) {
             if constexpr (CP >= 6) {
               // mainVideoUnshaded.py:460-465: clamp mask, normalise normal (shading.py:193-207), clamp depth / ao
-              p.out_state[o0] = fminf(fmaxf(rec[0], -1.f), 1.f);
+              __stcs(p.out_state + o0, fminf(fmaxf(rec[0], -1.f), 1.f));
               float len = sqrtf(rec[1] * rec[1] + rec[2] * rec[2] + rec[3] * rec[3]);
               len = fmaxf(len, 1e-7f);
-              p.out_state[o0 + plane] = rec[1] / len;
-              p.out_state[o0 + 2 * plane] = rec[2] / len;
-              p.out_state[o0 + 3 * plane] = rec[3] / len;
+              __stcs(p.out_state + o0 + plane, rec[1] / len);
+              __stcs(p.out_state + o0 + 2 * plane, rec[2] / len);
+              __stcs(p.out_state + o0 + 3 * plane, rec[3] / len);
 #pragma unroll
               for (int c = 4; c < CP; ++c)
-                if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+                if (c < p.cout) __stcs(p.out_state + o0 + c * plane, fminf(fmaxf(rec[c], 0.f), 1.f));
             }
           } else {
 #pragma unroll
             for (int c = 0; c < CP; ++c)
-              if (c < p.cout) p.out_state[o0 + c * plane] = fminf(fmaxf(rec[c], 0.f), 1.f);
+              if (c < p.cout) __stcs(p.out_state + o0 + c * plane, fminf(fmaxf(rec[c], 0.f), 1.f));
           }
         }
       }
