@@ -249,8 +249,8 @@ static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H,
   L->cp = cp;
   ConvParams &p = L->p;
   p.B = B; p.H = H; p.W = W;
-  p.tiles_x = (W + kTileW - 1) / kTileW;
-  p.tiles_y = (H + kTileH - 1) / kTileH;
+  p.tiles_x = (W + kFTileW - 1) / kFTileW;
+  p.tiles_y = (H + kFTileH - 1) / kFTileH;
   p.num_tiles = p.tiles_x * p.tiles_y * B;
   p.n_act_parts = n_act_parts;
   p.n_w_parts = n_w_parts;
@@ -258,7 +258,7 @@ static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H,
   p.w_row0 = 0;
   p.w_row_stride = nrows;
   const size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * nrows * 128, 1024);
-  p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kPitch) * kHaloH * 128, 1024));
+  p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kFPitch) * kFHaloH * 128, 1024));
   const size_t fixed = 1024 + w_bytes + kFinalGroups * final_pbytes(cp) + 256;
   int stages = static_cast<int>((kSmemLimit - kStaticSmem - fixed) / p.stage_bytes);
   if (stages > 8) stages = 8;
@@ -272,7 +272,7 @@ static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H,
   L->smem = fixed + static_cast<size_t>(stages) * p.stage_bytes;
   int cap = g_max_ctas > 0 ? g_max_ctas : num_sms();
   L->grid = p.num_tiles < cap ? p.num_tiles : cap;
-  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kPitch, kHaloH, is_bf16);
+  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kFPitch, kFHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
   return make_w_map(&L->tmW, wpacked, 2 * nrows, nrows, is_bf16);
 }

@@ -17,6 +17,11 @@
 
 namespace isr {
 
+// Tile of the output conv: 16 px wide x 8 rows (the hidden layers use 8 x 16): its outputs are fp32 NCHW planes, and a
+// 16-px row segment is 64 B = one HBM burst, where the 8-px segment (32 B) cost 0.3 ms of the launch in partial bursts
+// (tools/final_experiments.py).  Same 180 halo rows (18 x 10), same two M=128 row groups.
+constexpr int kFTileW = 16, kFTileH = 8, kFPitch = kFTileW + 2, kFHaloH = kFTileH + 2;
+static_assert(kFPitch * kFHaloH == 180, "the two MMA row groups (0..127, 52..179) assume 180 halo rows");
 constexpr int kFinalGroups = 3;                                   // epilogue groups of four warps
 constexpr int kFinalIssuers = kFinalGroups;                       // MMA-issuing warps: warp m issues tiles m, m+G, ... into buffer m
 constexpr int kFinalThreads = (4 * kFinalGroups + 1 + kFinalIssuers) * 32;   // + TMA producer warp + MMA issuer warps
@@ -29,7 +34,7 @@ struct FinalCfg {
   static constexpr int kPitch4 = ((kLd / 4) % 2 == 0) ? kLd / 4 + 1 : kLd / 4;   // odd number of 16 B units: conflict-free
   static constexpr int kPPitch = kPitch4 * 4;                // floats per halo row in the gather buffer
   static constexpr int kSkipFloats = 6 * 4 * 8;              // low-res skip patch of a tile: 6 rows x 4 cols x <= 8 channels
-  static constexpr int kPFloats = kPitch * kHaloH * kPPitch;  // gather buffer proper; the skip patch follows it
+  static constexpr int kPFloats = kFPitch * kFHaloH * kPPitch;  // gather buffer proper; the skip patch follows it
   static constexpr int kPBytes = ((kPFloats + kSkipFloats) * 4 + 1023) / 1024 * 1024;
   static constexpr uint32_t kTmemCols = (2 * kFinalGroups * kN <= 256) ? 256 : 512;   // one accumulator pair per group
 };
@@ -114,8 +119,8 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const uint32_t ph = (it / p.num_stages) & 1;
         mbar_wait(b_empty + 8 * s, ph ^ 1);
         if (elect_one()) {
-          mbar_arrive_expect_tx(b_full + 8 * s, kPitch * kHaloH * 128);
-          tma_load_4d(s_stage0 + s * p.stage_bytes, &tmA, b_full + 8 * s, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
+          mbar_arrive_expect_tx(b_full + 8 * s, kFPitch * kFHaloH * 128);
+          tma_load_4d(s_stage0 + s * p.stage_bytes, &tmA, b_full + 8 * s, ap * 64, tx * kFTileW - 1, ty * kFTileH - 1, b);
         }
         __syncwarp();
       }
@@ -174,13 +179,13 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const uint32_t acc_ph = (i / kFinalGroups) & 1;
       const uint32_t taddr = tmem_base + acc * (2 * N) + (static_cast<uint32_t>(q * 32) << 16);
       const int row = q * 32 + lane;   // output pixel of this thread inside the tile
-      const int py = row >> 3, px = row & 7;
-      const int y = ty * kTileH + py, x = tx * kTileW + px;
+      const int py = row >> 4, px = row & 15;   // a warp = two 16-px rows = two 64-byte segments per plane
+      const int y = ty * kFTileH + py, x = tx * kFTileW + px;
       const bool inb = (y < p.H) && (x < p.W);
       // Skip connection (_recon_image, enhancenet.py:67-71): the 4x bilinear / nearest upsample of the low-res input.
-      // A tile's 8 x 16 pixels read a 4 x 6 low-res patch per channel: the group stages it in shared memory (one or two
+      // A tile's 16 x 8 pixels read a 6 x 4 (cols x rows) low-res patch per channel: the group stages it in shared memory (one or two
       // loads per thread, issued before the accumulator wait; visible after the barrier between phases A and B) instead
-      // of 24 scattered global loads per thread.  Patch origin: (4 ty - 1, 2 tx - 1), indices clamped like bil_src.
+      // of 24 scattered global loads per thread.  Patch origin: row 2 ty - 1, column 4 tx - 1, indices clamped like bil_src.
       float lx0 = 1.f, lx1 = 0.f, ly0 = 1.f, ly1 = 0.f;
       int pr0 = 0, pr1 = 0, pc0 = 0, pc1 = 0;   // patch rows / columns of this pixel's taps
       float *S = P + C::kPFloats;
@@ -188,7 +193,7 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       int n_skip = 0;
       const bool want_skip = p.recon_residual && !(p.dbg & 128);   // dbg bit7: bench experiment without the skip
       if (want_skip) {
-        const int by = 4 * ty - 1, bx = 2 * tx - 1;
+        const int by = 2 * ty - 1, bx = 4 * tx - 1;
         const int nm = p.n_mask > 0 ? (p.n_mask < 8 ? p.n_mask : 8) : 1;
         n_skip = nm * 24;
         // the loads go to REGISTERS here and to shared memory only after phase A: a store to S right away would make the
@@ -197,7 +202,7 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         for (int k = 0; k < 2; ++k) {
           const int e = row + 128 * k;
           if (e < nm * 24) {
-            const int c = e / 24, r = (e % 24) >> 2, cc = e & 3;
+            const int c = e / 24, r = (e % 24) / 6, cc = (e % 24) % 6;
             const int yy = min(max(by + r, 0), p.h_low - 1), xx = min(max(bx + cc, 0), p.w_low - 1);
             sv[k] = __ldg(p.skip_src + b * p.skip_bstride + (static_cast<size_t>(c) * p.h_low + yy) * p.w_low + xx);
           }
@@ -210,8 +215,8 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           x0 = x1 = min(x >> 2, p.w_low - 1);
           y0 = y1 = min(y >> 2, p.h_low - 1);
         }
-        pr0 = min(max(y0 - by, 0), 5); pr1 = min(max(y1 - by, 0), 5);
-        pc0 = min(max(x0 - bx, 0), 3); pc1 = min(max(x1 - bx, 0), 3);
+        pr0 = min(max(y0 - by, 0), 3); pr1 = min(max(y1 - by, 0), 3);
+        pc0 = min(max(x0 - bx, 0), 5); pc1 = min(max(x1 - bx, 0), 5);
       }
       mbar_wait(b_tfull + 8 * acc, acc_ph);
       tc_fence_after();
@@ -253,7 +258,7 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       for (int c = 0; c < CP; ++c) rec[c] = s_bias[c];
 #pragma unroll
       for (int tap = 0; tap < 9; ++tap) {
-        const float *src = P + static_cast<size_t>((py + tap / 3) * kPitch + px + tap % 3) * C::kPPitch + tap * CP;
+        const float *src = P + static_cast<size_t>((py + tap / 3) * kFPitch + px + tap % 3) * C::kPPitch + tap * CP;
 #pragma unroll
         for (int c2 = 0; c2 < CP / 2; ++c2) {
           const float2 f = *reinterpret_cast<const float2 *>(src + 2 * c2);
@@ -272,7 +277,7 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
             if (want_skip && c < p.n_mask) {
               // _recon_image (enhancenet.py:67-71): bilinear (x first, then y) or nearest 4x skip + raw
               const float *sc = S + c * 24;
-              const float t00 = sc[pr0 * 4 + pc0], t01 = sc[pr0 * 4 + pc1], t10 = sc[pr1 * 4 + pc0], t11 = sc[pr1 * 4 + pc1];
+              const float t00 = sc[pr0 * 6 + pc0], t01 = sc[pr0 * 6 + pc1], t10 = sc[pr1 * 6 + pc0], t11 = sc[pr1 * 6 + pc1];
               const float r0 = fmaf(lx0, t00, lx1 * t01);
               const float r1 = fmaf(lx0, t10, lx1 * t11);
               rec[c] = (p.upsample == 1 ? fmaf(ly0, r0, ly1 * r1) : t00) + raw;
