@@ -233,6 +233,23 @@ def run_b200(args, rank, world, local_rank):
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e_value = world * out_px_per_step * e2e_steps / float(dt.item()) / 1e6
         e2e_checksum = float(recon_h[(e2e_steps - 1) % 3].double().abs().mean())
+        # the same pipeline in its display form: the host receives the shaded 8-bit RGB frame (what the reference's GUI /
+        # video writers consume, mainGUI.py:507) instead of the fp32 prediction: 3 instead of 24 bytes per output pixel
+        pipe.enable_display(shd.params22())
+        rgb_h = [torch.empty((B, H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(3)]
+        for j in range(2):
+            pipe.submit_display(low_h[j % nbuf], flow_h[j % nbuf], rgb_h[j % 3])
+        pipe.wait()
+        sync_all()
+        t0 = time.perf_counter()
+        for j in range(e2e_steps):
+            pipe.submit_display(low_h[j % nbuf], flow_h[j % nbuf], rgb_h[j % 3])
+        pipe.wait()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e_display_value = world * out_px_per_step * e2e_steps / float(dt.item()) / 1e6
+        e2e_display_checksum = float(rgb_h[(e2e_steps - 1) % 3].double().mean())
         pipe.close()
         h2d = B * 7 * h * w * 4
         d2h = B * 6 * H * W * 4
@@ -376,7 +393,10 @@ def run_b200(args, rank, world, local_rank):
                 "steps": e2e_steps, "api": "isr_pipe_submit / isr_pipe_wait, depth 2 (pinned host buffers; copies of "
                                              "neighbouring frames overlap the kernels)",
                 "serialised_value": e2e_sync_value, "serialised_api": "isr_net_forward_recurrent_host",
-                "output_checksum": e2e_checksum},
+                "output_checksum": e2e_checksum,
+                "display": {"value": e2e_display_value, "unit": UNIT, "d2h_bytes_per_step": B * H * W * 3,
+                            "api": "isr_pipe_submit_display: the host result is the shaded 8-bit RGB frame (B x H x W x 3)",
+                            "output_checksum": e2e_display_checksum}},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",

@@ -89,6 +89,12 @@ int isr_postprocess(const float *in, float *out, int B, int C, int H, int W, int
  * gbuf: B x C x H x W (C>=5: mask,nx,ny,nz,depth[,ao]), rgb: B x 3 x H x W. */
 int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, int C, int H, int W, void *stream);
 
+/* isr_shade straight to the display format: rgb8 = B x H x W x 3 interleaved bytes, uint8(clip(rgb * 255, 0, 255)), the
+ * conversion mainGUI.py:507 / mainComparisonVideo3.py:589 do on the host after copying the fp32 frame back (12 B/px
+ * instead of 3).  H * W must be a multiple of 4; gbuf 16-byte aligned. */
+int isr_shade_rgb8(const float *gbuf, const float *params_host, unsigned char *rgb8, int B, int C, int H, int W,
+                   void *stream);
+
 /* GUI / video composition (mainGUI.py:603-608,615-636; mainComparisonVideo3.py:540-556): bilinear x4 of the c_low-channel
  * low-res render (RGB, mask, normal, depth, flow, AO, shadow: c_low >= 12 for the unshaded form, >= 4 otherwise);
  * unshaded != 0: channels 0:3 = shading(pred), 3:8 = pred[0:5], 10 = pred[5] (pred = post-processed state, c_pred 5|6);
@@ -201,6 +207,12 @@ int isr_pipe_create(isr_pipe **pipe, isr_net *net, int c_low, int c_prev, int sp
  * initialImage(low, c_prev, initial_mode).  recon_host (B x Cout x 4h x 4w) is complete after isr_pipe_wait(). */
 int isr_pipe_submit(isr_pipe *pipe, const float *low_host, const float *flow_host, float *recon_host);
 /* Blocks until every submitted frame's prediction is in host memory (and the state is final on the device). */
+/* Display form of the pipeline: after isr_pipe_enable_display (shading parameters as isr_shade; rgb8_staging_dev: depth x
+ * B x 4h x 4w x 3 bytes on the device) isr_pipe_submit_display enqueues a frame whose host-side result is the shaded
+ * 8-bit RGB frame (B x 4h x 4w x 3, what the GUI / video writers of the reference consume) instead of the fp32
+ * prediction: 3 instead of 24 bytes per output pixel cross PCIe; the prediction itself is not written at all. */
+int isr_pipe_enable_display(isr_pipe *pipe, const float *params_host, unsigned char *rgb8_staging_dev, size_t bytes);
+int isr_pipe_submit_display(isr_pipe *pipe, const float *low_host, const float *flow_host, unsigned char *rgb8_host);
 int isr_pipe_wait(isr_pipe *pipe);
 void isr_pipe_destroy(isr_pipe *pipe);
 

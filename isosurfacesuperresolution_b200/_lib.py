@@ -57,6 +57,9 @@ SIGNATURES = {
     "isr_pipe_staging_floats": (_i, [_vp, _i, _i, _i, _i, _i, _c.POINTER(_sz)]),
     "isr_pipe_create": (_i, [_c.POINTER(_vp), _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp, _vp, _sz, _i]),
     "isr_pipe_submit": (_i, [_vp, _vp, _vp, _vp]),
+    "isr_pipe_enable_display": (_i, [_vp, _c.POINTER(_c.c_float), _vp, _sz]),
+    "isr_pipe_submit_display": (_i, [_vp, _vp, _vp, _vp]),
+    "isr_shade_rgb8": (_i, [_vp, _c.POINTER(_c.c_float), _vp, _i, _i, _i, _i, _vp]),
     "isr_pipe_wait": (_i, [_vp]),
     "isr_pipe_destroy": (None, [_vp]),
     "isr_debug_conv3x3": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),

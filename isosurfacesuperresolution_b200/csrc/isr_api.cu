@@ -734,6 +734,19 @@ int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, in
   return ISR_OK;
 }
 
+int isr_shade_rgb8(const float *gbuf, const float *params_host, unsigned char *rgb8, int B, int C, int H, int W,
+                   void *stream) {
+  if (gbuf == nullptr || params_host == nullptr || rgb8 == nullptr || B <= 0 || H <= 0 || W <= 0)
+    return fail(ISR_ERR_ARG, "shade_rgb8: bad arguments");
+  if (C < 5) return fail(ISR_ERR_ARG, "shade_rgb8: input must have at least 5 channels (shading.py:150)");
+  if ((static_cast<size_t>(H) * W) % 4 != 0 || reinterpret_cast<uintptr_t>(gbuf) % 16 != 0 || reinterpret_cast<uintptr_t>(rgb8) % 4 != 0)
+    return fail(ISR_ERR_UNSUPPORTED, "shade_rgb8: H*W must be a multiple of 4 and the buffers 16 / 4 byte aligned");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_shade_rgb8(gbuf, params_host, rgb8, B, C, H, W, S(stream)));
+  return ISR_OK;
+}
+
 int isr_compose(const float *low, const float *pred, const float *params_host, float *out, int B, int c_low, int c_pred,
                 int h, int w, int unshaded, int masking, float background0, void *stream) {
   if (low == nullptr || pred == nullptr || out == nullptr || B <= 0 || h <= 0 || w <= 0)
@@ -1014,6 +1027,11 @@ struct isr_pipe {
   cudaStream_t s_in = nullptr, s_comp = nullptr, s_out = nullptr;
   std::vector<cudaEvent_t> ev_in, ev_comp, ev_out;
   uint64_t submitted = 0;
+  // display form: shaded 8-bit RGB frames leave the device instead of the fp32 prediction
+  bool display = false;
+  float shade_params[22] = {0};
+  unsigned char *rgb8 = nullptr;
+  size_t n_rgb8 = 0;
 };
 
 extern "C" {
@@ -1064,8 +1082,8 @@ int isr_pipe_create(isr_pipe **out, isr_net *net, int c_low, int c_prev, int spe
   return ISR_OK;
 }
 
-int isr_pipe_submit(isr_pipe *p, const float *low_host, const float *flow_host, float *recon_host) {
-  if (p == nullptr || low_host == nullptr || recon_host == nullptr) return fail(ISR_ERR_ARG, "pipe_submit: null argument");
+static int pipe_submit(isr_pipe *p, const float *low_host, const float *flow_host, float *recon_host,
+                       unsigned char *rgb8_host) {
   const int k = static_cast<int>(p->submitted % p->depth);
   // the slot is reused: frame (j - depth) must have left it (its D2H finished => its kernels finished too)
   if (p->submitted >= static_cast<uint64_t>(p->depth)) ISR_CUDA(cudaEventSynchronize(p->ev_out[k]));
@@ -1081,16 +1099,50 @@ int isr_pipe_submit(isr_pipe *p, const float *low_host, const float *flow_host, 
     rc = isr_initial_image(low_d, p->state, p->B, p->c_low, p->h, p->w, p->c_prev, p->initial_mode, 0, 4, p->s_comp);
     if (rc != ISR_OK) return rc;
   }
+  // display form: the prediction is not written at all, only the recurrent state (which the shading reads)
   rc = isr_net_forward_recurrent(p->net, low_d, p->state, flow_host != nullptr ? flow_d : nullptr, p->c_low, p->c_prev,
-                                 p->special_mask, 0, recon_d, nullptr, p->state, p->net->cout == 6, p->B, p->h, p->w,
-                                 p->precision, p->ws, p->ws_bytes, p->s_comp);
+                                 p->special_mask, 0, rgb8_host != nullptr ? nullptr : recon_d, nullptr, p->state,
+                                 p->net->cout == 6, p->B, p->h, p->w, p->precision, p->ws, p->ws_bytes, p->s_comp);
   if (rc != ISR_OK) return rc;
+  unsigned char *rgb8_d = nullptr;
+  if (rgb8_host != nullptr) {
+    rgb8_d = p->rgb8 + static_cast<size_t>(k) * p->n_rgb8;
+    rc = isr_shade_rgb8(p->state, p->shade_params, rgb8_d, p->B, p->c_prev, 4 * p->h, 4 * p->w, p->s_comp);
+    if (rc != ISR_OK) return rc;
+  }
   ISR_CUDA(cudaEventRecord(p->ev_comp[k], p->s_comp));
   ISR_CUDA(cudaStreamWaitEvent(p->s_out, p->ev_comp[k], 0));
-  ISR_CUDA(cudaMemcpyAsync(recon_host, recon_d, p->n_out * sizeof(float), cudaMemcpyDeviceToHost, p->s_out));
+  if (rgb8_host != nullptr)
+    ISR_CUDA(cudaMemcpyAsync(rgb8_host, rgb8_d, p->n_rgb8, cudaMemcpyDeviceToHost, p->s_out));
+  else
+    ISR_CUDA(cudaMemcpyAsync(recon_host, recon_d, p->n_out * sizeof(float), cudaMemcpyDeviceToHost, p->s_out));
   ISR_CUDA(cudaEventRecord(p->ev_out[k], p->s_out));
   ++p->submitted;
   return ISR_OK;
+}
+
+int isr_pipe_submit(isr_pipe *p, const float *low_host, const float *flow_host, float *recon_host) {
+  if (p == nullptr || low_host == nullptr || recon_host == nullptr) return fail(ISR_ERR_ARG, "pipe_submit: null argument");
+  return pipe_submit(p, low_host, flow_host, recon_host, nullptr);
+}
+
+int isr_pipe_enable_display(isr_pipe *p, const float *params_host, unsigned char *rgb8_staging_dev, size_t bytes) {
+  if (p == nullptr || params_host == nullptr || rgb8_staging_dev == nullptr)
+    return fail(ISR_ERR_ARG, "pipe_enable_display: null argument");
+  if (p->c_prev < 5) return fail(ISR_ERR_ARG, "pipe_enable_display: shading needs the unshaded network's 5|6-channel state");
+  const size_t per = static_cast<size_t>(p->B) * 16 * p->h * p->w * 3;
+  if (bytes < per * p->depth) return fail(ISR_ERR_WORKSPACE, "pipe_enable_display: staging too small (%zu < %zu bytes)", bytes, per * p->depth);
+  memcpy(p->shade_params, params_host, sizeof p->shade_params);
+  p->rgb8 = rgb8_staging_dev;
+  p->n_rgb8 = per;
+  p->display = true;
+  return ISR_OK;
+}
+
+int isr_pipe_submit_display(isr_pipe *p, const float *low_host, const float *flow_host, unsigned char *rgb8_host) {
+  if (p == nullptr || low_host == nullptr || rgb8_host == nullptr) return fail(ISR_ERR_ARG, "pipe_submit_display: null argument");
+  if (!p->display) return fail(ISR_ERR_ARG, "pipe_submit_display: call isr_pipe_enable_display first");
+  return pipe_submit(p, low_host, flow_host, nullptr, rgb8_host);
 }
 
 int isr_pipe_wait(isr_pipe *p) {

@@ -31,6 +31,8 @@ cudaError_t launch_pack_weights(const float *w, uint16_t *out, int cout, int cin
 // tap-stacked output-conv weights: [fmt 2][part 2][nrows (n = tap*cp + co)][64]
 cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s);
 
+cudaError_t launch_shade_rgb8(const float *in, const float *params22, unsigned char *out, int B, int C, int H, int W,
+                              cudaStream_t s);
 // isr_ingest.cu
 int ingest_low_channels(int variant);
 cudaError_t launch_ingest(const float *render, int interleaved, int c_render, float *low, float *flow,

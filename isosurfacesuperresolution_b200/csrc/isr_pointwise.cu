@@ -413,6 +413,41 @@ shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams 
   }
 }
 
+// Shading straight to the display format: H x W x 3 interleaved 8-bit, v8 = uint8(clip(rgb * 255, 0, 255)) (truncation),
+// the conversion mainGUI.py:507 / mainComparisonVideo3.py:589 perform on the host after copying the fp32 frame back.
+// One thread = 4 pixels = 12 output bytes (three 32-bit stores).
+__global__ void __launch_bounds__(256)
+shade_rgb8_kernel(const float *__restrict__ in, unsigned char *__restrict__ out, ShadeParams s, float sf, int B, int C,
+                  size_t plane) {
+  const unsigned nvec = static_cast<unsigned>(plane / 4);
+  const size_t b = blockIdx.y;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {
+    const size_t q = static_cast<size_t>(i) * 4;
+    const float *p = in + b * C * plane + q;
+    const float4 m = __ldcs(reinterpret_cast<const float4 *>(p));
+    const float4 nx = __ldcs(reinterpret_cast<const float4 *>(p + plane));
+    const float4 ny = __ldcs(reinterpret_cast<const float4 *>(p + 2 * plane));
+    const float4 nz = __ldcs(reinterpret_cast<const float4 *>(p + 3 * plane));
+    float4 ao = make_float4(1.f, 1.f, 1.f, 1.f);
+    if (C >= 6) ao = __ldcs(reinterpret_cast<const float4 *>(p + 5 * plane));
+    const float mm[4] = {m.x, m.y, m.z, m.w}, ax[4] = {nx.x, nx.y, nx.z, nx.w}, ay[4] = {ny.x, ny.y, ny.z, ny.w},
+                az[4] = {nz.x, nz.y, nz.z, nz.w}, aa[4] = {ao.x, ao.y, ao.z, ao.w};
+    unsigned char bytes[12];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float rgb[3];
+      shade_pixel(s, mm[j], ax[j], ay[j], az[j], aa[j], C >= 6, sf, rgb);
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        bytes[3 * j + c] = static_cast<unsigned char>(static_cast<int>(fminf(fmaxf(rgb[c] * 255.f, 0.f), 255.f)));
+    }
+    uint32_t *o = reinterpret_cast<uint32_t *>(out + (b * plane + q) * 3);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      o[k] = bytes[4 * k] | (bytes[4 * k + 1] << 8) | (bytes[4 * k + 2] << 16) | (static_cast<uint32_t>(bytes[4 * k + 3]) << 24);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // GUI / video composition (mainGUI.py:603-608,615-636; mainComparisonVideo3.py:540-556), one pass:
 //   image = bilinear x4 of the 12-channel low-res render (RGB, mask, normal, depth, flow, AO, shadow)
@@ -675,6 +710,18 @@ cudaError_t launch_shade(const float *in, const float *params22, float *out, int
     dim3 grid(grid_for(plane, 256), B);
     shade_kernel<1><<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
   }
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_shade_rgb8(const float *in, const float *params22, unsigned char *out, int B, int C, int H, int W,
+                              cudaStream_t s) {
+  ShadeParams sp;
+  for (int i = 0; i < 22; ++i) sp.v[i] = params22[i];
+  const int expo = static_cast<int>(params22[19]);
+  const float sf = static_cast<float>((static_cast<double>(expo) + 2.0) / (2.0 * 3.14159265358979323846));
+  const size_t plane = static_cast<size_t>(H) * W;
+  dim3 grid(grid_for(plane / 4, 256), B);
+  shade_rgb8_kernel<<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
   count_launch();
   return cudaGetLastError();
 }

@@ -91,6 +91,18 @@ def shade(gbuffer, params22):
     return out
 
 
+def shade_rgb8(gbuffer, params22):
+    """isr_shade_rgb8: shading straight to B x H x W x 3 uint8 (uint8(clip(rgb * 255, 0, 255)), mainGUI.py:507)."""
+    x = _prep(gbuffer, "input")
+    B, C, H, W = x.shape
+    assert C >= 5
+    arr = (ctypes.c_float * 22)(*[float(v) for v in params22])
+    out = torch.empty((B, H, W, 3), device=x.device, dtype=torch.uint8)
+    with torch.cuda.device(x.device):
+        check(lib().isr_shade_rgb8(_p(x), arr, _p(out), B, C, H, W, _stream()))
+    return out
+
+
 def compose(image_low, pred, params22, unshaded=True, masking=False, background0=0.0):
     """GUI / video composition (mainGUI.py:603-608,615-636): 12-channel bilinear x4 + overwrite + optional mask lerp."""
     low, pr = _prep(image_low, "image_low"), _prep(pred, "pred")
@@ -320,6 +332,22 @@ class RecurrentPipeline:
         out = self._host(recon_host, "recon_host", self.out_shape)
         with torch.cuda.device(self.handle.device):
             check(lib().isr_pipe_submit(self._pipe, lo, fl, out))
+
+    def enable_display(self, params22):
+        """Switch on the display form: ``submit_display`` returns shaded 8-bit RGB frames (B x 4h x 4w x 3) to the host."""
+        arr = (ctypes.c_float * 22)(*[float(v) for v in params22])
+        depth_bytes = 2 * self.B * 16 * self.h * self.w * 3 * 4      # room for depth <= 8
+        self._rgb8 = torch.empty(depth_bytes, device=self.handle.device, dtype=torch.uint8)
+        check(lib().isr_pipe_enable_display(self._pipe, arr, _p(self._rgb8), depth_bytes))
+
+    def submit_display(self, low_host, flow_host, rgb8_host):
+        lo = self._host(low_host, "low_host", (self.B, self.c_low, self.h, self.w))
+        fl = self._host(flow_host, "flow_host", (self.B, 2, self.h, self.w)) if flow_host is not None else ctypes.c_void_p(0)
+        if (not isinstance(rgb8_host, torch.Tensor) or rgb8_host.is_cuda or rgb8_host.dtype != torch.uint8
+                or tuple(rgb8_host.shape) != (self.B, 4 * self.h, 4 * self.w, 3) or not rgb8_host.is_contiguous()):
+            raise TypeError("rgb8_host: expected a contiguous uint8 CPU tensor of shape B x 4h x 4w x 3 (pinned for overlap)")
+        with torch.cuda.device(self.handle.device):
+            check(lib().isr_pipe_submit_display(self._pipe, lo, fl, ctypes.c_void_p(rgb8_host.data_ptr())))
 
     def wait(self):
         check(lib().isr_pipe_wait(self._pipe))

@@ -583,3 +583,39 @@ def test_fused_upsample_conv_equals_unfused(isr, weights, shape):
         ref, _ = orc.enhancenet_forward(weights, x.cpu().numpy(), "bilinear", "residual", 5, backend="torch")
         _check_net(outs[1], ref)
         _check_net(outs[0], ref)
+
+
+def test_display_pipeline_rgb8(isr, weights):
+    """Display form of the host pipeline: the 8-bit shaded frames that reach the host equal
+    uint8(clip(ScreenSpaceShading(state) * 255, 0, 255)) (mainGUI.py:507 / mainComparisonVideo3.py:589) of the
+    device-resident recurrence, frame for frame; isr_shade_rgb8 equals the fp32 shading + the host conversion."""
+    from isosurfacesuperresolution_b200 import ops
+    net = _net(isr, weights)
+    B, T, h, w = 2, 4, 24, 40
+    low, flow, _ = orc.synthetic_gbuffer(B, h, w, 22, T=T)
+    params = orc.shading_params(material=(1.0, 0.3, 0.0), ao_strength=0.5)
+    shd = _shading_from_params(isr, params)
+    # reference frames: device recurrence, fp32 shading, host-side conversion as in the reference
+    state, refs = None, []
+    with torch.no_grad():
+        for j in range(T):
+            inp = cu(low[:, j])
+            if j == 0:
+                prev = isr.initialImage(inp, 6, "input", False, 4)
+                _, _, state = net(inp, prev, None, return_state=True)
+            else:
+                _, _, state = net(inp, state, cu(flow[:, j - 1]), special_mask=True, return_state=True)
+            rgb = shd(state).cpu().numpy()
+            refs.append(np.clip(rgb * 255, 0, 255).astype(np.uint8).transpose(0, 2, 3, 1))
+            assert np.array_equal(ops.shade_rgb8(state, shd.params22()).cpu().numpy(), refs[-1])
+    pipe = ops.RecurrentPipeline(net._native(), 5, 6, True, "input", B, h, w, net.precision, depth=2)
+    pipe.enable_display(shd.params22())
+    outs = [torch.empty((B, 4 * h, 4 * w, 3), dtype=torch.uint8).pin_memory() for _ in range(T)]
+    lows = [torch.from_numpy(np.ascontiguousarray(low[:, j])).pin_memory() for j in range(T)]
+    flows = [torch.from_numpy(np.ascontiguousarray(flow[:, j])).pin_memory() for j in range(T)]
+    for j in range(T):
+        pipe.submit_display(lows[j], None if j == 0 else flows[j - 1], outs[j])
+    pipe.wait()
+    for j in range(T):
+        assert np.array_equal(outs[j].numpy(), refs[j]), f"frame {j}"
+    pipe.close()
