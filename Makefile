@@ -17,7 +17,9 @@ $(CSRC)/isr_up2.o: $(CSRC)/isr_up2.cu $(CSRC)/isr_internal.h
 	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
 $(CSRC)/isr_ssao.o: $(CSRC)/isr_ssao.cu $(CSRC)/isr_internal.h
 	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
-$(LIB): $(CSRC)/isr_api.o $(CSRC)/isr_pointwise.o $(CSRC)/isr_ingest.o $(CSRC)/isr_ssao.o $(CSRC)/isr_up2.o
+$(CSRC)/isr_raycast.o: $(CSRC)/isr_raycast.cu $(CSRC)/isr_internal.h include/isr.h
+	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@
+$(LIB): $(CSRC)/isr_raycast.o $(CSRC)/isr_api.o $(CSRC)/isr_pointwise.o $(CSRC)/isr_ingest.o $(CSRC)/isr_ssao.o $(CSRC)/isr_up2.o
 	$(NVCC) $(ARCH) -shared -o $@ $^ -cudart static
 oracle:
 	$(MAKE) -C oracle -s

@@ -145,6 +145,49 @@ int isr_ssao(int width, int height, const float *input, int input_entry_stride, 
              void *stream);
 int isr_ssao_tables(int samples, int noise_samples, float *kernel_host, float *noise_host);
 
+/* Dense-grid isosurface ray-caster writing the renderer's 12-channel frame: the arithmetic of
+ * custom_iso_kernel, GPURendererDirect/render_kernel.cu:212-266 (fixed-step march, 10-step bisection :175-190, gradient
+ * normal, Phong colour, flow from the current / next view-projection matrices, screen-space depth and normal, ray-cast
+ * ambient occlusion :109-148) on ONE dense fp32 brick instead of GVDB's sparse atlas (GVDB is a closed binary and the
+ * repository ships no volume).  volume: DEVICE nz x ny x nx floats (x fastest), voxel centres at index + 0.5, clamp to
+ * edge, trilinear in fp32; the surface is {value >= iso}.  out: DEVICE height x width x 12 interleaved floats
+ * (RGB, mask, nx, ny, nz, depth, flow_x, flow_y, AO, shadow; render_kernel.cu:254-265), 16-byte aligned.
+ * params: HOST block of ISR_RC_PARAMS floats (indices below; matrices row-major as uploaded by
+ * GPURendererDirect.cpp:325-338).  ao_hemisphere: HOST 4 * ao_samples floats, ao_rotations: HOST 64 floats (4 x 4
+ * float4, index x%4 + 4*(y%4)); isr_raycast_ao_tables draws both as GPURendererDirect.cpp:146-190 does (512 samples).
+ * viewport: HOST minX, minY, maxX, maxY or NULL for the whole frame.  ao_samples in [0, 512]; nx, ny, nz >= 2. */
+enum {
+  ISR_RC_CAM_POS = 0,     /* 3: ray origin (world) */
+  ISR_RC_CAM_U = 3,       /* 3: ray(sx, sy) = normalize(sx * U + sy * V + S), sx = (x + 0.5) / width, sy likewise */
+  ISR_RC_CAM_V = 6,
+  ISR_RC_CAM_S = 9,
+  ISR_RC_BOX_MIN = 12,    /* 3: world position of the brick's index-space origin */
+  ISR_RC_VOXEL = 15,      /* world size of one voxel */
+  ISR_RC_ISO = 16,        /* isovalue */
+  ISR_RC_STEP = 17,       /* march step in voxels (the reference: 0.05, GPURendererDirect.cpp:365) */
+  ISR_RC_VIEW_CUR = 18,   /* 16: projection * view of the current camera */
+  ISR_RC_VIEW_NEXT = 34,  /* 16: projection * view of the next camera */
+  ISR_RC_NORMAL_MAT = 50, /* 16: view matrix (applied to (normal, 0)) */
+  ISR_RC_LIGHT = 66,      /* 3: light direction, normalised */
+  ISR_RC_AMBIENT = 69,
+  ISR_RC_DIFFUSE = 72,
+  ISR_RC_SPECULAR = 75,
+  ISR_RC_SPEC_EXP = 78,   /* integer-valued */
+  ISR_RC_AO_RADIUS = 79,  /* world units */
+  ISR_RC_AO_BIAS = 80,    /* world units the AO origin steps back along the primary ray (1e-3) */
+  ISR_RC_PARAMS = 81
+};
+int isr_raycast_iso(const float *volume, int nx, int ny, int nz, const float *params_host, const float *ao_hemisphere_host,
+                    const float *ao_rotations_host, int ao_samples, int binary_steps, const int *viewport_host,
+                    const float *skip, float *out, int width, int height, void *stream);
+/* Optional empty-space grid for isr_raycast_iso (`skip`, DEVICE, may be NULL): the max of the brick over each 8^3
+ * macro-cell plus apron, built once per volume (GVDB's brick topology plays this role in the reference).  A cell whose
+ * max is below iso cannot contain a sample >= iso, so the march steps over it; the samples that are evaluated and the
+ * frame are IDENTICAL to the plain march. */
+int isr_raycast_skip_bytes(int nx, int ny, int nz, size_t *bytes);
+int isr_raycast_build_skip(const float *volume, int nx, int ny, int nz, float *skip, size_t skip_bytes, void *stream);
+int isr_raycast_ao_tables(float *hemisphere_host /* 4 * 512 */, float *rotations_host /* 64 */);
+
 /* ---- EnhanceNet generator (models/enhancenet.py:8-26,92-145) ------------------------------------------- */
 
 typedef struct isr_net isr_net;

@@ -19,6 +19,7 @@ from .shading import ScreenSpaceShading     # noqa: E402
 from .videotools import VideoTools          # noqa: E402
 from .inference import LoadedModel, SequenceRunner, compose_frame   # noqa: E402
 from .dataset import SequenceDataset, evaluate, masked_psnr           # noqa: E402
+from .renderer import DenseGridRenderer, camera_matrices              # noqa: E402
 
 
 def createNetwork(name, upscale_factor, input_channels, channel_mask, output_channels, additional_opt):

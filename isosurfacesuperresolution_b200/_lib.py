@@ -28,6 +28,11 @@ class IsrError(RuntimeError):
 _c = ctypes
 _vp, _i, _sz = _c.c_void_p, _c.c_int, _c.c_size_t
 
+# include/isr.h ISR_RC_*: float indices of the ray-caster's parameter block
+(RC_CAM_POS, RC_CAM_U, RC_CAM_V, RC_CAM_S, RC_BOX_MIN, RC_VOXEL, RC_ISO, RC_STEP, RC_VIEW_CUR, RC_VIEW_NEXT, RC_NORMAL_MAT,
+ RC_LIGHT, RC_AMBIENT, RC_DIFFUSE, RC_SPECULAR, RC_SPEC_EXP, RC_AO_RADIUS, RC_AO_BIAS, RC_PARAMS) = (
+    0, 3, 6, 9, 12, 15, 16, 17, 18, 34, 50, 66, 69, 72, 75, 78, 79, 80, 81)
+
 # name -> (restype, argtypes); every symbol include/isr.h declares
 SIGNATURES = {
     "isr_version": (_i, []),
@@ -45,6 +50,10 @@ SIGNATURES = {
     "isr_inpaint_flow": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "isr_ssao": (_i, [_i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _c.c_float, _c.c_float, _i, _vp]),
     "isr_ssao_tables": (_i, [_i, _i, _vp, _vp]),
+    "isr_raycast_iso": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
+    "isr_raycast_skip_bytes": (_i, [_i, _i, _i, _c.POINTER(_sz)]),
+    "isr_raycast_build_skip": (_i, [_vp, _i, _i, _i, _vp, _sz, _vp]),
+    "isr_raycast_ao_tables": (_i, [_vp, _vp]),
     "isr_net_create": (_i, [_c.POINTER(_vp), _i, _i, _i, _i, _i]),
     "isr_net_destroy": (None, [_vp]),
     "isr_net_load_weights": (_i, [_vp, _c.POINTER(_vp), _i, _vp]),

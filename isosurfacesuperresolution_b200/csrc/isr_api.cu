@@ -826,6 +826,92 @@ int isr_ssao(int width, int height, const float *input, int input_entry_stride, 
   return ISR_OK;
 }
 
+int isr_raycast_ao_tables(float *hemisphere_host, float *rotations_host) {
+  // GPURendererDirect.cpp:146-190: default-seeded engine, one shared uniform(0,1) stream, hemisphere first
+  std::default_random_engine rnd;
+  std::uniform_real_distribution<float> distr(0.0f, 1.0f);
+  for (int i = 0; i < 512; ++i) {
+    const float u1 = distr(rnd);
+    const float u2 = distr(rnd);
+    const float r = std::sqrt(u1);
+    const float theta = static_cast<float>(2 * M_PI * u2);
+    const float x = r * std::cos(theta), y = r * std::sin(theta);
+    float scale = distr(rnd);
+    scale = static_cast<float>(0.1 + 0.9 * scale * scale);
+    if (hemisphere_host != nullptr) {
+      hemisphere_host[4 * i] = x * scale;
+      hemisphere_host[4 * i + 1] = y * scale;
+      hemisphere_host[4 * i + 2] = std::sqrt(1 - u1) * scale;
+      hemisphere_host[4 * i + 3] = 0.f;
+    }
+  }
+  for (int i = 0; i < 16; ++i) {
+    const float x = distr(rnd) * 2 - 1;
+    const float y = distr(rnd) * 2 - 1;
+    const float linv = 1.0f / std::sqrt(x * x + y * y);
+    if (rotations_host != nullptr) {
+      rotations_host[4 * i] = x * linv;
+      rotations_host[4 * i + 1] = y * linv;
+      rotations_host[4 * i + 2] = 0.f;
+      rotations_host[4 * i + 3] = 0.f;
+    }
+  }
+  return ISR_OK;
+}
+
+int isr_raycast_skip_bytes(int nx, int ny, int nz, size_t *bytes) {
+  if (bytes == nullptr || nx < 2 || ny < 2 || nz < 2) return fail(ISR_ERR_ARG, "raycast: bad brick size");
+  int cx, cy, cz;
+  raycast_skip_dims(nx, ny, nz, &cx, &cy, &cz);
+  *bytes = sizeof(float) * static_cast<size_t>(cx) * cy * cz;
+  return ISR_OK;
+}
+
+int isr_raycast_build_skip(const float *volume, int nx, int ny, int nz, float *skip, size_t skip_bytes, void *stream) {
+  size_t need = 0;
+  int rc = isr_raycast_skip_bytes(nx, ny, nz, &need);
+  if (rc != ISR_OK) return rc;
+  if (volume == nullptr || skip == nullptr || skip_bytes < need) return fail(ISR_ERR_ARG, "raycast: skip grid too small");
+  rc = check_device();
+  if (rc != ISR_OK) return rc;
+  ISR_CUDA(launch_raycast_skip(volume, skip, nx, ny, nz, S(stream)));
+  return ISR_OK;
+}
+
+int isr_raycast_iso(const float *volume, int nx, int ny, int nz, const float *params_host, const float *ao_hemisphere_host,
+                    const float *ao_rotations_host, int ao_samples, int binary_steps, const int *viewport_host,
+                    const float *skip, float *out, int width, int height, void *stream) {
+  if (volume == nullptr || params_host == nullptr || out == nullptr || width <= 0 || height <= 0)
+    return fail(ISR_ERR_ARG, "raycast: bad arguments");
+  if (nx < 2 || ny < 2 || nz < 2) return fail(ISR_ERR_ARG, "raycast: the brick needs at least 2 voxels per axis");
+  if (ao_samples < 0 || ao_samples > 512 || binary_steps < 0 || binary_steps > 64)
+    return fail(ISR_ERR_UNSUPPORTED, "raycast: ao_samples must be in [0,512] and binary_steps in [0,64]");
+  if (ao_samples > 0 && (ao_hemisphere_host == nullptr || ao_rotations_host == nullptr))
+    return fail(ISR_ERR_ARG, "raycast: ambient-occlusion tables missing");
+  if (!(params_host[ISR_RC_STEP] > 0.f) || !(params_host[ISR_RC_VOXEL] > 0.f))
+    return fail(ISR_ERR_ARG, "raycast: step and voxel size must be positive");
+  if ((reinterpret_cast<uintptr_t>(out) & 15) != 0) return fail(ISR_ERR_ARG, "raycast: out must be 16-byte aligned");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  static thread_local RaycastArgs a;
+  a.width = width; a.height = height; a.nx = nx; a.ny = ny; a.nz = nz;
+  a.binary_steps = binary_steps; a.ao_samples = ao_samples;
+  if (viewport_host != nullptr) {
+    memcpy(a.viewport, viewport_host, sizeof a.viewport);
+  } else {
+    a.viewport[0] = 0; a.viewport[1] = 0; a.viewport[2] = width; a.viewport[3] = height;
+  }
+  memcpy(a.p, params_host, sizeof a.p);
+  memset(a.hemisphere, 0, sizeof a.hemisphere);
+  memset(a.rotations, 0, sizeof a.rotations);
+  if (ao_samples > 0) {
+    memcpy(a.hemisphere, ao_hemisphere_host, sizeof(float) * 4 * ao_samples);
+    memcpy(a.rotations, ao_rotations_host, sizeof a.rotations);
+  }
+  ISR_CUDA(launch_raycast_iso(volume, skip, out, a, S(stream)));
+  return ISR_OK;
+}
+
 int isr_ingest_low_channels(int variant) {
   if (variant < 0 || variant > 4) return fail(ISR_ERR_ARG, "ingest: unknown variant %d", variant);
   return ingest_low_channels(variant);

@@ -58,4 +58,16 @@ cudaError_t launch_ssao(const float *input, int es, int rs, int inx, int iny, in
                         int ors, int oidx, int width, int height, int samples, float radius, float bias, int ns,
                         const SsaoTables &tab, cudaStream_t s);
 
+// isr_raycast.cu: everything the ray-caster needs, passed by value (about 8.6 KB of kernel parameters)
+struct RaycastArgs {
+  int width, height, nx, ny, nz, binary_steps, ao_samples;
+  int viewport[4];
+  float p[81];                // include/isr.h ISR_RC_*
+  float hemisphere[4 * 512];
+  float rotations[4 * 16];
+};
+cudaError_t launch_raycast_iso(const float *vol, const float *skip, float *out, const RaycastArgs &args, cudaStream_t s);
+void raycast_skip_dims(int nx, int ny, int nz, int *cx, int *cy, int *cz);   // macro-cells per axis of the skip grid
+cudaError_t launch_raycast_skip(const float *vol, float *skip, int nx, int ny, int nz, cudaStream_t s);
+
 }  // namespace isr

@@ -3,6 +3,7 @@
 Every function requires CUDA fp32 tensors and raises otherwise -- there is no CPU path.
 """
 import ctypes
+import numpy as np
 
 import torch
 
@@ -180,6 +181,56 @@ def ssao(frame, samples=64, sample_radius=0.1, bias=0.025, noise_samples=4, norm
                                  C, W, output_index, int(samples), float(sample_radius), float(bias), int(noise_samples),
                                  _stream()))
     return frame
+
+
+RC_PARAMS = 81   # include/isr.h ISR_RC_PARAMS
+
+
+def raycast_ao_tables():
+    """Hemisphere samples (512 x 4) and rotation vectors (16 x 4) of the ray-caster's ambient occlusion, drawn as
+    GPURendererDirect.cpp:146-190 draws them (host arrays)."""
+    hemi = np.zeros((512, 4), np.float32)
+    rot = np.zeros((16, 4), np.float32)
+    check(lib().isr_raycast_ao_tables(hemi.ctypes.data_as(ctypes.c_void_p), rot.ctypes.data_as(ctypes.c_void_p)))
+    return hemi, rot
+
+
+def raycast_build_skip(volume):
+    """Empty-space grid of a brick for ``raycast_iso(..., skip=...)``: one float per 8^3 macro-cell (device tensor)."""
+    if not isinstance(volume, torch.Tensor) or not volume.is_cuda or volume.dtype != torch.float32 or not volume.is_contiguous():
+        raise RuntimeError("volume: a contiguous CUDA float32 tensor is required; there is no CPU fallback")
+    nz, ny, nx = volume.shape
+    n = ctypes.c_size_t(0)
+    check(lib().isr_raycast_skip_bytes(nx, ny, nz, ctypes.byref(n)))
+    skip = torch.empty(n.value // 4, device=volume.device, dtype=torch.float32)
+    with torch.cuda.device(volume.device):
+        check(lib().isr_raycast_build_skip(_p(volume), nx, ny, nz, _p(skip), n.value, _stream()))
+    return skip
+
+
+def raycast_iso(volume, params, out, ao_samples=0, hemisphere=None, rotations=None, binary_steps=10, viewport=None,
+                skip=None):
+    """custom_iso_kernel (GPURendererDirect/render_kernel.cu:212-266) on one dense brick: ``volume`` nz x ny x nx CUDA
+    float32, ``params`` the 81-float ISR_RC_* block (host), ``out`` a caller-allocated H x W x 12 CUDA float32 tensor
+    (the reference's render(target) convention, inference/renderer.py:104-107).  Asynchronous on the current stream."""
+    for name, t in (("volume", volume), ("out", out)):
+        if not isinstance(t, torch.Tensor) or not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+            raise RuntimeError(f"{name}: a contiguous CUDA float32 tensor is required; there is no CPU fallback")
+    assert volume.dim() == 3 and out.dim() == 3 and out.shape[2] == 12
+    P = np.ascontiguousarray(params, dtype=np.float32)
+    assert P.shape == (RC_PARAMS,)
+    nz, ny, nx = volume.shape
+    H, W, _ = out.shape
+    hemi = np.ascontiguousarray(hemisphere, dtype=np.float32) if hemisphere is not None else None
+    rot = np.ascontiguousarray(rotations, dtype=np.float32) if rotations is not None else None
+    assert hemi is None or hemi.size >= 4 * ao_samples
+    assert rot is None or rot.size == 64
+    vp = np.ascontiguousarray(viewport, dtype=np.int32) if viewport is not None else None
+    vpp = lambda a: a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+    with torch.cuda.device(out.device):
+        check(lib().isr_raycast_iso(_p(volume), nx, ny, nz, vpp(P), vpp(hemi), vpp(rot), int(ao_samples), int(binary_steps),
+                                    vpp(vp), _p(skip) if skip is not None else None, _p(out), W, H, _stream()))
+    return out
 
 
 def _workspace(device, nbytes):

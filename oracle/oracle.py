@@ -391,3 +391,48 @@ def ssao(frame, samples=64, sample_radius=0.1, bias=0.025, noise_samples=4, norm
     else:
         _ssao_lib().orc_ssao(*args)
     return f
+
+
+# ---- dense-grid isosurface ray-caster ---------------------------------------------------------
+_RAYCAST = None
+
+
+def _raycast_lib():
+    global _RAYCAST
+    if _RAYCAST is None:
+        so = os.path.join(_HERE, "libisr_oracle_raycast.so")
+        src = os.path.join(_HERE, "raycast_oracle.c")
+        if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+            subprocess.check_call(["make", "-C", _HERE, "-s", "libisr_oracle_raycast.so"])
+        _RAYCAST = ctypes.CDLL(so)
+        _RAYCAST.isr_oracle_raycast_iso.restype = None
+        _RAYCAST.isr_oracle_raycast_iso.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                    ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                    ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                                    ctypes.c_int]
+    return _RAYCAST
+
+
+def raycast_ao_tables():
+    """Hemisphere samples (512 x 4) and rotation vectors (16 x 4) as GPURendererDirect.cpp:146-190 draws them."""
+    hemi = np.zeros((512, 4), np.float32)
+    rot = np.zeros((16, 4), np.float32)
+    _ssao_lib().orc_raycast_ao_tables(_p(hemi), _p(rot))
+    return hemi, rot
+
+
+def raycast_iso(volume, params, width, height, ao_samples=0, hemisphere=None, rotations=None, binary_steps=10,
+                viewport=None):
+    """custom_iso_kernel (GPURendererDirect/render_kernel.cu:212-266) on one dense brick ``volume`` (nz x ny x nx).
+    ``params``: the ISR_RC_* block of include/isr.h (81 floats).  Returns the height x width x 12 frame."""
+    vol = _f32(volume)
+    nz, ny, nx = vol.shape
+    P = _f32(params)
+    assert P.shape == (81,)
+    hemi = _f32(hemisphere) if hemisphere is not None else np.zeros((max(ao_samples, 1), 4), np.float32)
+    rot = _f32(rotations) if rotations is not None else np.zeros((16, 4), np.float32)
+    vp = np.ascontiguousarray(viewport, dtype=np.int32) if viewport is not None else None
+    out = np.empty((height, width, 12), np.float32)
+    _raycast_lib().isr_oracle_raycast_iso(_p(vol), nx, ny, nz, _p(P), _p(hemi), _p(rot), int(ao_samples),
+                                          int(binary_steps), _p(vp) if vp is not None else None, _p(out), width, height)
+    return out

@@ -99,3 +99,31 @@ extern "C" void orc_ssao(int width, int height, const float *input, int es, int 
     for (int x = 0; x < width; ++x)
       output[oidx + static_cast<size_t>(oes) * (x + static_cast<size_t>(ors) * y)] = buf[x + static_cast<size_t>(width) * y];
 }
+
+// Ambient-occlusion tables of the ray-caster, GPURendererDirect.cpp:146-190: a default-seeded engine and ONE uniform(0,1)
+// stream; 512 cosine-distributed hemisphere directions scaled into [0.1, 1], then 16 unit rotation vectors in the plane.
+extern "C" void orc_raycast_ao_tables(float *hemisphere /* 4 * 512 */, float *rotations /* 4 * 16 */) {
+  std::default_random_engine engine;
+  std::uniform_real_distribution<float> uni(0.0f, 1.0f);
+  for (int i = 0; i < 512; ++i) {
+    float u1 = uni(engine);
+    float u2 = uni(engine);
+    float r = std::sqrt(u1);
+    float theta = 2 * M_PI * u2;
+    float s = uni(engine);
+    s = 0.1 + 0.9 * s * s;
+    hemisphere[4 * i + 0] = r * std::cos(theta) * s;
+    hemisphere[4 * i + 1] = r * std::sin(theta) * s;
+    hemisphere[4 * i + 2] = std::sqrt(1 - u1) * s;
+    hemisphere[4 * i + 3] = 0;
+  }
+  for (int i = 0; i < 16; ++i) {
+    float x = uni(engine) * 2 - 1;
+    float y = uni(engine) * 2 - 1;
+    float linv = 1.0f / std::sqrt(x * x + y * y);
+    rotations[4 * i + 0] = x * linv;
+    rotations[4 * i + 1] = y * linv;
+    rotations[4 * i + 2] = 0;
+    rotations[4 * i + 3] = 0;
+  }
+}
