@@ -861,9 +861,7 @@ int isr_raycast_ao_tables(float *hemisphere_host, float *rotations_host) {
 
 int isr_raycast_skip_bytes(int nx, int ny, int nz, size_t *bytes) {
   if (bytes == nullptr || nx < 2 || ny < 2 || nz < 2) return fail(ISR_ERR_ARG, "raycast: bad brick size");
-  int cx, cy, cz;
-  raycast_skip_dims(nx, ny, nz, &cx, &cy, &cz);
-  *bytes = sizeof(float) * static_cast<size_t>(cx) * cy * cz;
+  *bytes = sizeof(float) * raycast_skip_floats(nx, ny, nz);
   return ISR_OK;
 }
 

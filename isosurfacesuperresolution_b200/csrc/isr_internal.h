@@ -67,7 +67,7 @@ struct RaycastArgs {
   float rotations[4 * 16];
 };
 cudaError_t launch_raycast_iso(const float *vol, const float *skip, float *out, const RaycastArgs &args, cudaStream_t s);
-void raycast_skip_dims(int nx, int ny, int nz, int *cx, int *cy, int *cz);   // macro-cells per axis of the skip grid
+size_t raycast_skip_floats(int nx, int ny, int nz);   // coarse (8^3) + fine (2^3) macro-cell grids
 cudaError_t launch_raycast_skip(const float *vol, float *skip, int nx, int ny, int nz, cudaStream_t s);
 
 }  // namespace isr

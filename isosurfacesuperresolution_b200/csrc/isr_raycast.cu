@@ -38,13 +38,16 @@ __device__ __forceinline__ V3 normalize3(V3 a) {
 }
 __device__ __forceinline__ V3 ld3(const float *p) { return v3(p[0], p[1], p[2]); }
 
-constexpr int kSkipCell = 8;   // macro-cell edge in voxels (isr_internal.h raycast_skip_dims)
+constexpr int kSkipCell = 8;   // coarse macro-cell edge in voxels
+constexpr int kSkipFine = 2;   // fine macro-cell edge
 
 struct Grid {
   const float *__restrict__ v;
   int nx, ny, nz;
-  const float *__restrict__ skip;   // per macro-cell max, or nullptr
+  const float *__restrict__ skip;   // max per coarse macro-cell, or nullptr
   int cx, cy, cz;
+  const float *__restrict__ fine;   // max per fine macro-cell (follows the coarse grid in the same buffer)
+  int fx, fy, fz;
 };
 
 __device__ __forceinline__ void cell(float p, int n, int &i, float &f) {
@@ -95,11 +98,39 @@ __device__ __forceinline__ bool clip(const Grid &g, V3 p0, V3 d, float &tn, floa
   return tn <= tf;
 }
 
+// Number of samples the march may step over from p inside the macro-cell of edge `cell` that contains it, or 0 when the
+// cell's max reaches iso.  A trilinear sample is a convex combination of its 8 voxels, so inside a cell whose max (over
+// the cell plus a 1-voxel apron, the trilinear footprint) is below iso every sample is below iso.
+__device__ __forceinline__ int hop(const float *__restrict__ grid, int gx, int gy, int gz, int cell, V3 p, V3 d, float iso,
+                                   float inv_step) {
+  const float inv_cell = 1.0f / static_cast<float>(cell);
+  int cx = static_cast<int>(floorf(p.x * inv_cell)), cy = static_cast<int>(floorf(p.y * inv_cell)),
+      cz = static_cast<int>(floorf(p.z * inv_cell));
+  cx = cx < 0 ? 0 : (cx > gx - 1 ? gx - 1 : cx);
+  cy = cy < 0 ? 0 : (cy > gy - 1 ? gy - 1 : cy);
+  cz = cz < 0 ? 0 : (cz > gz - 1 ? gz - 1 : cz);
+  if (!(__ldg(grid + (static_cast<size_t>(cz) * gy + cy) * gx + cx) < iso)) return 0;
+  // distance to the cell's exit face (a point outside the brick sits in a clamped edge cell: its exit distance is then
+  // over-estimated towards the brick only, where the clamped samples read the same edge voxels)
+  float te = 3.0e38f;
+  const float pc[3] = {p.x, p.y, p.z}, dc[3] = {d.x, d.y, d.z};
+  const int cc[3] = {cx, cy, cz};
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    if (fabsf(dc[a]) > 1e-12f) {
+      const float face = static_cast<float>(dc[a] > 0.f ? (cc[a] + 1) * cell : cc[a] * cell);
+      const float ta = (face - pc[a]) / dc[a];
+      te = ta < te ? ta : te;
+    }
+  }
+  int k = te > 0.f ? static_cast<int>(floorf((te - 0.25f) * inv_step)) : 1;   // stay 1/4 voxel short of the face
+  return k < 1 ? 1 : (k > (1 << 20) ? (1 << 20) : k);
+}
+
 // fixed-step march: first sample >= iso at t = t0 + i * step; returns false when the ray leaves the brick.
-// With a skip grid (max over each 8^3 macro-cell and a 2-voxel apron, skip_cells_kernel) whole runs of samples that
-// cannot reach iso are stepped over: a trilinear sample is a convex combination of its 8 voxels, so inside a cell whose
-// max < iso every sample is < iso.  Only the index i advances -- the samples that ARE evaluated sit at the same
-// t = t0 + i * step as without the grid, so the result is identical to the plain march (tests compare the two).
+// With the skip grids (skip_cells_kernel: 8^3 macro-cells, then 2^3) whole runs of samples that cannot reach iso are
+// stepped over.  Only the index i advances -- the samples that ARE evaluated sit at the same t = t0 + i * step as
+// without the grids, so the result is identical to the plain march (tests compare the two bit for bit).
 __device__ __forceinline__ bool march(const Grid &g, V3 p0, V3 d, float iso, float step, float &t_hit) {
   float tn, tf;
   if (!clip(g, p0, d, tn, tf)) return false;
@@ -110,30 +141,9 @@ __device__ __forceinline__ bool march(const Grid &g, V3 p0, V3 d, float iso, flo
     if (t > tf) return false;
     const V3 p = p0 + t * d;
     if (g.skip != nullptr) {
-      int cx = static_cast<int>(floorf(p.x * (1.0f / kSkipCell))), cy = static_cast<int>(floorf(p.y * (1.0f / kSkipCell))),
-          cz = static_cast<int>(floorf(p.z * (1.0f / kSkipCell)));
-      cx = cx < 0 ? 0 : (cx > g.cx - 1 ? g.cx - 1 : cx);
-      cy = cy < 0 ? 0 : (cy > g.cy - 1 ? g.cy - 1 : cy);
-      cz = cz < 0 ? 0 : (cz > g.cz - 1 ? g.cz - 1 : cz);
-      if (__ldg(g.skip + (static_cast<size_t>(cz) * g.cy + cy) * g.cx + cx) < iso) {
-        // distance to the cell's exit face along each axis (a point outside the brick sits in a clamped edge cell: its
-        // exit distance is then over-estimated towards the brick only, where the clamped samples read the same voxels)
-        float te = 3.0e38f;
-        const float pc[3] = {p.x, p.y, p.z}, dc[3] = {d.x, d.y, d.z};
-        const int cc[3] = {cx, cy, cz};
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-          if (fabsf(dc[a]) > 1e-12f) {
-            const float face = static_cast<float>(dc[a] > 0.f ? (cc[a] + 1) * kSkipCell : cc[a] * kSkipCell);
-            const float ta = (face - pc[a]) / dc[a];
-            te = ta < te ? ta : te;
-          }
-        }
-        int k = te > 0.f ? static_cast<int>(floorf((te - 0.25f) * inv_step)) : 1;   // stay 1/4 voxel short of the face
-        k = k < 1 ? 1 : (k > (1 << 20) ? (1 << 20) : k);
-        i += k;
-        continue;
-      }
+      int k = hop(g.skip, g.cx, g.cy, g.cz, kSkipCell, p, d, iso, inv_step);
+      if (k == 0) k = hop(g.fine, g.fx, g.fy, g.fz, kSkipFine, p, d, iso, inv_step);
+      if (k > 0) { i += k; continue; }
     }
     if (sample(g, p) >= iso) { t_hit = t; return true; }
     ++i;
@@ -158,16 +168,16 @@ __device__ __forceinline__ void matvec4(const float *m, V3 v, float w, float out
 
 }  // namespace
 
-// max over the voxels a sample inside macro-cell c can touch: [8c - 2, 8c + 9] per axis (1 voxel for the trilinear
-// footprint, 1 for rounding slack), clamped to the brick
+// max over the voxels a sample inside macro-cell c can touch: [cell * c - 1, cell * c + cell] per axis (the trilinear
+// footprint), clamped to the brick.  One block per coarse cell, one thread per fine cell.
 __global__ void skip_cells_kernel(const float *__restrict__ vol, float *__restrict__ skip, int nx, int ny, int nz, int cx,
                                   int cy, int cz) {
-  const int c = blockIdx.x;                     // one block per macro-cell
+  const int c = blockIdx.x;
   const int ix = c % cx, iy = (c / cx) % cy, iz = c / (cx * cy);
-  const int e = kSkipCell + 4;
+  const int e = kSkipCell + 2;
   float m = -3.0e38f;
   for (int j = threadIdx.x; j < e * e * e; j += blockDim.x) {
-    int x = ix * kSkipCell - 2 + j % e, y = iy * kSkipCell - 2 + (j / e) % e, z = iz * kSkipCell - 2 + j / (e * e);
+    int x = ix * kSkipCell - 1 + j % e, y = iy * kSkipCell - 1 + (j / e) % e, z = iz * kSkipCell - 1 + j / (e * e);
     x = x < 0 ? 0 : (x > nx - 1 ? nx - 1 : x);
     y = y < 0 ? 0 : (y > ny - 1 ? ny - 1 : y);
     z = z < 0 ? 0 : (z > nz - 1 ? nz - 1 : z);
@@ -179,6 +189,25 @@ __global__ void skip_cells_kernel(const float *__restrict__ vol, float *__restri
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
   __syncthreads();
   if (threadIdx.x == 0) skip[c] = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+}
+
+__global__ void skip_fine_kernel(const float *__restrict__ vol, float *__restrict__ fine, int nx, int ny, int nz, int fx,
+                                 int fy, int fz) {
+  const size_t total = static_cast<size_t>(fx) * fy * fz;
+  for (size_t c = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; c < total;
+       c += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int ix = static_cast<int>(c % fx), iy = static_cast<int>((c / fx) % fy), iz = static_cast<int>(c / (static_cast<size_t>(fx) * fy));
+    const int e = kSkipFine + 2;
+    float m = -3.0e38f;
+    for (int j = 0; j < e * e * e; ++j) {
+      int x = ix * kSkipFine - 1 + j % e, y = iy * kSkipFine - 1 + (j / e) % e, z = iz * kSkipFine - 1 + j / (e * e);
+      x = x < 0 ? 0 : (x > nx - 1 ? nx - 1 : x);
+      y = y < 0 ? 0 : (y > ny - 1 ? ny - 1 : y);
+      z = z < 0 ? 0 : (z > nz - 1 ? nz - 1 : z);
+      m = fmaxf(m, __ldg(vol + (static_cast<size_t>(z) * ny + y) * nx + x));
+    }
+    fine[c] = m;
+  }
 }
 
 __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restrict__ vol, const float *__restrict__ skip,
@@ -193,6 +222,8 @@ __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restric
   g.v = vol; g.nx = a.nx; g.ny = a.ny; g.nz = a.nz;
   g.skip = skip;
   g.cx = (a.nx + kSkipCell - 1) / kSkipCell; g.cy = (a.ny + kSkipCell - 1) / kSkipCell; g.cz = (a.nz + kSkipCell - 1) / kSkipCell;
+  g.fine = skip + static_cast<size_t>(g.cx) * g.cy * g.cz;
+  g.fx = (a.nx + kSkipFine - 1) / kSkipFine; g.fy = (a.ny + kSkipFine - 1) / kSkipFine; g.fz = (a.nz + kSkipFine - 1) / kSkipFine;
 
   float color[3] = {0.f, 0.f, 0.f}, mask = 0.f, normal[3] = {0.f, 0.f, 0.f}, depth = 0.f, flow[2] = {0.f, 0.f}, ao = 1.f;
   const float shadow = 1.f;
@@ -285,16 +316,23 @@ cudaError_t launch_raycast_iso(const float *vol, const float *skip, float *out, 
   return cudaGetLastError();
 }
 
-void raycast_skip_dims(int nx, int ny, int nz, int *cx, int *cy, int *cz) {
-  *cx = (nx + kSkipCell - 1) / kSkipCell;
-  *cy = (ny + kSkipCell - 1) / kSkipCell;
-  *cz = (nz + kSkipCell - 1) / kSkipCell;
+size_t raycast_skip_floats(int nx, int ny, int nz) {
+  const size_t c = static_cast<size_t>((nx + kSkipCell - 1) / kSkipCell) * ((ny + kSkipCell - 1) / kSkipCell) *
+                   ((nz + kSkipCell - 1) / kSkipCell);
+  const size_t f = static_cast<size_t>((nx + kSkipFine - 1) / kSkipFine) * ((ny + kSkipFine - 1) / kSkipFine) *
+                   ((nz + kSkipFine - 1) / kSkipFine);
+  return c + f;
 }
 
 cudaError_t launch_raycast_skip(const float *vol, float *skip, int nx, int ny, int nz, cudaStream_t s) {
-  int cx, cy, cz;
-  raycast_skip_dims(nx, ny, nz, &cx, &cy, &cz);
+  const int cx = (nx + kSkipCell - 1) / kSkipCell, cy = (ny + kSkipCell - 1) / kSkipCell, cz = (nz + kSkipCell - 1) / kSkipCell;
+  const int fx = (nx + kSkipFine - 1) / kSkipFine, fy = (ny + kSkipFine - 1) / kSkipFine, fz = (nz + kSkipFine - 1) / kSkipFine;
   skip_cells_kernel<<<cx * cy * cz, 128, 0, s>>>(vol, skip, nx, ny, nz, cx, cy, cz);
+  count_launch();
+  const size_t nf = static_cast<size_t>(fx) * fy * fz;
+  const size_t blocks = (nf + 255) / 256;
+  skip_fine_kernel<<<static_cast<unsigned>(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, s>>>(
+      vol, skip + static_cast<size_t>(cx) * cy * cz, nx, ny, nz, fx, fy, fz);
   count_launch();
   return cudaGetLastError();
 }

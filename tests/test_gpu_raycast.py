@@ -83,14 +83,20 @@ def test_raycast_viewport_no_ao_and_coarse_steps(isr):
 
 
 def test_raycast_skip_grid_is_the_cell_maximum(isr):
-    vol = smooth_volume(21, 11)[:, :19, :]                          # ragged: 21 x 19 x 21 voxels -> 3 x 3 x 3 cells
-    skip = isr.ops.raycast_build_skip(torch.from_numpy(np.ascontiguousarray(vol)).cuda()).cpu().numpy().reshape(3, 3, 3)
+    vol = np.ascontiguousarray(smooth_volume(21, 11)[:, :19, :])    # ragged: 21 x 19 x 21 voxels
     nz, ny, nx = vol.shape
-    for cz in range(3):
-        for cy in range(3):
-            for cx in range(3):
-                sl = tuple(slice(max(8 * c - 2, 0), min(8 * c + 10, n)) for c, n in ((cz, nz), (cy, ny), (cx, nx)))
-                assert skip[cz, cy, cx] == vol[sl].max()
+    skip = isr.ops.raycast_build_skip(torch.from_numpy(vol).cuda()).cpu().numpy()
+    off = 0
+    for cell in (8, 2):                                             # coarse grid, then the fine one
+        dims = [(n + cell - 1) // cell for n in (nz, ny, nx)]
+        grid = skip[off:off + int(np.prod(dims))].reshape(dims)
+        off += int(np.prod(dims))
+        for cz in range(dims[0]):
+            for cy in range(dims[1]):
+                for cx in range(dims[2]):
+                    sl = tuple(slice(max(cell * c - 1, 0), min(cell * c + cell + 1, n)) for c, n in ((cz, nz), (cy, ny), (cx, nx)))
+                    assert grid[cz, cy, cx] == vol[sl].max()
+    assert off == skip.size
 
 
 def test_raycast_argument_errors(isr):
