@@ -31,8 +31,11 @@ struct FinalCfg {
   static constexpr int kCols = 9 * CP;                       // useful accumulator columns
   static constexpr int kN = (kCols + 15) / 16 * 16;          // UMMA N
   static constexpr int kLd = (kCols + 7) / 8 * 8;            // columns fetched from TMEM (x8 loads)
-  static constexpr int kPitch4 = ((kLd / 4) % 2 == 0) ? kLd / 4 + 1 : kLd / 4;   // odd number of 16 B units: conflict-free
-  static constexpr int kPPitch = kPitch4 * 4;                // floats per halo row in the gather buffer
+  // floats per halo row in the gather buffer: an ODD number of 8-byte units, so that both the 64-bit stores of phase A
+  // (a half-warp = 16 consecutive halo rows) and the 64-bit tap loads of phase B (a half-warp = the 16 pixels of one
+  // tile row) fall on 16 distinct bank pairs.  (An odd number of 16-byte units with 128-bit stores left phase B with
+  // 2-way conflicts: ncu counted 63 M conflicts in 149 M shared wavefronts, LSU data pipe 68 % busy.)
+  static constexpr int kPPitch = ((kLd / 2) % 2 == 1) ? kLd : kLd + 2;
   static constexpr int kSkipFloats = 6 * 4 * 8;              // low-res skip patch of a tile: 6 rows x 4 cols x <= 8 channels
   static constexpr int kPFloats = kFPitch * kFHaloH * kPPitch;  // gather buffer proper; the skip patch follows it
   static constexpr int kPBytes = ((kPFloats + kSkipFloats) * 4 + 1023) / 1024 * 1024;
@@ -226,22 +229,18 @@ conv3x3_final_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll
         for (int c8 = 0; c8 < C::kLd / 8; ++c8) tmem_ld8(taddr + 8 * c8, v + 8 * c8);
         tmem_ld_wait();
-        float4 *dst = reinterpret_cast<float4 *>(P + static_cast<size_t>(row) * C::kPPitch);
+        float2 *dst = reinterpret_cast<float2 *>(P + static_cast<size_t>(row) * C::kPPitch);
 #pragma unroll
-        for (int c4 = 0; c4 < C::kLd / 4; ++c4)
-          dst[c4] = make_float4(__uint_as_float(v[4 * c4]), __uint_as_float(v[4 * c4 + 1]),
-                                __uint_as_float(v[4 * c4 + 2]), __uint_as_float(v[4 * c4 + 3]));
+        for (int c2 = 0; c2 < C::kLd / 2; ++c2) dst[c2] = make_float2(__uint_as_float(v[2 * c2]), __uint_as_float(v[2 * c2 + 1]));
         if (q >= 2) {   // second row group: accumulator lane L holds halo row 52 + L; rows 128..179 are new
 #pragma unroll
           for (int c8 = 0; c8 < C::kLd / 8; ++c8) tmem_ld8(taddr + N + 8 * c8, v + 8 * c8);
           tmem_ld_wait();
           const int hr = 52 + row;
           if (hr >= 128) {
-            float4 *d2 = reinterpret_cast<float4 *>(P + static_cast<size_t>(hr) * C::kPPitch);
+            float2 *d2 = reinterpret_cast<float2 *>(P + static_cast<size_t>(hr) * C::kPPitch);
 #pragma unroll
-            for (int c4 = 0; c4 < C::kLd / 4; ++c4)
-              d2[c4] = make_float4(__uint_as_float(v[4 * c4]), __uint_as_float(v[4 * c4 + 1]),
-                                   __uint_as_float(v[4 * c4 + 2]), __uint_as_float(v[4 * c4 + 3]));
+            for (int c2 = 0; c2 < C::kLd / 2; ++c2) d2[c2] = make_float2(__uint_as_float(v[2 * c2]), __uint_as_float(v[2 * c2 + 1]));
           }
         }
       }

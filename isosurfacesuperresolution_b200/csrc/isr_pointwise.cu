@@ -171,19 +171,24 @@ __global__ void warp_upscale_kernel(const float *__restrict__ prev, const float 
 // NHWC 16-bit hi|lo planes in 64-channel groups (videotools.py:8-25,49-87 + mainVideoUnshaded.py:441-445 fused).
 // One block = 16 low-res pixels of one row = 64 x 4 high-res pixels = 256 threads.
 constexpr int kPackLow = 16;
+// CP = c_prev at compile time (6 unshaded, 3 shaded; 0 = any, runtime loop).  The pass is bound by instruction issue
+// (ncu: issue slots 78 % busy, 746 instructions per high-res pixel before this form), so the channel loop is unrolled
+// without clamps or predicates and every tap address is ONE 32 x 32 + 64-bit multiply-add from the tap's base pointer.
+template <int CP>
 __global__ void __launch_bounds__(256)
 pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ prev, const float *__restrict__ flow,
-                      uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int B, int c_low, int c_prev, int h,
+                      uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int B, int c_low, int c_prev_rt, int h,
                       int w, int special_mask, int align_corners, int nparts, int is_bf16) {
   __shared__ float tile[kPackLow][129];
+  const int c_prev = CP > 0 ? CP : c_prev_rt;
   const int xb = blockIdx.x * kPackLow;
   const int y = blockIdx.y;
   const int b = blockIdx.z;
   const int H = h * 4, W = w * 4;
   const int tid = threadIdx.x;
   const int cin = c_low + 16 * c_prev;
-  for (int i = tid; i < kPackLow * 128; i += 256) tile[i >> 7][i & 127] = 0.f;
-  __syncthreads();
+  // only the padding channels [cin, 128) need zeros: every other column of an in-range pixel is written below
+  for (int i = tid; i < kPackLow * (128 - cin); i += 256) tile[i / (128 - cin)][cin + i % (128 - cin)] = 0.f;
   for (int i = tid; i < kPackLow * c_low; i += 256) {
     const int lp = i % kPackLow, c = i / kPackLow;
     if (xb + lp < w) tile[lp][c] = __ldg(low + ((static_cast<size_t>(b) * c_low + c) * h + y) * w + xb + lp);
@@ -195,36 +200,63 @@ pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ p
       const size_t plane = static_cast<size_t>(H) * W;
       const float *pb = prev + static_cast<size_t>(b) * c_prev * plane;
       const int lp = hx >> 2, dx = hx & 3;
+      float *trow = &tile[lp][c_low + dy * 4 + dx];
       if (flow != nullptr) {
         const WarpTaps t = warp_taps(flow + static_cast<size_t>(b) * 2 * h * w, h, w, 4, Y, X, align_corners);
-        // all taps of up to 6 channels are requested before the first use (24 loads in flight per thread): the pass is
-        // bound by gather latency, not by issue slots
-        for (int c0 = 0; c0 < c_prev; c0 += 6) {
-          float v[6][4];
+        if constexpr (CP > 0) {
+          // all 4 * CP taps are requested before the first use: the loads of a thread are independent
+          const char *q00 = reinterpret_cast<const char *>(pb + t.o00), *q01 = reinterpret_cast<const char *>(pb + t.o01);
+          const char *q10 = reinterpret_cast<const char *>(pb + t.o10), *q11 = reinterpret_cast<const char *>(pb + t.o11);
+          const unsigned plane_bytes = static_cast<unsigned>(plane) * 4u;   // host side checks H * W * 4 < 2^32
+          float v[CP][4];
 #pragma unroll
-          for (int c = 0; c < 6; ++c) {
-            const float *pc = pb + static_cast<size_t>(min(c0 + c, c_prev - 1)) * plane;
-            v[c][0] = __ldg(pc + t.o00); v[c][1] = __ldg(pc + t.o01); v[c][2] = __ldg(pc + t.o10); v[c][3] = __ldg(pc + t.o11);
+          for (int c = 0; c < CP; ++c) {
+            const size_t off = static_cast<size_t>(static_cast<unsigned>(c) * static_cast<unsigned long long>(plane_bytes));
+            v[c][0] = __ldg(reinterpret_cast<const float *>(q00 + off));
+            v[c][1] = __ldg(reinterpret_cast<const float *>(q01 + off));
+            v[c][2] = __ldg(reinterpret_cast<const float *>(q10 + off));
+            v[c][3] = __ldg(reinterpret_cast<const float *>(q11 + off));
           }
 #pragma unroll
-          for (int c = 0; c < 6; ++c) {
-            if (c0 + c < c_prev) {
-              const bool sm = special_mask && (c0 + c == 0);
-              float a0 = v[c][0], a1 = v[c][1], a2 = v[c][2], a3 = v[c][3];
-              if (sm) { a0 = a0 * 0.5f + 0.5f; a1 = a1 * 0.5f + 0.5f; a2 = a2 * 0.5f + 0.5f; a3 = a3 * 0.5f + 0.5f; }
-              float acc = 0.f;
-              acc += a0 * t.nw;
-              acc += a1 * t.ne;
-              acc += a2 * t.sw;
-              acc += a3 * t.se;
-              if (sm) acc = acc * 2.f - 1.f;
-              tile[lp][c_low + (c0 + c) * 16 + dy * 4 + dx] = acc;
+          for (int c = 0; c < CP; ++c) {
+            float a0 = v[c][0], a1 = v[c][1], a2 = v[c][2], a3 = v[c][3];
+            const bool sm = special_mask && c == 0;
+            if (c == 0 && sm) { a0 = a0 * 0.5f + 0.5f; a1 = a1 * 0.5f + 0.5f; a2 = a2 * 0.5f + 0.5f; a3 = a3 * 0.5f + 0.5f; }
+            float acc = 0.f;
+            acc += a0 * t.nw;
+            acc += a1 * t.ne;
+            acc += a2 * t.sw;
+            acc += a3 * t.se;
+            if (c == 0 && sm) acc = acc * 2.f - 1.f;
+            trow[c * 16] = acc;
+          }
+        } else {
+          for (int c0 = 0; c0 < c_prev; c0 += 6) {
+            float v[6][4];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              const float *pc = pb + static_cast<size_t>(min(c0 + c, c_prev - 1)) * plane;
+              v[c][0] = __ldg(pc + t.o00); v[c][1] = __ldg(pc + t.o01); v[c][2] = __ldg(pc + t.o10); v[c][3] = __ldg(pc + t.o11);
+            }
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              if (c0 + c < c_prev) {
+                const bool sm = special_mask && (c0 + c == 0);
+                float a0 = v[c][0], a1 = v[c][1], a2 = v[c][2], a3 = v[c][3];
+                if (sm) { a0 = a0 * 0.5f + 0.5f; a1 = a1 * 0.5f + 0.5f; a2 = a2 * 0.5f + 0.5f; a3 = a3 * 0.5f + 0.5f; }
+                float acc = 0.f;
+                acc += a0 * t.nw;
+                acc += a1 * t.ne;
+                acc += a2 * t.sw;
+                acc += a3 * t.se;
+                if (sm) acc = acc * 2.f - 1.f;
+                trow[(c0 + c) * 16] = acc;
+              }
             }
           }
         }
       } else {
-        for (int c = 0; c < c_prev; ++c)
-          tile[lp][c_low + c * 16 + dy * 4 + dx] = __ldg(pb + c * plane + static_cast<size_t>(Y) * W + X);
+        for (int c = 0; c < c_prev; ++c) trow[c * 16] = __ldg(pb + c * plane + static_cast<size_t>(Y) * W + X);
       }
     }
   }
@@ -739,8 +771,16 @@ cudaError_t launch_pack_recurrent(const float *low, const float *prev, const flo
                                   int B, int c_low, int c_prev, int h, int w, int special_mask, int align_corners,
                                   int nparts, int is_bf16, cudaStream_t s) {
   dim3 grid((w + kPackLow - 1) / kPackLow, h, B);
-  pack_recurrent_kernel<<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
-                                            align_corners, nparts, is_bf16);
+  const bool small_plane = static_cast<size_t>(h) * 4 * w * 4 * 4 * 8 < (1ull << 32);   // 32-bit byte offsets inside a frame
+  if (c_prev == 6 && small_plane)
+    pack_recurrent_kernel<6><<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
+                                                 align_corners, nparts, is_bf16);
+  else if (c_prev == 3 && small_plane)
+    pack_recurrent_kernel<3><<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
+                                                 align_corners, nparts, is_bf16);
+  else
+    pack_recurrent_kernel<0><<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
+                                                 align_corners, nparts, is_bf16);
   count_launch();
   return cudaGetLastError();
 }

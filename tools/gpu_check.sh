@@ -14,7 +14,7 @@ if [ "$2" != "noncu" ]; then
 timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-latency > gpurun_out/${TAG}_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 500 --csv \
     --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-latency > gpurun_out/${TAG}_ncu1.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:conv3x3_ -s 23 -c 3 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:conv3x3_ -s 58 -c 2 \
     -o gpurun_out/${TAG}_conv_full python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-latency > gpurun_out/${TAG}_ncu2.log 2>&1
 fi
 tail -3 gpurun_out/${TAG}_pytest.log; cat gpurun_out/${TAG}_bench.json; cat gpurun_out/${TAG}_bench_ref.json
