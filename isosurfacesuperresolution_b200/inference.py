@@ -153,7 +153,16 @@ class SequenceRunner:
         self.unshaded = self.model.output_channels == 6
 
     @torch.no_grad()
-    def run(self, low, flow, keep_outputs=True):
+    def run(self, low, flow, keep_outputs=True, max_batch=None):
+        """``max_batch``: process the sequences in chunks of at most that many (they are independent, and a sequence's
+        result does not depend on its batch, bit for bit), which bounds the workspace: BASELINE.json configs[4] (64
+        sequences of 512^2 -> 2048^2 per GPU) needs 32 GiB per 64-channel 4x tensor in one piece, 2 GiB with max_batch=4."""
+        if max_batch is not None and low.shape[0] > max_batch:
+            parts = [self.run(low[i:i + max_batch], flow[i:i + max_batch], keep_outputs)
+                     for i in range(0, low.shape[0], max_batch)]
+            preds = [torch.cat([p[0][j] for p in parts]) for j in range(len(parts[0][0]))]
+            rgbs = [torch.cat([p[1][j] for p in parts]) for j in range(len(parts[0][1]))]
+            return preds, rgbs, torch.cat([p[2] for p in parts])
         B, T = low.shape[:2]
         c_prev = self.model.output_channels
         preds, rgbs = [], []

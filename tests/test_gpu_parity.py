@@ -265,6 +265,18 @@ def test_fused_recurrent_equals_unfused(isr, weights):
     assert torch.equal(a, b)
 
 
+def test_sequence_runner_chunks_are_bit_identical(isr, weights):
+    """configs[4]-style micro-batching: chunks of sequences give exactly the unchunked result."""
+    net = _net(isr, weights)
+    low, flow, _ = orc.synthetic_gbuffer(5, 24, 32, 31, T=3)
+    runner = isr.SequenceRunner(net, initial_image="input", shading=_shading_from_params(isr, orc.shading_params()))
+    p_all, r_all, s_all = runner.run(cu(low), cu(flow))
+    p_ch, r_ch, s_ch = runner.run(cu(low), cu(flow), max_batch=2)
+    assert len(p_ch) == 3 and len(r_ch) == 3 and p_ch[0].shape[0] == 5
+    assert all(torch.equal(a, b) for a, b in zip(p_all, p_ch)) and all(torch.equal(a, b) for a, b in zip(r_all, r_ch))
+    assert torch.equal(s_all, s_ch)
+
+
 def test_loaded_model_facade(isr, weights):
     net = _net(isr, weights)
     lm = isr.LoadedModel({"model": net, "parameters": {"initialImage": "input"}}, torch.device("cuda"), 4)
@@ -516,7 +528,7 @@ def test_ssao_equals_oracle(isr, cfg):
 
 
 # ---- full BASELINE.json sizes through a size-independent property ---------------------------------------------------
-@pytest.mark.parametrize("cfg", ["C2", "C3", "C4"])
+@pytest.mark.parametrize("cfg", ["C2", "C3", "C4", "C5"])
 def test_full_size_crop_parity(isr, weights, cfg):
     """The network is translation-covariant with a finite receptive field (21 low-res convs + the three high-res ones and
     the bilinear steps: < 28 low-res pixels), so far enough from a crop's border the output of the FULL-size problem must
@@ -532,7 +544,8 @@ def test_full_size_crop_parity(isr, weights, cfg):
         B, h, w, cin, nm = 4, 540, 960, 56, 3
     else:
         net, wts, cin, nm = _net(isr, weights), weights, 101, 5
-        B, h, w = (16, 256, 256) if cfg == "C2" else (1, 270, 480)
+        # C5: one 4-sequence chunk of configs[4] (64 sequences of 512^2 -> 2048^2 per GPU, SequenceRunner max_batch)
+        B, h, w = {"C2": (16, 256, 256), "C3": (1, 270, 480), "C5": (4, 512, 512)}[cfg]
     g = torch.Generator(device="cuda").manual_seed(77)
     x = torch.rand(B, cin, h, w, device="cuda", generator=g) * 2 - 1
     with torch.no_grad():
