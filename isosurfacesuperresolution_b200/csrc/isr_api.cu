@@ -361,6 +361,7 @@ struct Plan {
   int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0, fin_stacked = 0, stack_w = 0, cta_pair = 0,
       full_blocks = 0, f_last_parts = 1;
   void *ws = nullptr;
+  size_t ws_need = 0;   // bytes of workspace this plan uses (checked on every call, also on a cache hit)
   Scheme trunk, tail;
   int fin_nw = 0;
   uint16_t *in_g[2] = {nullptr, nullptr};
@@ -444,7 +445,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   if (ws == nullptr || ws_bytes < need)
     return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, need);
   if (reinterpret_cast<uintptr_t>(ws) % 1024 != 0) return fail(ISR_ERR_ARG, "workspace must be 1024-byte aligned");
-  pl->B = B; pl->h = h; pl->w = w; pl->precision = precision; pl->ws = ws;
+  pl->B = B; pl->h = h; pl->w = w; pl->precision = precision; pl->ws = ws; pl->ws_need = need;
   pl->pitch = g_halo_pitch; pl->bo = g_base_offset_mode; pl->max_ctas = g_max_ctas;
   pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w; pl->cta_pair = g_cta_pair;
   pl->full_blocks = g_trunk_full_blocks;
@@ -562,6 +563,8 @@ static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision
         pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
         pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair &&
         pl->full_blocks == g_trunk_full_blocks && pl->fuse_up == g_fuse_up && pl->fin_issuers == g_final_issuers) {
+      if (ws_bytes < pl->ws_need)
+        return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, pl->ws_need);
       *out = pl;
       return ISR_OK;
     }
