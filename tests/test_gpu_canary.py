@@ -163,3 +163,56 @@ def test_raycaster_stays_inside_its_frame(isr):
         isr.ops.raycast_iso(vol, Pm, out.t, ao_samples=4, hemisphere=hemi, rotations=rot, skip=isr.ops.raycast_build_skip(vol))
         torch.cuda.synchronize()
         assert out.intact() and out.written()
+
+
+def nan_guarded(t):
+    """a copy of ``t`` with NaN on both sides: a read outside the tensor poisons whatever it feeds"""
+    big = torch.full((t.numel() + 2 * PAD + 64,), float("nan") if t.dtype.is_floating_point else 0xA5, dtype=t.dtype,
+                     device="cuda")
+    off = PAD
+    while (big.data_ptr() + off * big.element_size()) % 256:
+        off += 1
+    v = big[off:off + t.numel()].view(t.shape)
+    v.copy_(t)
+    return v
+
+
+@pytest.mark.parametrize("shape", [(1, 9, 11), (2, 19, 27), (1, 33, 130)])
+def test_no_reads_outside_the_inputs(isr, weights, shape):
+    """Inputs surrounded by NaN: every result must equal the one computed from ordinary tensors, bit for bit (a stray read
+    of a neighbour would show up as NaN or as a different value)."""
+    from argparse import Namespace
+    from isosurfacesuperresolution_b200 import ops
+    from isosurfacesuperresolution_b200.synthetic import shading_params
+    B, h, w = shape
+    opt = Namespace(upsample="bilinear", reconType="residual", useBN=False)
+    net = isr.createNetwork("EnhanceNet", 4, 101, [0, 1, 2, 3, 4], 6, opt)
+    net.load_state_dict({k: torch.from_numpy(v) for k, v in weights.items()})
+    net = net.cuda().eval()
+    low, flow = rnd(B, 5, h, w, seed=11), rnd(B, 2, h, w, seed=12) * 0.2      # large flow: taps leave the image
+    prev = rnd(B, 6, 4 * h, 4 * w, seed=13)
+    frame = rnd(B, h, w, 12, seed=14)
+    prm = shading_params()
+    with torch.no_grad():
+        a = net(low, prev, flow, special_mask=True, return_state=True)
+        b = net(nan_guarded(low), nan_guarded(prev), nan_guarded(flow), special_mask=True, return_state=True)
+    for u, v in zip(a, b):
+        if u is not None:
+            assert torch.isfinite(v).all() and torch.equal(u, v)
+    pairs = [
+        (ops.warp_upscale(prev, flow, 4, True), ops.warp_upscale(nan_guarded(prev), nan_guarded(flow), 4, True)),
+        (ops.flatten_high(prev, 4), ops.flatten_high(nan_guarded(prev), 4)),
+        (ops.shade(prev, prm), ops.shade(nan_guarded(prev), prm)),
+        (ops.shade_rgb8(prev, prm), ops.shade_rgb8(nan_guarded(prev), prm)),
+        (ops.postprocess(prev, True), ops.postprocess(nan_guarded(prev), True)),
+        (ops.initial_image(low, 6, "input", False, 4), ops.initial_image(nan_guarded(low), 6, "input", False, 4)),
+    ]
+    ia, ib = ops.ingest_gbuffer(frame, "unshaded", interleaved=True), ops.ingest_gbuffer(nan_guarded(frame), "unshaded",
+                                                                                        interleaved=True)
+    pairs += [(x, y) for x, y in zip(ia, ib) if x is not None]
+    hole = (rnd(B, h, w, seed=15) > 0.3).to(torch.uint8)
+    pairs.append((ops.inpaint_flow(flow, hole), ops.inpaint_flow(nan_guarded(flow), nan_guarded(hole))))
+    for i, (u, v) in enumerate(pairs):
+        assert torch.equal(u, v), f"pair {i}"
+        if v.dtype.is_floating_point:
+            assert torch.isfinite(v).all(), f"pair {i}"
