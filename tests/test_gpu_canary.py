@@ -216,3 +216,29 @@ def test_no_reads_outside_the_inputs(isr, weights, shape):
         assert torch.equal(u, v), f"pair {i}"
         if v.dtype.is_floating_point:
             assert torch.isfinite(v).all(), f"pair {i}"
+
+
+def test_calls_follow_the_callers_stream(isr, weights):
+    """Every entry point takes the caller's stream (asynchronous, no hidden synchronisation): the same
+    recurrence issued on a side stream, interleaved with unrelated work on the default stream, gives the same frames."""
+    from argparse import Namespace
+    from oracle import oracle as orc
+    opt = Namespace(upsample="bilinear", reconType="residual", useBN=False)
+    net = isr.createNetwork("EnhanceNet", 4, 101, [0, 1, 2, 3, 4], 6, opt)
+    net.load_state_dict({k: torch.from_numpy(v) for k, v in weights.items()})
+    net = net.cuda().eval()
+    low, flow, _ = orc.synthetic_gbuffer(2, 24, 40, 41, T=4)
+    low, flow = torch.from_numpy(low).cuda(), torch.from_numpy(flow).cuda()
+    runner = isr.SequenceRunner(net, initial_image="input")
+    ref, _, ref_state = runner.run(low, flow)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    junk = torch.zeros(4096, 4096, device="cuda")
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        out, _, state = runner.run(low, flow)
+    for _ in range(20):                       # the default stream stays busy while the side stream runs the frames
+        junk = junk @ junk
+    side.synchronize()
+    torch.cuda.synchronize()
+    assert all(torch.equal(a, b) for a, b in zip(ref, out)) and torch.equal(ref_state, state)
