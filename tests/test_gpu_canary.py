@@ -242,3 +242,46 @@ def test_calls_follow_the_callers_stream(isr, weights):
     side.synchronize()
     torch.cuda.synchronize()
     assert all(torch.equal(a, b) for a, b in zip(ref, out)) and torch.equal(ref_state, state)
+
+
+def test_two_host_threads_with_their_own_networks(isr, weights):
+    """The library keeps per-network plans and thread-local error state: two host threads, each with its own module and
+    stream, run their recurrences concurrently (ctypes releases the GIL inside the calls) and get the serial results."""
+    import threading
+    from argparse import Namespace
+    from oracle import oracle as orc
+    opt = Namespace(upsample="bilinear", reconType="residual", useBN=False)
+    jobs = []
+    for k, (hh, ww) in enumerate(((24, 40), (19, 27))):
+        net = isr.createNetwork("EnhanceNet", 4, 101, [0, 1, 2, 3, 4], 6, opt)
+        net.load_state_dict({n: torch.from_numpy(v) for n, v in weights.items()})
+        net = net.cuda().eval()
+        low, flow, _ = orc.synthetic_gbuffer(2, hh, ww, 50 + k, T=4)
+        low, flow = torch.from_numpy(low).cuda(), torch.from_numpy(flow).cuda()
+        runner = isr.SequenceRunner(net, initial_image="input")
+        ref, _, _ = runner.run(low, flow)
+        jobs.append((runner, low, flow, ref))
+    torch.cuda.synchronize()
+    results, errors = [None, None], []
+
+    def work(i):
+        try:
+            runner, low, flow, _ = jobs[i]
+            st = torch.cuda.Stream()
+            st.wait_stream(torch.cuda.default_stream())
+            with torch.cuda.stream(st):
+                for _ in range(3):
+                    out, _, _ = runner.run(low, flow)
+            st.synchronize()
+            results[i] = out
+        except Exception as e:                                # surfaced in the main thread
+            errors.append(e)
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for i in range(2):
+        assert all(torch.equal(a, b) for a, b in zip(jobs[i][3], results[i]))
