@@ -32,6 +32,7 @@ static int g_final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (meas
                                   // 0 = generic single-CTA N=16 kernel
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
 static int g_fuse_up = 1;   // bilinear nets: the 4x upsample + first 4x conv run as one phase-decomposed kernel (isr_up2.cu)
+static int g_final_w_parts = 0;   // output conv weight planes: 0 = the scheme's choice, 1 = single, 2 = hi + lo
 static int g_final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
 static int g_pdl = 1;   // CTA-pair convs are launched with programmatic stream serialization (prologue overlaps the previous tail)
 static int g_trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
@@ -370,7 +371,7 @@ struct Plan {
   uint16_t *f_last = nullptr, *u2 = nullptr, *c2 = nullptr, *u4 = nullptr, *c4 = nullptr;
   int idx_post1 = 0, idx_post4 = 0, idx_final = 0;
   // fused 4x upsample + conv (isr_up2.cu): the phase kernel, the two band convs and their buffers
-  int fuse_up = 0, fin_issuers = 0;
+  int fuse_up = 0, fin_issuers = 0, fin_w_parts = 0;
   struct Fused {
     int on = 0, hl = 0, wl = 0, in_parts = 1;   // low-res size and stored planes of the input
     const uint16_t *src = nullptr;
@@ -450,7 +451,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w; pl->cta_pair = g_cta_pair;
   pl->full_blocks = g_trunk_full_blocks;
   pl->fuse_up = g_fuse_up;
-  pl->fin_issuers = g_final_issuers;
+  pl->fin_issuers = g_final_issuers; pl->fin_w_parts = g_final_w_parts;
   uint8_t *base = static_cast<uint8_t *>(ws);
   auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
   const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
@@ -539,6 +540,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->idx_final = static_cast<int>(pl->convs.size());
   Scheme Fs = Hs;
   if (pl->fin_nw > 0) Fs.nw = pl->fin_nw;
+  if (g_final_w_parts > 0) Fs.nw = g_final_w_parts;
   if (net->layers[24].packed_fin != nullptr && g_final_stacked == 1) {
     const int cp = final_cp(net->cout), nrows = final_rows(cp);
     const uint16_t *wb = net->layers[24].packed_fin + (Fs.bf16 ? 0 : static_cast<size_t>(2) * nrows * 64);
@@ -562,7 +564,7 @@ static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision
     if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
         pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
         pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair &&
-        pl->full_blocks == g_trunk_full_blocks && pl->fuse_up == g_fuse_up && pl->fin_issuers == g_final_issuers) {
+        pl->full_blocks == g_trunk_full_blocks && pl->fuse_up == g_fuse_up && pl->fin_issuers == g_final_issuers && pl->fin_w_parts == g_final_w_parts) {
       if (ws_bytes < pl->ws_need)
         return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, pl->ws_need);
       *out = pl;
@@ -672,6 +674,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "final_issuers") == 0) {
     if (value != 1 && value != 3) return fail(ISR_ERR_ARG, "final_issuers must be 1 or 3");
     slot = &g_final_issuers;
+  } else if (key != nullptr && strcmp(key, "final_w_parts") == 0) {
+    if (value < 0 || value > 2) return fail(ISR_ERR_ARG, "final_w_parts must be 0 (scheme), 1 or 2");
+    slot = &g_final_w_parts;
   } else if (key != nullptr && strcmp(key, "pdl") == 0) {
     if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "pdl must be 0 or 1");
     slot = &g_pdl;

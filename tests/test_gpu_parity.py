@@ -277,6 +277,24 @@ def test_sequence_runner_chunks_are_bit_identical(isr, weights):
     assert torch.equal(s_all, s_ch)
 
 
+def test_output_conv_single_weight_plane_tunable(isr, golden, weights):
+    """final_w_parts = 1 drops the low weight plane of the output conv (-1.7 % step time, +0.4e-3 error,
+    profiles/r01_precision_sweep_final_w_parts.json); not the default, but it must stay inside the parity bar."""
+    g = golden("enhancenet_forward")
+    net = _net(isr, weights)
+    old = isr._lib.set_tunable("final_w_parts", 1)
+    try:
+        with torch.no_grad():
+            recon, _ = net(cu(g["x"]))
+        _check_net(recon, g["recon_bilinear"])
+    finally:
+        isr._lib.set_tunable("final_w_parts", old)
+    with torch.no_grad():
+        recon2, _ = net(cu(g["x"]))
+    assert not torch.equal(recon, recon2)          # the tunable did change the arithmetic, and was restored
+    _check_net(recon2, g["recon_bilinear"])
+
+
 def test_loaded_model_facade(isr, weights):
     net = _net(isr, weights)
     lm = isr.LoadedModel({"model": net, "parameters": {"initialImage": "input"}}, torch.device("cuda"), 4)

@@ -47,9 +47,13 @@ for seed in (11, 12, 13):
 for mk in modes:
     r = {}
     m = mk
-    if ":" in mk:                      # "hybrid:K" = ISR_PREC_HYBRID with K fully split residual blocks
-        m, k = mk.split(":")
-        isr._lib.set_tunable("trunk_full_blocks", int(k))
+    isr._lib.set_tunable("final_w_parts", 0)
+    if ":" in mk:                      # "hybrid:K[:F]" = ISR_PREC_HYBRID with K fully split residual blocks, F output-conv weight planes
+        parts = mk.split(":")
+        m = parts[0]
+        isr._lib.set_tunable("trunk_full_blocks", int(parts[1]))
+        if len(parts) > 2:
+            isr._lib.set_tunable("final_w_parts", int(parts[2]))
     with torch.no_grad():
         for ups in ("bilinear", "nearest"):
             n = net_for(ups)
