@@ -181,7 +181,7 @@ int isr_raycast_iso(const float *volume, int nx, int ny, int nz, const float *pa
                     const float *ao_rotations_host, int ao_samples, int binary_steps, const int *viewport_host,
                     const float *skip, float *out, int width, int height, void *stream);
 /* Optional empty-space grids for isr_raycast_iso (`skip`, DEVICE, may be NULL): the max of the brick over each 8^3 and
- * each 2^3 macro-cell plus the trilinear footprint, built once per volume (GVDB's brick topology plays this role in the
+ * each 2^3 macro-cell plus the trilinear footprint, and over the 8 voxels of every interpolation cell, built once per volume (GVDB's brick topology plays this role in the
  * reference).  A cell whose max is below iso cannot contain a sample >= iso, so the march steps over it; the samples
  * that are evaluated and the frame are IDENTICAL to the plain march. */
 int isr_raycast_skip_bytes(int nx, int ny, int nz, size_t *bytes);

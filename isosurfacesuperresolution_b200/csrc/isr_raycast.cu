@@ -48,6 +48,7 @@ struct Grid {
   int cx, cy, cz;
   const float *__restrict__ fine;   // max per fine macro-cell (follows the coarse grid in the same buffer)
   int fx, fy, fz;
+  const float *__restrict__ dual;   // max of the 8 voxels of each interpolation cell, [nz][ny][nx] (follows the fine grid)
 };
 
 __device__ __forceinline__ void cell(float p, int n, int &i, float &f) {
@@ -127,8 +128,41 @@ __device__ __forceinline__ int hop(const float *__restrict__ grid, int gx, int g
   return k < 1 ? 1 : (k > (1 << 20) ? (1 << 20) : k);
 }
 
+// Third level: the interpolation cell itself.  A sample at p interpolates the 8 voxels (i0, i0 + 1) per axis with
+// i0 = the index cell() computes; dual[i0] is their max, so the bound is exact for the sample at p, and for the
+// following samples as long as they stay inside [i0 + 0.5, i0 + 1.5) per axis (open-ended at the clamped brick faces).
+// The samples stepped over keep eps = 1/512 voxel of distance to the faces along every axis (rounding of p is ~1e-4).
+__device__ __forceinline__ int hop_dual(const Grid &g, V3 p, V3 d, float iso, float inv_step) {
+  int i0[3];
+  float f;
+  cell(p.x, g.nx, i0[0], f);
+  cell(p.y, g.ny, i0[1], f);
+  cell(p.z, g.nz, i0[2], f);
+  if (!(__ldg(g.dual + (static_cast<size_t>(i0[2]) * g.ny + i0[1]) * g.nx + i0[0]) < iso)) return 0;
+  const float eps = 1.0f / 512.0f;
+  float te = 3.0e38f;
+  const float pc[3] = {p.x, p.y, p.z}, dc[3] = {d.x, d.y, d.z};
+  const int n[3] = {g.nx, g.ny, g.nz};
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    if (dc[a] > 1e-12f) {
+      if (i0[a] < n[a] - 2) {                                // otherwise the cell extends to +infinity (clamped)
+        const float ta = ((static_cast<float>(i0[a]) + 1.5f - eps) - pc[a]) / dc[a];
+        te = ta < te ? ta : te;
+      }
+    } else if (dc[a] < -1e-12f) {
+      if (i0[a] > 0) {
+        const float ta = ((static_cast<float>(i0[a]) + 0.5f + eps) - pc[a]) / dc[a];
+        te = ta < te ? ta : te;
+      }
+    }
+  }
+  int k = te > 0.f ? static_cast<int>(floorf(te * inv_step)) : 1;
+  return k < 1 ? 1 : (k > (1 << 20) ? (1 << 20) : k);
+}
+
 // fixed-step march: first sample >= iso at t = t0 + i * step; returns false when the ray leaves the brick.
-// With the skip grids (skip_cells_kernel: 8^3 macro-cells, then 2^3) whole runs of samples that cannot reach iso are
+// With the skip grids (8^3 macro-cells, then 2^3, then the interpolation cell itself) whole runs of samples that cannot reach iso are
 // stepped over.  Only the index i advances -- the samples that ARE evaluated sit at the same t = t0 + i * step as
 // without the grids, so the result is identical to the plain march (tests compare the two bit for bit).
 __device__ __forceinline__ bool march(const Grid &g, V3 p0, V3 d, float iso, float step, float &t_hit) {
@@ -143,6 +177,7 @@ __device__ __forceinline__ bool march(const Grid &g, V3 p0, V3 d, float iso, flo
     if (g.skip != nullptr) {
       int k = hop(g.skip, g.cx, g.cy, g.cz, kSkipCell, p, d, iso, inv_step);
       if (k == 0) k = hop(g.fine, g.fx, g.fy, g.fz, kSkipFine, p, d, iso, inv_step);
+      if (k == 0) k = hop_dual(g, p, d, iso, inv_step);
       if (k > 0) { i += k; continue; }
     }
     if (sample(g, p) >= iso) { t_hit = t; return true; }
@@ -210,6 +245,22 @@ __global__ void skip_fine_kernel(const float *__restrict__ vol, float *__restric
   }
 }
 
+// dual[z][y][x] = max of the 8 voxels (x..x+1, y..y+1, z..z+1), indices clamped: the interpolation cell of cell()
+__global__ void skip_dual_kernel(const float *__restrict__ vol, float *__restrict__ dual, int nx, int ny, int nz) {
+  const size_t total = static_cast<size_t>(nx) * ny * nz;
+  for (size_t c = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; c < total;
+       c += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int x = static_cast<int>(c % nx), y = static_cast<int>((c / nx) % ny), z = static_cast<int>(c / (static_cast<size_t>(nx) * ny));
+    const int x1 = x + 1 < nx ? x + 1 : x, y1 = y + 1 < ny ? y + 1 : y, z1 = z + 1 < nz ? z + 1 : z;
+    float m = -3.0e38f;
+    const int xs[2] = {x, x1}, ys[2] = {y, y1}, zs[2] = {z, z1};
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      m = fmaxf(m, __ldg(vol + (static_cast<size_t>(zs[j >> 2]) * ny + ys[(j >> 1) & 1]) * nx + xs[j & 1]));
+    dual[c] = m;
+  }
+}
+
 __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restrict__ vol, const float *__restrict__ skip,
                                                           float *__restrict__ out, const __grid_constant__ RaycastArgs a) {
   // 8 x 4 pixels per warp, 2 x 2 warps per block (16 x 8 pixels)
@@ -224,6 +275,7 @@ __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restric
   g.cx = (a.nx + kSkipCell - 1) / kSkipCell; g.cy = (a.ny + kSkipCell - 1) / kSkipCell; g.cz = (a.nz + kSkipCell - 1) / kSkipCell;
   g.fine = skip + static_cast<size_t>(g.cx) * g.cy * g.cz;
   g.fx = (a.nx + kSkipFine - 1) / kSkipFine; g.fy = (a.ny + kSkipFine - 1) / kSkipFine; g.fz = (a.nz + kSkipFine - 1) / kSkipFine;
+  g.dual = g.fine + static_cast<size_t>(g.fx) * g.fy * g.fz;
 
   float color[3] = {0.f, 0.f, 0.f}, mask = 0.f, normal[3] = {0.f, 0.f, 0.f}, depth = 0.f, flow[2] = {0.f, 0.f}, ao = 1.f;
   const float shadow = 1.f;
@@ -321,7 +373,7 @@ size_t raycast_skip_floats(int nx, int ny, int nz) {
                    ((nz + kSkipCell - 1) / kSkipCell);
   const size_t f = static_cast<size_t>((nx + kSkipFine - 1) / kSkipFine) * ((ny + kSkipFine - 1) / kSkipFine) *
                    ((nz + kSkipFine - 1) / kSkipFine);
-  return c + f;
+  return c + f + static_cast<size_t>(nx) * ny * nz;
 }
 
 cudaError_t launch_raycast_skip(const float *vol, float *skip, int nx, int ny, int nz, cudaStream_t s) {
@@ -333,6 +385,11 @@ cudaError_t launch_raycast_skip(const float *vol, float *skip, int nx, int ny, i
   const size_t blocks = (nf + 255) / 256;
   skip_fine_kernel<<<static_cast<unsigned>(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, s>>>(
       vol, skip + static_cast<size_t>(cx) * cy * cz, nx, ny, nz, fx, fy, fz);
+  count_launch();
+  const size_t nv = static_cast<size_t>(nx) * ny * nz;
+  const size_t vb = (nv + 255) / 256;
+  skip_dual_kernel<<<static_cast<unsigned>(vb < 148 * 16 ? vb : 148 * 16), 256, 0, s>>>(
+      vol, skip + static_cast<size_t>(cx) * cy * cz + nf, nx, ny, nz);
   count_launch();
   return cudaGetLastError();
 }

@@ -96,6 +96,12 @@ def test_raycast_skip_grid_is_the_cell_maximum(isr):
                 for cx in range(dims[2]):
                     sl = tuple(slice(max(cell * c - 1, 0), min(cell * c + cell + 1, n)) for c, n in ((cz, nz), (cy, ny), (cx, nx)))
                     assert grid[cz, cy, cx] == vol[sl].max()
+    dual = skip[off:off + vol.size].reshape(vol.shape)             # third level: max of each interpolation cell
+    off += vol.size
+    for z in range(nz):
+        for y in range(ny):
+            for x in range(nx):
+                assert dual[z, y, x] == vol[z:z + 2, y:y + 2, x:x + 2].max()
     assert off == skip.size
 
 
