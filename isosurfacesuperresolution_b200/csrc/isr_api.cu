@@ -32,6 +32,7 @@ static int g_final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (meas
                                   // 0 = generic single-CTA N=16 kernel
 static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
 static int g_fuse_up = 1;   // bilinear nets: the 4x upsample + first 4x conv run as one phase-decomposed kernel (isr_up2.cu)
+static int g_raycast_two_pass = 1;   // AO of the ray-caster as a second pass with one thread per (pixel, ray): 0 never, 1 auto, 2 always
 static int g_final_w_parts = 0;   // output conv weight planes: 0 = the scheme's choice, 1 = single, 2 = hi + lo
 static int g_final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
 static int g_pdl = 1;   // CTA-pair convs are launched with programmatic stream serialization (prologue overlaps the previous tail)
@@ -674,6 +675,9 @@ int isr_set_tunable(const char *key, int value) {
   } else if (key != nullptr && strcmp(key, "final_issuers") == 0) {
     if (value != 1 && value != 3) return fail(ISR_ERR_ARG, "final_issuers must be 1 or 3");
     slot = &g_final_issuers;
+  } else if (key != nullptr && strcmp(key, "raycast_two_pass") == 0) {
+    if (value < 0 || value > 2) return fail(ISR_ERR_ARG, "raycast_two_pass must be 0 (never), 1 (auto) or 2 (always)");
+    slot = &g_raycast_two_pass;
   } else if (key != nullptr && strcmp(key, "final_w_parts") == 0) {
     if (value < 0 || value > 2) return fail(ISR_ERR_ARG, "final_w_parts must be 0 (scheme), 1 or 2");
     slot = &g_final_w_parts;
@@ -901,7 +905,11 @@ int isr_raycast_iso(const float *volume, int nx, int ny, int nz, const float *pa
   if (rc != ISR_OK) return rc;
   static thread_local RaycastArgs a;
   a.width = width; a.height = height; a.nx = nx; a.ny = ny; a.nz = nz;
-  a.binary_steps = binary_steps; a.ao_samples = ao_samples;
+  a.binary_steps = binary_steps; a.ao_samples = ao_samples; 
+  // measured on B200: the second pass pays for redoing the primary hits when the AO rays dominate and the frame alone
+  // cannot fill the GPU (480x270, 32 rays: 1.7x faster); with 8 rays or at 1080p the one-pass kernel is faster
+  a.ao_two_pass = g_raycast_two_pass == 2 ||
+                  (g_raycast_two_pass == 1 && ao_samples >= 16 && static_cast<size_t>(width) * height <= 600000);
   if (viewport_host != nullptr) {
     memcpy(a.viewport, viewport_host, sizeof a.viewport);
   } else {

@@ -60,7 +60,7 @@ cudaError_t launch_ssao(const float *input, int es, int rs, int inx, int iny, in
 
 // isr_raycast.cu: everything the ray-caster needs, passed by value (about 8.6 KB of kernel parameters)
 struct RaycastArgs {
-  int width, height, nx, ny, nz, binary_steps, ao_samples;
+  int width, height, nx, ny, nz, binary_steps, ao_samples, ao_two_pass;
   int viewport[4];
   float p[81];                // include/isr.h ISR_RC_*
   float hemisphere[4 * 512];

@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restric
       depth = cur[2] / cur[3];
       normal[0] = nm[0]; normal[1] = nm[1]; normal[2] = nm[2];
       // ambient occlusion: hemisphere rays through the plain surface tracer (render_kernel.cu:109-148)
-      if (a.ao_samples > 0) {
+      if (a.ao_samples > 0 && !a.ao_two_pass) {
         const float ao_radius = P[ISR_RC_AO_RADIUS];
         const V3 apos = hit - P[ISR_RC_AO_BIAS] * rdir;
         const V3 ap0 = inv_vdel * (apos - bmin);
@@ -361,10 +361,104 @@ __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restric
   o[2] = make_float4(flow[0], flow[1], ao, shadow);
 }
 
+// Second pass of the two-pass form (RaycastArgs::ao_two_pass): ambient occlusion with ONE THREAD PER (pixel, AO ray).
+// In the one-pass kernel a thread traces all AO rays of its pixel: ncu showed 13 of 32 lanes active and 16 % of the warp
+// slots occupied (pixels that miss idle, rays differ in length).  Here a block owns 8 x 2 pixels: 16 threads redo the
+// primary hit (same expressions as the first pass), all 128 threads then take (pixel, ray) pairs, and the per-ray values
+// are summed per pixel IN SAMPLE ORDER from shared memory, so the frame equals the one-pass frame bit for bit.
+constexpr int kAoPix = 16;
+__global__ void __launch_bounds__(128) raycast_ao_kernel(const float *__restrict__ vol, const float *__restrict__ skip,
+                                                         float *__restrict__ out, const __grid_constant__ RaycastArgs a) {
+  __shared__ float s_val[kAoPix][512];
+  __shared__ float s_rec[kAoPix][12];     // apos (index space) 0..2, apos (world) 3..5, normal 6..8, hit flag 9
+  const float *P = a.p;
+  Grid g;
+  g.v = vol; g.nx = a.nx; g.ny = a.ny; g.nz = a.nz;
+  g.skip = skip;
+  g.cx = (a.nx + kSkipCell - 1) / kSkipCell; g.cy = (a.ny + kSkipCell - 1) / kSkipCell; g.cz = (a.nz + kSkipCell - 1) / kSkipCell;
+  g.fine = skip + static_cast<size_t>(g.cx) * g.cy * g.cz;
+  g.fx = (a.nx + kSkipFine - 1) / kSkipFine; g.fy = (a.ny + kSkipFine - 1) / kSkipFine; g.fz = (a.nz + kSkipFine - 1) / kSkipFine;
+  g.dual = g.fine + static_cast<size_t>(g.fx) * g.fy * g.fz;
+  const V3 bmin = ld3(P + ISR_RC_BOX_MIN);
+  const float vdel = P[ISR_RC_VOXEL], iso = P[ISR_RC_ISO], step = P[ISR_RC_STEP];
+  const float inv_vdel = 1.0f / vdel;
+  const int tid = threadIdx.x;
+  if (tid < kAoPix) {
+    const int x = blockIdx.x * 8 + (tid & 7), y = blockIdx.y * 2 + (tid >> 3);
+    float flag = 0.f;
+    if (x < a.width && y < a.height && x >= a.viewport[0] && y >= a.viewport[1] && x < a.viewport[2] && y < a.viewport[3]) {
+      const float sx = (static_cast<float>(x) + 0.5f) / static_cast<float>(a.width);
+      const float sy = (static_cast<float>(y) + 0.5f) / static_cast<float>(a.height);
+      const V3 rpos = ld3(P + ISR_RC_CAM_POS);
+      const V3 rdir = normalize3((sx * ld3(P + ISR_RC_CAM_U) + sy * ld3(P + ISR_RC_CAM_V)) + ld3(P + ISR_RC_CAM_S));
+      const V3 p0 = inv_vdel * (rpos - bmin);
+      float t_in;
+      if (march(g, p0, rdir, iso, step, t_in)) {
+        float lo = t_in - step, up = t_in;
+        for (int i = 0; i < a.binary_steps; ++i) {
+          const float mid = 0.5f * (lo + up);
+          if (sample(g, p0 + mid * rdir) >= iso) up = mid; else lo = mid;
+        }
+        const V3 p = p0 + lo * rdir;
+        const V3 hit = vdel * p + bmin;
+        V3 grad = v3(sample(g, v3(p.x - 0.5f, p.y, p.z)) - sample(g, v3(p.x + 0.5f, p.y, p.z)),
+                     sample(g, v3(p.x, p.y - 0.5f, p.z)) - sample(g, v3(p.x, p.y + 0.5f, p.z)),
+                     sample(g, v3(p.x, p.y, p.z - 0.5f)) - sample(g, v3(p.x, p.y, p.z + 0.5f)));
+        const float gl = len3(grad);
+        const V3 norm = gl > 1e-6f ? v3(grad.x / gl, grad.y / gl, grad.z / gl) : v3(0.f, 0.f, 0.f);
+        const V3 apos = hit - P[ISR_RC_AO_BIAS] * rdir;
+        const V3 ap0 = inv_vdel * (apos - bmin);
+        s_rec[tid][0] = ap0.x; s_rec[tid][1] = ap0.y; s_rec[tid][2] = ap0.z;
+        s_rec[tid][3] = apos.x; s_rec[tid][4] = apos.y; s_rec[tid][5] = apos.z;
+        s_rec[tid][6] = norm.x; s_rec[tid][7] = norm.y; s_rec[tid][8] = norm.z;
+        flag = 1.f;
+      }
+    }
+    s_rec[tid][9] = flag;
+  }
+  __syncthreads();
+  const float ao_radius = P[ISR_RC_AO_RADIUS];
+  for (int pair = tid; pair < kAoPix * a.ao_samples; pair += 128) {
+    const int pix = pair % kAoPix, sidx = pair / kAoPix;
+    if (s_rec[pix][9] == 0.f) continue;
+    const int x = blockIdx.x * 8 + (pix & 7), y = blockIdx.y * 2 + (pix >> 3);
+    const V3 ap0 = v3(s_rec[pix][0], s_rec[pix][1], s_rec[pix][2]);
+    const V3 apos = v3(s_rec[pix][3], s_rec[pix][4], s_rec[pix][5]);
+    const V3 norm = v3(s_rec[pix][6], s_rec[pix][7], s_rec[pix][8]);
+    const V3 noise = ld3(a.rotations + 4 * ((x % 4) + 4 * (y % 4)));
+    const V3 tangent = normalize3(noise - dot3(noise, norm) * norm);
+    const V3 bitangent = cross3(norm, tangent);
+    const V3 st = normalize3(ld3(a.hemisphere + 4 * sidx));
+    const V3 sw = v3(dot3(v3(tangent.x, bitangent.x, norm.x), st), dot3(v3(tangent.y, bitangent.y, norm.y), st),
+                     dot3(v3(tangent.z, bitangent.z, norm.z), st));
+    float value = 1.f, th;
+    if (march(g, ap0, sw, iso, step, th)) {
+      const V3 h2 = vdel * (ap0 + th * sw) + bmin;
+      const float dist = len3(apos - h2);
+      float yy = (ao_radius / dist - 1.0f) / (0.0f - 1.0f);
+      yy = yy < 0.f ? 0.f : (yy > 1.f ? 1.f : yy);
+      value = (yy * yy) * (3.0f - 2.0f * yy);
+    }
+    s_val[pix][sidx] = value;
+  }
+  __syncthreads();
+  if (tid < kAoPix && s_rec[tid][9] != 0.f) {
+    const int x = blockIdx.x * 8 + (tid & 7), y = blockIdx.y * 2 + (tid >> 3);
+    float acc = 0.f;
+    for (int sidx = 0; sidx < a.ao_samples; ++sidx) acc = acc + s_val[tid][sidx];
+    out[12 * (static_cast<size_t>(y) * a.width + x) + 10] = acc / static_cast<float>(a.ao_samples);
+  }
+}
+
 cudaError_t launch_raycast_iso(const float *vol, const float *skip, float *out, const RaycastArgs &args, cudaStream_t s) {
   const dim3 grid((args.width + 15) / 16, (args.height + 7) / 8);
   raycast_iso_kernel<<<grid, 128, 0, s>>>(vol, skip, out, args);
   count_launch();
+  if (args.ao_samples > 0 && args.ao_two_pass) {
+    const dim3 grid2((args.width + 7) / 8, (args.height + 1) / 2);
+    raycast_ao_kernel<<<grid2, 128, 0, s>>>(vol, skip, out, args);
+    count_launch();
+  }
   return cudaGetLastError();
 }
 

@@ -67,6 +67,18 @@ def test_raycast_bit_exact_against_oracle(isr, scene):
     # the empty-space grid changes which samples are evaluated, never their positions or the frame
     fast = run_gpu(isr, vol, P, W, H, skip=True, ao_samples=8, hemisphere=hemi, rotations=rot)
     assert np.array_equal(fast, ref)
+    # one-pass form (a thread traces all AO rays of its pixel) and two-pass form (one thread per (pixel, ray), summed in
+    # sample order; chosen automatically for small frames with many rays): same frame
+    try:
+        for mode in (0, 2):
+            isr._lib.set_tunable("raycast_two_pass", mode)
+            for skip in (False, True):
+                one = run_gpu(isr, vol, P, W, H, skip=skip, ao_samples=8, hemisphere=hemi, rotations=rot)
+                assert np.array_equal(one, ref), f"two_pass mode {mode}"
+    finally:
+        assert isr._lib.set_tunable("raycast_two_pass", 1) == 2
+    many = run_gpu(isr, vol, P, W, H, skip=True, ao_samples=40, hemisphere=hemi, rotations=rot)     # auto -> two-pass
+    assert np.array_equal(many, orc.raycast_iso(vol, P, W, H, ao_samples=40, hemisphere=hemi, rotations=rot))
     if scene != "sphere":
         assert ref[..., 10][ref[..., 3] == 1].min() < (0.9 if scene == "two_spheres" else 1.0)   # AO rays did hit something
 
