@@ -160,9 +160,12 @@ def test_raycaster_stays_inside_its_frame(isr):
         Pm, _, _ = make_params(24, [0.0, 0.1, -1.5], [0, 0, 0], W, H)
         out = Guarded((H, W, 12))
         hemi, rot = isr.ops.raycast_ao_tables()
-        isr.ops.raycast_iso(vol, Pm, out.t, ao_samples=4, hemisphere=hemi, rotations=rot, skip=isr.ops.raycast_build_skip(vol))
-        torch.cuda.synchronize()
-        assert out.intact() and out.written()
+        for n_ao in (4, 20):                                   # one-pass kernel, then the two-pass form (>= 16 rays)
+            out.t.fill_(F_SENT)
+            isr.ops.raycast_iso(vol, Pm, out.t, ao_samples=n_ao, hemisphere=hemi, rotations=rot,
+                                skip=isr.ops.raycast_build_skip(vol))
+            torch.cuda.synchronize()
+            assert out.intact() and out.written()
 
 
 def nan_guarded(t):
