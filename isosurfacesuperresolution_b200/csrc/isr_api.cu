@@ -906,10 +906,9 @@ int isr_raycast_iso(const float *volume, int nx, int ny, int nz, const float *pa
   static thread_local RaycastArgs a;
   a.width = width; a.height = height; a.nx = nx; a.ny = ny; a.nz = nz;
   a.binary_steps = binary_steps; a.ao_samples = ao_samples; 
-  // measured on B200: the second pass pays for redoing the primary hits when the AO rays dominate and the frame alone
-  // cannot fill the GPU (480x270, 32 rays: 1.7x faster); with 8 rays or at 1080p the one-pass kernel is faster
-  a.ao_two_pass = g_raycast_two_pass == 2 ||
-                  (g_raycast_two_pass == 1 && ao_samples >= 16 && static_cast<size_t>(width) * height <= 600000);
+  // measured on B200 (profiles/r01_raycast_one_vs_two_pass.txt): from 8 rays on the second pass wins at every frame size
+  // (480x270, 32 rays: 2.3-2.5x; 1080p: 1.2x); with 4 rays its fixed cost is not recovered
+  a.ao_two_pass = g_raycast_two_pass == 2 || (g_raycast_two_pass == 1 && ao_samples >= 8);
   if (viewport_host != nullptr) {
     memcpy(a.viewport, viewport_host, sizeof a.viewport);
   } else {

@@ -327,6 +327,7 @@ __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restric
       depth = cur[2] / cur[3];
       normal[0] = nm[0]; normal[1] = nm[1]; normal[2] = nm[2];
       // ambient occlusion: hemisphere rays through the plain surface tracer (render_kernel.cu:109-148)
+      if (a.ao_samples > 0 && a.ao_two_pass) ao = lo;   // the hit parameter, for raycast_ao_kernel (which overwrites it)
       if (a.ao_samples > 0 && !a.ao_two_pass) {
         const float ao_radius = P[ISR_RC_AO_RADIUS];
         const V3 apos = hit - P[ISR_RC_AO_BIAS] * rdir;
@@ -363,8 +364,9 @@ __global__ void __launch_bounds__(128) raycast_iso_kernel(const float *__restric
 
 // Second pass of the two-pass form (RaycastArgs::ao_two_pass): ambient occlusion with ONE THREAD PER (pixel, AO ray).
 // In the one-pass kernel a thread traces all AO rays of its pixel: ncu showed 13 of 32 lanes active and 16 % of the warp
-// slots occupied (pixels that miss idle, rays differ in length).  Here a block owns 8 x 2 pixels: 16 threads redo the
-// primary hit (same expressions as the first pass), all 128 threads then take (pixel, ray) pairs, and the per-ray values
+// slots occupied (pixels that miss idle, rays differ in length).  Here a block owns 8 x 2 pixels: 16 threads rebuild the
+// hit point and normal from the ray parameter the first pass left in the AO channel (same expressions, no march), all
+// 128 threads then take (pixel, ray) pairs, and the per-ray values
 // are summed per pixel IN SAMPLE ORDER from shared memory, so the frame equals the one-pass frame bit for bit.
 constexpr int kAoPix = 16;
 __global__ void __launch_bounds__(128) raycast_ao_kernel(const float *__restrict__ vol, const float *__restrict__ skip,
@@ -392,13 +394,9 @@ __global__ void __launch_bounds__(128) raycast_ao_kernel(const float *__restrict
       const V3 rpos = ld3(P + ISR_RC_CAM_POS);
       const V3 rdir = normalize3((sx * ld3(P + ISR_RC_CAM_U) + sy * ld3(P + ISR_RC_CAM_V)) + ld3(P + ISR_RC_CAM_S));
       const V3 p0 = inv_vdel * (rpos - bmin);
-      float t_in;
-      if (march(g, p0, rdir, iso, step, t_in)) {
-        float lo = t_in - step, up = t_in;
-        for (int i = 0; i < a.binary_steps; ++i) {
-          const float mid = 0.5f * (lo + up);
-          if (sample(g, p0 + mid * rdir) >= iso) up = mid; else lo = mid;
-        }
+      const float *rec = out + 12 * (static_cast<size_t>(y) * a.width + x);
+      if (rec[3] == 1.f) {                                   // hit: the first pass left the ray parameter in the AO channel
+        const float lo = rec[10];
         const V3 p = p0 + lo * rdir;
         const V3 hit = vdel * p + bmin;
         V3 grad = v3(sample(g, v3(p.x - 0.5f, p.y, p.z)) - sample(g, v3(p.x + 0.5f, p.y, p.z)),
