@@ -269,8 +269,19 @@ int isr_debug_conv3x3(const float *x, const float *weight, const float *bias, co
                       size_t workspace_bytes, void *stream);
 int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
 
-/* Tunables of the convolution kernel's shared-memory operand addressing (see DESIGN.md "UMMA descriptors"):
- * key "halo_pitch" (10 | 16), "base_offset_mode" (0 | 1), "max_ctas" (0 = #SMs).  Returns previous value. */
+/* Process-wide tunables for tests, experiments and bench ablations (defaults in brackets); returns the previous value,
+ * or a negative ISR_ERR_* for an unknown key / value:
+ *   "halo_pitch" (10 | [16]), "base_offset_mode" ([0] | 1), "max_ctas" ([0] = #SMs)   operand addressing, DESIGN.md 4.1
+ *   "cta_pair" (0 | [1])             CTA-pair (cta_group::2) form of the 64->64 conv
+ *   "stack_w" (0 | [1])              hi/lo weight planes as one N=128 B operand
+ *   "pdl" (0 | [1])                  programmatic dependent launch between consecutive convs
+ *   "fuse_up" (0 | [1])              bilinear 2x upsample fused into the following conv (four phase convolutions)
+ *   "trunk_full_blocks" (0..10, [4]) residual blocks of ISR_PREC_HYBRID that run fully split
+ *   "final_stacked" (0 | [1] | 2)    output conv: generic / tap-stacked / CTA-pair N=16
+ *   "final_issuers" (1 | [3])        MMA-issuing warps of the tap-stacked output conv
+ *   "final_w_parts" ([0] = scheme | 1 | 2)   weight planes of the output conv
+ *   "raycast_two_pass" (0 | [1] = from 8 AO rays on | 2)   ambient occlusion of the ray-caster as a second pass
+ *   "dbg"                            bit mask of bench experiments (tools/), 0 in production */
 int isr_set_tunable(const char *key, int value);
 
 /* Times `iters` back-to-back launches of the network's dominant kernel (the 64->64 conv at 4h x 4w) with CUDA events
