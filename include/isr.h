@@ -95,6 +95,12 @@ int isr_shade(const float *gbuf, const float *params_host, float *rgb, int B, in
 int isr_shade_rgb8(const float *gbuf, const float *params_host, unsigned char *rgb8, int B, int C, int H, int W,
                    void *stream);
 
+/* Temporal post-smoothing of the displayed frame (mainGUI.py:834-849): out = factor * warp_upscale(prev_rgb, flow, r,
+ * special_mask = False) + (1 - factor) * cur_rgb in one pass (the GUI's second warp of the previous RGB frame + exponential
+ * blend; factor = slider / 100).  prev_rgb / cur_rgb / out: B x C x h*r x w*r, flow: B x 2 x h x w (in-painted). */
+int isr_temporal_blend(const float *prev_rgb, const float *flow, const float *cur_rgb, float *out, int B, int C, int h,
+                       int w, int r, float factor, void *stream);
+
 /* GUI / video composition (mainGUI.py:603-608,615-636; mainComparisonVideo3.py:540-556): bilinear x4 of the c_low-channel
  * low-res render (RGB, mask, normal, depth, flow, AO, shadow: c_low >= 12 for the unshaded form, >= 4 otherwise);
  * unshaded != 0: channels 0:3 = shading(pred), 3:8 = pred[0:5], 10 = pred[5] (pred = post-processed state, c_pred 5|6);
@@ -256,6 +262,16 @@ int isr_pipe_submit(isr_pipe *pipe, const float *low_host, const float *flow_hos
  * prediction: 3 instead of 24 bytes per output pixel cross PCIe; the prediction itself is not written at all. */
 int isr_pipe_enable_display(isr_pipe *pipe, const float *params_host, unsigned char *rgb8_staging_dev, size_t bytes);
 int isr_pipe_submit_display(isr_pipe *pipe, const float *low_host, const float *flow_host, unsigned char *rgb8_host);
+/* Switches the recurrent-state tensor (B x c_prev x 4h x 4w, device) used by the frames submitted from now on: one pipeline
+ * (one workspace, one set of staging slots) can serve several chunks of independent sequences in turn -- BASELINE.json
+ * configs[4] runs 64 sequences per GPU as 16 chunks of 4.  Stream-ordered: frames already submitted keep their state. */
+int isr_pipe_set_state(isr_pipe *pipe, float *state_dev);
+/* 16-bit form of the full prediction: after isr_pipe_enable_f16 (f16_staging_dev: depth x B x Cout x 4h x 4w x 2 bytes on
+ * the device) isr_pipe_submit_f16 enqueues a frame whose host-side result is the prediction rounded to IEEE fp16 (round to
+ * nearest even; |prediction| < 16 for this network, so the rounding error is <= 2^-8 * 2^-3 relative to the 1e-2 parity
+ * bar): 12 instead of 24 bytes per output pixel cross the host link.  The recurrent state stays fp32 on the device. */
+int isr_pipe_enable_f16(isr_pipe *pipe, void *f16_staging_dev, size_t bytes);
+int isr_pipe_submit_f16(isr_pipe *pipe, const float *low_host, const float *flow_host, void *recon_f16_host);
 int isr_pipe_wait(isr_pipe *pipe);
 void isr_pipe_destroy(isr_pipe *pipe);
 
@@ -269,8 +285,10 @@ int isr_debug_conv3x3(const float *x, const float *weight, const float *bias, co
                       size_t workspace_bytes, void *stream);
 int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
 
-/* Process-wide tunables for tests, experiments and bench ablations (defaults in brackets); returns the previous value,
- * or a negative ISR_ERR_* for an unknown key / value:
+/* Tunables for tests, experiments and bench ablations (defaults in brackets).  isr_set_tunable changes the process-wide
+ * DEFAULTS, of which every isr_net takes a snapshot at isr_net_create; isr_net_set_tunable changes ONE handle (its cached
+ * plans are dropped), so handles in different threads can run different settings.  Both return the previous value, or a
+ * negative ISR_ERR_* for an unknown key / value ("raycast_two_pass" is process-wide only):
  *   "halo_pitch" (10 | [16]), "base_offset_mode" ([0] | 1), "max_ctas" ([0] = #SMs)   operand addressing, DESIGN.md 4.1
  *   "cta_pair" (0 | [1])             CTA-pair (cta_group::2) form of the 64->64 conv
  *   "stack_w" (0 | [1])              hi/lo weight planes as one N=128 B operand
@@ -283,6 +301,7 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "raycast_two_pass" (0 | [1] = from 8 AO rays on | 2)   ambient occlusion of the ray-caster as a second pass
  *   "dbg"                            bit mask of bench experiments (tools/), 0 in production */
 int isr_set_tunable(const char *key, int value);
+int isr_net_set_tunable(isr_net *net, const char *key, int value);
 
 /* Times `iters` back-to-back launches of the network's dominant kernel (the 64->64 conv at 4h x 4w) with CUDA events
  * on `stream`; returns the average milliseconds per launch in *ms (bench.py's roofline leg). */

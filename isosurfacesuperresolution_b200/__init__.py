@@ -17,7 +17,7 @@ from .enhancenet import EnhanceNet          # noqa: E402
 from .initial_image import initialImage     # noqa: E402
 from .shading import ScreenSpaceShading     # noqa: E402
 from .videotools import VideoTools          # noqa: E402
-from .inference import LoadedModel, SequenceRunner, compose_frame   # noqa: E402
+from .inference import LoadedModel, SequenceRunner, compose_frame, temporal_smoothing   # noqa: E402
 from .dataset import SequenceDataset, evaluate, masked_psnr           # noqa: E402
 from .renderer import DenseGridRenderer, camera_matrices              # noqa: E402
 
@@ -32,4 +32,4 @@ def createNetwork(name, upscale_factor, input_channels, channel_mask, output_cha
 
 
 __all__ = ["createNetwork", "EnhanceNet", "VideoTools", "initialImage", "ScreenSpaceShading", "LoadedModel",
-           "SequenceRunner", "compose_frame", "SequenceDataset", "evaluate", "masked_psnr"]
+           "SequenceRunner", "compose_frame", "temporal_smoothing", "SequenceDataset", "evaluate", "masked_psnr"]

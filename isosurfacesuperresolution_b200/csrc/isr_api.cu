@@ -9,6 +9,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <random>
 #include <string>
 #include <vector>
@@ -23,20 +24,27 @@ namespace isr {
 
 static thread_local std::string g_err;
 static std::atomic<uint64_t> g_launches{0};
-static int g_halo_pitch = 10;
-static int g_base_offset_mode = 0;
-static int g_max_ctas = 0;
-static int g_dbg = 0;             // ConvParams::dbg of isr_net_time_conv launches (bench experiments)
-static int g_cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta_group::2, isr_conv_pair.cuh)
-static int g_final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (measured slower: 1.24 vs 0.92 ms), 1 = tap-stacked kernel (isr_conv_final.cuh, Cout <= 8),
-                                  // 0 = generic single-CTA N=16 kernel
-static int g_stack_w = 1;   // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
-static int g_fuse_up = 1;   // bilinear nets: the 4x upsample + first 4x conv run as one phase-decomposed kernel (isr_up2.cu)
-static int g_raycast_two_pass = 1;   // AO of the ray-caster as a second pass with one thread per (pixel, ray): 0 never, 1 auto, 2 always
-static int g_final_w_parts = 0;   // output conv weight planes: 0 = the scheme's choice, 1 = single, 2 = hi + lo
-static int g_final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
-static int g_pdl = 1;   // CTA-pair convs are launched with programmatic stream serialization (prologue overlaps the previous tail)
-static int g_trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
+// Tunables of the network plans.  `g_tun` holds the process-wide DEFAULTS (isr_set_tunable); every isr_net takes a snapshot
+// at isr_net_create and is from then on independent of them (isr_net_set_tunable changes one handle), so two handles in two
+// threads can run different settings and a test that dies between two isr_set_tunable calls cannot alter existing handles.
+struct Tunables {
+  int halo_pitch = 10;
+  int base_offset_mode = 0;
+  int max_ctas = 0;
+  int dbg = 0;             // ConvParams::dbg of isr_net_time_conv launches (bench experiments)
+  int cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta_group::2, isr_conv_pair.cuh)
+  int final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (measured slower: 1.24 vs 0.92 ms), 1 = tap-stacked kernel
+                           // (isr_conv_final.cuh, Cout <= 8), 0 = generic single-CTA N=16 kernel
+  int stack_w = 1;         // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
+  int fuse_up = 1;         // bilinear nets: upsample + conv run as one phase-decomposed kernel (isr_up2.cu)
+  int final_w_parts = 0;   // output conv weight planes: 0 = the scheme's choice, 1 = single, 2 = hi + lo
+  int final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
+  int pdl = 1;             // CTA-pair convs are launched with programmatic stream serialization
+  int trunk_full_blocks = 4;   // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3)
+};
+static Tunables g_tun;
+static std::mutex g_tun_mutex;
+static int g_raycast_two_pass = 1;   // (process-wide, not a network tunable) AO of the ray-caster as a second pass: 0 never, 1 auto, 2 always
 
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
@@ -113,6 +121,8 @@ struct ConvLaunch {
   int cp = 0;  // > 0: tap-stacked output conv (conv3x3_final_kernel<cp>)
   int pair = 0;  // 1: CTA-pair kernel (conv3x3_pair_kernel)
   int ph = 1;    // 4: fused upsample + conv (four output phases per low-res tile)
+  int stack = 0; // split weights stacked as one N=128 operand
+  int pdl = 1;   // programmatic dependent launch
   size_t smem;
   int grid;
 };
@@ -120,50 +130,54 @@ struct ConvLaunch {
 constexpr size_t kSmemLimit = 232448;  // 227 KB per CTA
 constexpr size_t kStaticSmem = 512;    // s_bias + slack
 
+constexpr int kMaxDevices = 64;
+
 static int num_sms() {
-  static int n = 0;
+  static std::atomic<int> cache[kMaxDevices];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 148;
+  int n = cache[dev].load(std::memory_order_relaxed);
   if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-      n = 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
   }
   return n;
 }
 
+// cudaFuncSetAttribute applies to the device that is current when it is called: the opt-in to 227 KB of dynamic shared
+// memory is made once PER DEVICE (a process may drive several GPUs through several handles), under a mutex
+template <typename K>
+static cudaError_t set_max_smem(K kernel) {
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kSmemLimit - kStaticSmem));
+}
 static int setup_kernel_attrs() {
-  static bool done = false;
-  if (done) return ISR_OK;
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<64, EPI_STORE16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<64, EPI_STORE16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_umma_kernel<16, EPI_FINAL, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<0, 16, EPI_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_pair_kernel<1, 16, EPI_FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  ISR_CUDA(cudaFuncSetAttribute(conv3x3_final_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(kSmemLimit - kStaticSmem)));
-  done = true;
+  static std::mutex mu;
+  static bool done[kMaxDevices] = {false};
+  int dev = 0;
+  ISR_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(ISR_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (done[dev]) return ISR_OK;
+  ISR_CUDA(set_max_smem(conv3x3_umma_kernel<64, EPI_STORE16, 0>));
+  ISR_CUDA(set_max_smem(conv3x3_umma_kernel<64, EPI_STORE16, 1>));
+  ISR_CUDA(set_max_smem(conv3x3_umma_kernel<16, EPI_FINAL, 0>));
+  ISR_CUDA(set_max_smem(conv3x3_umma_kernel<16, EPI_FINAL, 1>));
+  ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0>));
+  ISR_CUDA(set_max_smem(conv3x3_pair_kernel<1>));
+  ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>));
+  ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 16, EPI_FINAL>));
+  ISR_CUDA(set_max_smem(conv3x3_pair_kernel<1, 16, EPI_FINAL>));
+  ISR_CUDA(set_max_smem(conv3x3_final_kernel<4>));
+  ISR_CUDA(set_max_smem(conv3x3_final_kernel<6>));
+  ISR_CUDA(set_max_smem(conv3x3_final_kernel<8>));
+  done[dev] = true;
   return ISR_OK;
 }
 
 // fills geometry, smem plan and tensor maps of one conv launch; epilogue fields are set by the caller
-static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W, int n_act_parts, const void *wpacked,
-                     int w_rows_total, int w_row0, int w_row_stride, int n_w_parts, int is_bf16, int tensor_parts = 0) {
+static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act, int B, int H, int W, int n_act_parts,
+                     const void *wpacked, int w_rows_total, int w_row0, int w_row_stride, int n_w_parts, int is_bf16,
+                     int tensor_parts = 0) {
   if (tensor_parts < n_act_parts) tensor_parts = n_act_parts;   // planes stored per pixel (>= planes the MMAs read)
   memset(&L->p, 0, sizeof L->p);
   L->n = n;
@@ -177,8 +191,11 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   p.is_bf16 = is_bf16;
   p.w_row0 = w_row0;
   p.w_row_stride = w_row_stride;
-  L->pair = ((n == 64 && g_cta_pair) || (n == 16 && g_final_stacked == 2)) ? 1 : 0;
-  const bool stack = n_w_parts == 2 && g_stack_w;
+  L->pair = ((n == 64 && tun.cta_pair) || (n == 16 && tun.final_stacked == 2)) ? 1 : 0;
+  const bool stack = n_w_parts == 2 && tun.stack_w;
+  L->stack = stack ? 1 : 0;
+  L->pdl = tun.pdl;
+  L->cp = 0; L->ph = 1;
   // weight bytes per CTA: the pair kernel keeps half of the B operand per CTA (+ its half of W_hi when stacked)
   size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * 9 * n * 128, 1024);
   if (L->pair) w_bytes = align_up(static_cast<size_t>(stack ? 3 : n_w_parts) * 9 * (n / 2) * 128, 1024);
@@ -192,7 +209,7 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
   if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "conv smem plan: fewer than 2 halo stages fit");
   p.num_stages = stages;
   L->smem = 1024 + w_bytes + static_cast<size_t>(stages) * p.stage_bytes + 256;
-  int cap = g_max_ctas > 0 ? g_max_ctas : num_sms();
+  int cap = tun.max_ctas > 0 ? tun.max_ctas : num_sms();
   L->grid = p.num_tiles < cap ? p.num_tiles : cap;
   if (L->pair) {
     const int want = 2 * ((p.num_tiles + 1) / 2);
@@ -207,10 +224,10 @@ static int init_conv(ConvLaunch *L, int n, const void *act, int B, int H, int W,
 
 // fused bilinear-2x-upsample + conv (64 -> 64): act = LOW-res input [B][hl][wl][64 * tensor_parts], wpacked = composite
 // weights of the chosen format [phase 4][tap 9][64][64]; the launch writes the (2 hl) x (2 wl) output
-static int init_conv_up2(ConvLaunch *L, const void *act, int B, int hl, int wl, int tensor_parts, const void *wpacked,
-                         int is_bf16) {
+static int init_conv_up2(const Tunables &tun, ConvLaunch *L, const void *act, int B, int hl, int wl, int tensor_parts,
+                         const void *wpacked, int is_bf16) {
   memset(&L->p, 0, sizeof L->p);
-  L->n = 64; L->cp = 0; L->pair = 1; L->ph = 4;
+  L->n = 64; L->cp = 0; L->pair = 1; L->ph = 4; L->stack = 0; L->pdl = tun.pdl;
   ConvParams &p = L->p;
   p.B = B; p.H = hl; p.W = wl;
   p.tiles_x = (wl + kTileW - 1) / kTileW;
@@ -225,7 +242,7 @@ static int init_conv_up2(ConvLaunch *L, const void *act, int B, int hl, int wl, 
   if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "up2 conv smem plan: fewer than 2 halo stages fit");
   p.num_stages = stages;
   L->smem = 1024 + w_bytes + static_cast<size_t>(stages) * p.stage_bytes + 512;   // 8 accumulator barriers: 512 B block
-  int cap = (g_max_ctas > 0 ? g_max_ctas : num_sms()) & ~1;
+  int cap = (tun.max_ctas > 0 ? tun.max_ctas : num_sms()) & ~1;
   if (cap < 2) cap = 2;
   const int want = 2 * ((p.num_tiles + 1) / 2);
   L->grid = want < cap ? want : cap;
@@ -243,12 +260,13 @@ static size_t final_pbytes(int cp) {
 }
 
 // tap-stacked output conv: wpacked = [part 2][nrows][64] of the chosen format
-static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H, int W, int n_act_parts,
-                           const void *wpacked, int n_w_parts, int is_bf16) {
+static int init_conv_final(const Tunables &tun, ConvLaunch *L, int cp, const void *act, int B, int H, int W,
+                           int n_act_parts, const void *wpacked, int n_w_parts, int is_bf16) {
   memset(&L->p, 0, sizeof L->p);
   const int nrows = final_rows(cp);
   L->n = nrows;
   L->cp = cp;
+  L->pair = 0; L->ph = 1; L->stack = 0; L->pdl = tun.pdl;
   ConvParams &p = L->p;
   p.B = B; p.H = H; p.W = W;
   p.tiles_x = (W + kFTileW - 1) / kFTileW;
@@ -266,13 +284,13 @@ static int init_conv_final(ConvLaunch *L, int cp, const void *act, int B, int H,
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "final conv smem plan: fewer than 2 halo stages fit");
   p.issuers = 1;
-  if (g_final_issuers == 3 && stages >= kFinalIssuers * n_act_parts) {   // three issuing warps need every stage to belong to one of them
+  if (tun.final_issuers == 3 && stages >= kFinalIssuers * n_act_parts) {   // three issuing warps need every stage to belong to one of them
     stages -= stages % (kFinalIssuers * n_act_parts);
     p.issuers = kFinalIssuers;
   }
   p.num_stages = stages;
   L->smem = fixed + static_cast<size_t>(stages) * p.stage_bytes;
-  int cap = g_max_ctas > 0 ? g_max_ctas : num_sms();
+  int cap = tun.max_ctas > 0 ? tun.max_ctas : num_sms();
   L->grid = p.num_tiles < cap ? p.num_tiles : cap;
   int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kFPitch, kFHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
@@ -288,7 +306,7 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     ISR_CUDA(cudaGetLastError());
     return ISR_OK;
   }
-  const bool stack = L.p.n_w_parts == 2 && g_stack_w;
+  const bool stack = L.stack != 0;
   if (L.pair) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(L.grid);
@@ -299,7 +317,7 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = g_pdl ? 1 : 0;
+    cfg.numAttrs = L.pdl ? 1 : 0;
     if (L.ph == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, L.tmA, L.tmW, L.p));
     else if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
     else if (L.n == 16) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
@@ -360,8 +378,7 @@ struct Layer {
 };
 
 struct Plan {
-  int B = 0, h = 0, w = 0, precision = -1, pitch = 0, bo = 0, max_ctas = 0, fin_stacked = 0, stack_w = 0, cta_pair = 0,
-      full_blocks = 0, f_last_parts = 1;
+  int B = 0, h = 0, w = 0, precision = -1, f_last_parts = 1;
   void *ws = nullptr;
   size_t ws_need = 0;   // bytes of workspace this plan uses (checked on every call, also on a cache hit)
   Scheme trunk, tail;
@@ -372,7 +389,6 @@ struct Plan {
   uint16_t *f_last = nullptr, *u2 = nullptr, *c2 = nullptr, *u4 = nullptr, *c4 = nullptr;
   int idx_post1 = 0, idx_post4 = 0, idx_final = 0;
   // fused 4x upsample + conv (isr_up2.cu): the phase kernel, the two band convs and their buffers
-  int fuse_up = 0, fin_issuers = 0, fin_w_parts = 0;
   struct Fused {
     int on = 0, hl = 0, wl = 0, in_parts = 1;   // low-res size and stored planes of the input
     const uint16_t *src = nullptr;
@@ -385,6 +401,7 @@ struct Plan {
 }  // namespace isr
 
 struct isr_net {
+  isr::Tunables tun;   // snapshot of the process defaults at isr_net_create; isr_net_set_tunable changes it (and drops the plans)
   int cin, cout, n_mask, upsample, recon_residual;
   int G;  // 64-channel input groups of the first conv
   isr::Layer layers[25];
@@ -432,10 +449,10 @@ static void set_store(ConvLaunch *L, const float *bias, int relu, const uint16_t
   L->p.out_parts = out_parts;
 }
 
-static int conv_for_layer(ConvLaunch *L, const Layer &ly, int g, const uint16_t *act, int B, int H, int W,
-                          const Scheme &sc, int tensor_parts = 0) {
+static int conv_for_layer(const Tunables &tun, ConvLaunch *L, const Layer &ly, int g, const uint16_t *act, int B, int H,
+                          int W, const Scheme &sc, int tensor_parts = 0) {
   const uint16_t *wbase = ly.packed + (sc.bf16 ? 0 : ly.per_fmt());
-  return init_conv(L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16,
+  return init_conv(tun, L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16,
                    tensor_parts);
 }
 
@@ -448,11 +465,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
     return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, need);
   if (reinterpret_cast<uintptr_t>(ws) % 1024 != 0) return fail(ISR_ERR_ARG, "workspace must be 1024-byte aligned");
   pl->B = B; pl->h = h; pl->w = w; pl->precision = precision; pl->ws = ws; pl->ws_need = need;
-  pl->pitch = g_halo_pitch; pl->bo = g_base_offset_mode; pl->max_ctas = g_max_ctas;
-  pl->fin_stacked = g_final_stacked; pl->stack_w = g_stack_w; pl->cta_pair = g_cta_pair;
-  pl->full_blocks = g_trunk_full_blocks;
-  pl->fuse_up = g_fuse_up;
-  pl->fin_issuers = g_final_issuers; pl->fin_w_parts = g_final_w_parts;
+  const Tunables &tun = net->tun;
   uint8_t *base = static_cast<uint8_t *>(ws);
   auto at = [&](int i) { return reinterpret_cast<uint16_t *>(base + offs[i]); };
   const size_t t2 = align_up(static_cast<size_t>(B) * h * w * 4 * 128 * pl->tail.na, 1024);
@@ -470,14 +483,14 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   int rc;
   // preblock (enhancenet.py:93-95): one launch per 64-channel input group; the second adds the first's partial sums
   if (net->G == 1) {
-    if ((rc = conv_for_layer(&L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, nullptr, 0, f0, FS);
     pl->convs.push_back(L);
   } else {
-    if ((rc = conv_for_layer(&L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, nullptr, 0, nullptr, 0, partial, FS);
     pl->convs.push_back(L);
-    if ((rc = conv_for_layer(&L, net->layers[0], 1, pl->in_g[1], B, h, w, T)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[0], 1, pl->in_g[1], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, partial, FS, f0, FS);
     pl->convs.push_back(L);
   }
@@ -486,17 +499,17 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   // split weights (one N=128 MMA per k-step); rounding errors injected early are amplified by every later block, so the
   // expensive scheme is spent where it matters.
   const bool hybrid = precision == ISR_PREC_HYBRID;
-  const int K = hybrid ? pl->full_blocks : 10;
+  const int K = hybrid ? tun.trunk_full_blocks : 10;
   const Scheme cheap = {0, 1, 2, 1};
   uint16_t *fc = f0, *fn = f1;
   int pf = FS;   // planes stored in the current stream tensor
   for (int blk = 0; blk < 10; ++blk) {
     const Scheme &Sb = (hybrid && blk >= K) ? cheap : T;
     const int pn = hybrid ? ((blk + 1 < K) ? 2 : 1) : FS;
-    if ((rc = conv_for_layer(&L, net->layers[1 + 2 * blk], 0, fc, B, h, w, Sb, pf)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[1 + 2 * blk], 0, fc, B, h, w, Sb, pf)) != ISR_OK) return rc;
     set_store(&L, net->layers[1 + 2 * blk].bias, 1, nullptr, 0, t, Sb.na);
     pl->convs.push_back(L);
-    if ((rc = conv_for_layer(&L, net->layers[2 + 2 * blk], 0, t, B, h, w, Sb)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[2 + 2 * blk], 0, t, B, h, w, Sb)) != ISR_OK) return rc;
     set_store(&L, net->layers[2 + 2 * blk].bias, 0, fc, pf, fn, pn);
     pl->convs.push_back(L);
     uint16_t *sw = fc; fc = fn; fn = sw;
@@ -506,11 +519,11 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->f_last = fc;
   // postblock (enhancenet.py:115-125): up2 -> conv -> relu -> up2 -> conv -> relu -> conv -> relu -> conv
   pl->idx_post1 = static_cast<int>(pl->convs.size());
-  if ((rc = conv_for_layer(&L, net->layers[21], 0, pl->u2, B, 2 * h, 2 * w, Hs)) != ISR_OK) return rc;
+  if ((rc = conv_for_layer(tun, &L, net->layers[21], 0, pl->u2, B, 2 * h, 2 * w, Hs)) != ISR_OK) return rc;
   set_store(&L, net->layers[21].bias, 1, nullptr, 0, pl->c2, Hs.na);
   pl->convs.push_back(L);
   pl->idx_post4 = static_cast<int>(pl->convs.size());
-  if ((rc = conv_for_layer(&L, net->layers[22], 0, pl->u4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
+  if ((rc = conv_for_layer(tun, &L, net->layers[22], 0, pl->u4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
   set_store(&L, net->layers[22].bias, 1, nullptr, 0, pl->c4, Hs.na);
   pl->convs.push_back(L);
   // fused form of (upsample 2x -> conv): phase-decomposed kernel on the low-res tensor + the plain conv on four border
@@ -521,32 +534,32 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
                          uint16_t *dst) -> int {
     const uint16_t *wu = ly.packed_up + (Hs.bf16 ? 0 : static_cast<size_t>(36) * 4096);
     int r;
-    if ((r = init_conv_up2(&f->up, src, B, hl, wl, in_parts, wu, Hs.bf16)) != ISR_OK) return r;
+    if ((r = init_conv_up2(tun, &f->up, src, B, hl, wl, in_parts, wu, Hs.bf16)) != ISR_OK) return r;
     set_store(&f->up, ly.bias, 1, nullptr, 0, dst, Hs.na);
-    if ((r = conv_for_layer(&f->band_r, ly, 0, pl->rows_in, 2 * B, 3, 2 * wl, Hs)) != ISR_OK) return r;
+    if ((r = conv_for_layer(tun, &f->band_r, ly, 0, pl->rows_in, 2 * B, 3, 2 * wl, Hs)) != ISR_OK) return r;
     set_store(&f->band_r, ly.bias, 1, nullptr, 0, pl->rows_out, Hs.na);
-    if ((r = conv_for_layer(&f->band_c, ly, 0, pl->cols_in, 2 * B, 2 * hl, 3, Hs)) != ISR_OK) return r;
+    if ((r = conv_for_layer(tun, &f->band_c, ly, 0, pl->cols_in, 2 * B, 2 * hl, 3, Hs)) != ISR_OK) return r;
     set_store(&f->band_c, ly.bias, 1, nullptr, 0, pl->cols_out, Hs.na);
     f->src = src; f->dst = dst; f->hl = hl; f->wl = wl; f->in_parts = in_parts; f->on = 1;
     return ISR_OK;
   };
-  const bool can_fuse = g_fuse_up && g_cta_pair && net->upsample == ISR_UPSAMPLE_BILINEAR && Hs.na == 1 && Hs.nw == 1;
+  const bool can_fuse = tun.fuse_up && tun.cta_pair && net->upsample == ISR_UPSAMPLE_BILINEAR && Hs.na == 1 && Hs.nw == 1;
   if (can_fuse && net->layers[22].packed_up != nullptr && 2 * h >= 4 && 2 * w >= 4)
     if ((rc = build_fused(&pl->fuse4, net->layers[22], pl->c2, Hs.na, 2 * h, 2 * w, pl->c4)) != ISR_OK) return rc;
   if (can_fuse && net->layers[21].packed_up != nullptr && h >= 4 && w >= 4 && pl->f_last_parts == 1 && T.bf16 == Hs.bf16)
     if ((rc = build_fused(&pl->fuse2, net->layers[21], pl->f_last, 1, h, w, pl->c2)) != ISR_OK) return rc;
-  if ((rc = conv_for_layer(&L, net->layers[23], 0, pl->c4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
+  if ((rc = conv_for_layer(tun, &L, net->layers[23], 0, pl->c4, B, 4 * h, 4 * w, Hs)) != ISR_OK) return rc;
   set_store(&L, net->layers[23].bias, 1, nullptr, 0, pl->u4, Hs.na);
   pl->convs.push_back(L);
   pl->idx_final = static_cast<int>(pl->convs.size());
   Scheme Fs = Hs;
   if (pl->fin_nw > 0) Fs.nw = pl->fin_nw;
-  if (g_final_w_parts > 0) Fs.nw = g_final_w_parts;
-  if (net->layers[24].packed_fin != nullptr && g_final_stacked == 1) {
+  if (tun.final_w_parts > 0) Fs.nw = tun.final_w_parts;
+  if (net->layers[24].packed_fin != nullptr && tun.final_stacked == 1) {
     const int cp = final_cp(net->cout), nrows = final_rows(cp);
     const uint16_t *wb = net->layers[24].packed_fin + (Fs.bf16 ? 0 : static_cast<size_t>(2) * nrows * 64);
-    if ((rc = init_conv_final(&L, cp, pl->u4, B, 4 * h, 4 * w, Fs.na, wb, Fs.nw, Fs.bf16)) != ISR_OK) return rc;
-  } else if ((rc = conv_for_layer(&L, net->layers[24], 0, pl->u4, B, 4 * h, 4 * w, Fs)) != ISR_OK) {
+    if ((rc = init_conv_final(tun, &L, cp, pl->u4, B, 4 * h, 4 * w, Fs.na, wb, Fs.nw, Fs.bf16)) != ISR_OK) return rc;
+  } else if ((rc = conv_for_layer(tun, &L, net->layers[24], 0, pl->u4, B, 4 * h, 4 * w, Fs)) != ISR_OK) {
     return rc;
   }
   L.p.bias = net->layers[24].bias;
@@ -562,10 +575,7 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
 
 static int get_plan(isr_net *net, Plan **out, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
   for (Plan *pl : net->plans)
-    if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws &&
-        pl->pitch == g_halo_pitch && pl->bo == g_base_offset_mode && pl->max_ctas == g_max_ctas &&
-        pl->fin_stacked == g_final_stacked && pl->stack_w == g_stack_w && pl->cta_pair == g_cta_pair &&
-        pl->full_blocks == g_trunk_full_blocks && pl->fuse_up == g_fuse_up && pl->fin_issuers == g_final_issuers && pl->fin_w_parts == g_final_w_parts) {
+    if (pl->B == B && pl->h == h && pl->w == w && pl->precision == precision && pl->ws == ws) {
       if (ws_bytes < pl->ws_need)
         return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, pl->ws_need);
       *out = pl;
@@ -647,51 +657,54 @@ int isr_version(void) { return 100; }
 const char *isr_last_error(void) { return g_err.c_str(); }
 uint64_t isr_launch_count(void) { return g_launches.load(); }
 
+// key -> slot of a Tunables block, with the range check; nullptr (and the error set) when the key / value is refused
+static int *tunable_slot(Tunables *t, const char *key, int value) {
+  auto bad = [](const char *msg) -> int * { fail(ISR_ERR_ARG, "%s", msg); return nullptr; };
+  if (key == nullptr) return bad("unknown tunable");
+  if (strcmp(key, "halo_pitch") == 0)
+    return value == 10 ? &t->halo_pitch : bad("halo_pitch is fixed at 10 (validated on B200, profiles/r01_probe_umma_addressing.json)");
+  if (strcmp(key, "base_offset_mode") == 0) return value == 0 ? &t->base_offset_mode : bad("base_offset_mode is fixed at 0 (validated on B200)");
+  if (strcmp(key, "max_ctas") == 0) return value >= 0 ? &t->max_ctas : bad("max_ctas must be >= 0");
+  if (strcmp(key, "dbg") == 0) return &t->dbg;
+  if (strcmp(key, "cta_pair") == 0) return (value == 0 || value == 1) ? &t->cta_pair : bad("cta_pair must be 0 or 1");
+  if (strcmp(key, "final_stacked") == 0)
+    return (value >= 0 && value <= 2) ? &t->final_stacked : bad("final_stacked must be 0 (generic), 1 (tap-stacked) or 2 (CTA pair)");
+  if (strcmp(key, "trunk_full_blocks") == 0)
+    return (value >= 0 && value <= 10) ? &t->trunk_full_blocks : bad("trunk_full_blocks must be in [0, 10]");
+  if (strcmp(key, "fuse_up") == 0) return (value == 0 || value == 1) ? &t->fuse_up : bad("fuse_up must be 0 or 1");
+  if (strcmp(key, "final_issuers") == 0) return (value == 1 || value == 3) ? &t->final_issuers : bad("final_issuers must be 1 or 3");
+  if (strcmp(key, "final_w_parts") == 0)
+    return (value >= 0 && value <= 2) ? &t->final_w_parts : bad("final_w_parts must be 0 (scheme), 1 or 2");
+  if (strcmp(key, "pdl") == 0) return (value == 0 || value == 1) ? &t->pdl : bad("pdl must be 0 or 1");
+  if (strcmp(key, "stack_w") == 0) return (value == 0 || value == 1) ? &t->stack_w : bad("stack_w must be 0 or 1");
+  return bad("unknown tunable");
+}
+
 int isr_set_tunable(const char *key, int value) {
-  int *slot = nullptr;
-  if (key != nullptr && strcmp(key, "halo_pitch") == 0) {
-    if (value != 10) return fail(ISR_ERR_ARG, "halo_pitch is fixed at 10 (validated on B200, profiles/r01_probe_umma_addressing.json)");
-    slot = &g_halo_pitch;
-  } else if (key != nullptr && strcmp(key, "base_offset_mode") == 0) {
-    if (value != 0) return fail(ISR_ERR_ARG, "base_offset_mode is fixed at 0 (validated on B200)");
-    slot = &g_base_offset_mode;
-  } else if (key != nullptr && strcmp(key, "max_ctas") == 0) {
-    if (value < 0) return fail(ISR_ERR_ARG, "max_ctas must be >= 0");
-    slot = &g_max_ctas;
-  } else if (key != nullptr && strcmp(key, "dbg") == 0) {
-    slot = &g_dbg;
-  } else if (key != nullptr && strcmp(key, "cta_pair") == 0) {
-    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "cta_pair must be 0 or 1");
-    slot = &g_cta_pair;
-  } else if (key != nullptr && strcmp(key, "final_stacked") == 0) {
-    if (value < 0 || value > 2) return fail(ISR_ERR_ARG, "final_stacked must be 0 (generic), 1 (tap-stacked) or 2 (CTA pair)");
-    slot = &g_final_stacked;
-  } else if (key != nullptr && strcmp(key, "trunk_full_blocks") == 0) {
-    if (value < 0 || value > 10) return fail(ISR_ERR_ARG, "trunk_full_blocks must be in [0, 10]");
-    slot = &g_trunk_full_blocks;
-  } else if (key != nullptr && strcmp(key, "fuse_up") == 0) {
-    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "fuse_up must be 0 or 1");
-    slot = &g_fuse_up;
-  } else if (key != nullptr && strcmp(key, "final_issuers") == 0) {
-    if (value != 1 && value != 3) return fail(ISR_ERR_ARG, "final_issuers must be 1 or 3");
-    slot = &g_final_issuers;
-  } else if (key != nullptr && strcmp(key, "raycast_two_pass") == 0) {
+  std::lock_guard<std::mutex> lock(g_tun_mutex);
+  if (key != nullptr && strcmp(key, "raycast_two_pass") == 0) {   // the one process-wide switch that is not a network tunable
     if (value < 0 || value > 2) return fail(ISR_ERR_ARG, "raycast_two_pass must be 0 (never), 1 (auto) or 2 (always)");
-    slot = &g_raycast_two_pass;
-  } else if (key != nullptr && strcmp(key, "final_w_parts") == 0) {
-    if (value < 0 || value > 2) return fail(ISR_ERR_ARG, "final_w_parts must be 0 (scheme), 1 or 2");
-    slot = &g_final_w_parts;
-  } else if (key != nullptr && strcmp(key, "pdl") == 0) {
-    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "pdl must be 0 or 1");
-    slot = &g_pdl;
-  } else if (key != nullptr && strcmp(key, "stack_w") == 0) {
-    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "stack_w must be 0 or 1");
-    slot = &g_stack_w;
-  } else {
-    return fail(ISR_ERR_ARG, "unknown tunable");
+    const int old = g_raycast_two_pass;
+    g_raycast_two_pass = value;
+    return old;
   }
-  int old = *slot;
+  int *slot = tunable_slot(&g_tun, key, value);
+  if (slot == nullptr) return ISR_ERR_ARG;
+  const int old = *slot;
   *slot = value;
+  return old;
+}
+
+int isr_net_set_tunable(isr_net *net, const char *key, int value) {
+  if (net == nullptr) return fail(ISR_ERR_ARG, "net_set_tunable: null handle");
+  int *slot = tunable_slot(&net->tun, key, value);
+  if (slot == nullptr) return ISR_ERR_ARG;
+  const int old = *slot;
+  if (old != value) {
+    *slot = value;
+    for (Plan *pl : net->plans) delete pl;   // cached plans were built under the old settings
+    net->plans.clear();
+  }
   return old;
 }
 
@@ -711,6 +724,19 @@ int isr_warp_upscale(const float *prev, const float *flow, float *out, int B, in
   int rc = check_device();
   if (rc != ISR_OK) return rc;
   ISR_CUDA(launch_warp_upscale(prev, flow, out, B, C, h, w, r, special_mask, align_corners, S(stream)));
+  return ISR_OK;
+}
+
+int isr_temporal_blend(const float *prev_rgb, const float *flow, const float *cur_rgb, float *out, int B, int C, int h,
+                       int w, int r, float factor, void *stream) {
+  if (prev_rgb == nullptr || flow == nullptr || cur_rgb == nullptr || out == nullptr || B <= 0 || C <= 0 || h <= 0 ||
+      w <= 0 || r <= 0)
+    return fail(ISR_ERR_ARG, "temporal_blend: bad arguments");
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  // the reference multiplies fp32 tensors by the Python floats `factor` and `1 - factor` (taken in double, mainGUI.py:846-847)
+  const float fa = factor, fb = static_cast<float>(1.0 - static_cast<double>(factor));
+  ISR_CUDA(launch_temporal_blend(prev_rgb, flow, cur_rgb, out, B, C, h, w, r, fa, fb, S(stream)));
   return ISR_OK;
 }
 
@@ -976,6 +1002,10 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
   int rc = check_device();
   if (rc != ISR_OK) return rc;
   isr_net *net = new isr_net();
+  {
+    std::lock_guard<std::mutex> lock(g_tun_mutex);
+    net->tun = g_tun;
+  }
   net->cin = input_channels;
   net->cout = output_channels;
   net->n_mask = n_mask;
@@ -1131,6 +1161,8 @@ struct isr_pipe {
   float shade_params[22] = {0};
   unsigned char *rgb8 = nullptr;
   size_t n_rgb8 = 0;
+  // 16-bit form of the prediction
+  uint16_t *f16 = nullptr;
 };
 
 extern "C" {
@@ -1182,7 +1214,7 @@ int isr_pipe_create(isr_pipe **out, isr_net *net, int c_low, int c_prev, int spe
 }
 
 static int pipe_submit(isr_pipe *p, const float *low_host, const float *flow_host, float *recon_host,
-                       unsigned char *rgb8_host) {
+                       unsigned char *rgb8_host, void *f16_host = nullptr) {
   const int k = static_cast<int>(p->submitted % p->depth);
   // the slot is reused: frame (j - depth) must have left it (its D2H finished => its kernels finished too)
   if (p->submitted >= static_cast<uint64_t>(p->depth)) ISR_CUDA(cudaEventSynchronize(p->ev_out[k]));
@@ -1209,10 +1241,17 @@ static int pipe_submit(isr_pipe *p, const float *low_host, const float *flow_hos
     rc = isr_shade_rgb8(p->state, p->shade_params, rgb8_d, p->B, p->c_prev, 4 * p->h, 4 * p->w, p->s_comp);
     if (rc != ISR_OK) return rc;
   }
+  uint16_t *f16_d = nullptr;
+  if (f16_host != nullptr) {
+    f16_d = p->f16 + static_cast<size_t>(k) * p->n_out;
+    ISR_CUDA(launch_f32_to_f16(recon_d, f16_d, p->n_out, p->s_comp));
+  }
   ISR_CUDA(cudaEventRecord(p->ev_comp[k], p->s_comp));
   ISR_CUDA(cudaStreamWaitEvent(p->s_out, p->ev_comp[k], 0));
   if (rgb8_host != nullptr)
     ISR_CUDA(cudaMemcpyAsync(rgb8_host, rgb8_d, p->n_rgb8, cudaMemcpyDeviceToHost, p->s_out));
+  else if (f16_host != nullptr)
+    ISR_CUDA(cudaMemcpyAsync(f16_host, f16_d, p->n_out * sizeof(uint16_t), cudaMemcpyDeviceToHost, p->s_out));
   else
     ISR_CUDA(cudaMemcpyAsync(recon_host, recon_d, p->n_out * sizeof(float), cudaMemcpyDeviceToHost, p->s_out));
   ISR_CUDA(cudaEventRecord(p->ev_out[k], p->s_out));
@@ -1242,6 +1281,28 @@ int isr_pipe_submit_display(isr_pipe *p, const float *low_host, const float *flo
   if (p == nullptr || low_host == nullptr || rgb8_host == nullptr) return fail(ISR_ERR_ARG, "pipe_submit_display: null argument");
   if (!p->display) return fail(ISR_ERR_ARG, "pipe_submit_display: call isr_pipe_enable_display first");
   return pipe_submit(p, low_host, flow_host, nullptr, rgb8_host);
+}
+
+int isr_pipe_set_state(isr_pipe *p, float *state_dev) {
+  if (p == nullptr || state_dev == nullptr) return fail(ISR_ERR_ARG, "pipe_set_state: null argument");
+  p->state = state_dev;   // read at submit time; launches already enqueued captured the old pointer
+  return ISR_OK;
+}
+
+int isr_pipe_enable_f16(isr_pipe *p, void *f16_staging_dev, size_t bytes) {
+  if (p == nullptr || f16_staging_dev == nullptr) return fail(ISR_ERR_ARG, "pipe_enable_f16: null argument");
+  const size_t need = p->n_out * sizeof(uint16_t) * p->depth;
+  if (bytes < need) return fail(ISR_ERR_WORKSPACE, "pipe_enable_f16: staging too small (%zu < %zu bytes)", bytes, need);
+  if (reinterpret_cast<uintptr_t>(f16_staging_dev) % 16 != 0 || (p->n_out * sizeof(uint16_t)) % 16 != 0)
+    return fail(ISR_ERR_ARG, "pipe_enable_f16: staging must be 16-byte aligned (and B*Cout*16*h*w a multiple of 8)");
+  p->f16 = static_cast<uint16_t *>(f16_staging_dev);
+  return ISR_OK;
+}
+
+int isr_pipe_submit_f16(isr_pipe *p, const float *low_host, const float *flow_host, void *recon_f16_host) {
+  if (p == nullptr || low_host == nullptr || recon_f16_host == nullptr) return fail(ISR_ERR_ARG, "pipe_submit_f16: null argument");
+  if (p->f16 == nullptr) return fail(ISR_ERR_ARG, "pipe_submit_f16: call isr_pipe_enable_f16 first");
+  return pipe_submit(p, low_host, flow_host, nullptr, nullptr, recon_f16_host);
 }
 
 int isr_pipe_wait(isr_pipe *p) {
@@ -1281,31 +1342,41 @@ int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scal
     L.p.skip_src = reinterpret_cast<const float *>(pl->in_g[0]);
     L.p.skip_bstride = static_cast<long long>(net->n_mask > 0 ? net->n_mask : 1) * h * w;
   }
-  L.p.dbg = g_dbg;
+  L.p.dbg = net->tun.dbg;
   unsigned long long *cyc = nullptr;
-  if (g_dbg & 32) {   // bench experiment: cycles of the MMA issue loop (clock64 in the issuing warp)
-    ISR_CUDA(cudaMalloc(&cyc, 256 * sizeof(unsigned long long)));
-    ISR_CUDA(cudaMemset(cyc, 0, 256 * sizeof(unsigned long long)));
-    L.p.dbg_cycles = cyc;
-  }
-  cudaEvent_t e0, e1;
-  ISR_CUDA(cudaEventCreate(&e0));
-  ISR_CUDA(cudaEventCreate(&e1));
-  if ((rc = run_conv(L, S(stream))) != ISR_OK) return rc;  // warm-up
-  ISR_CUDA(cudaEventRecord(e0, S(stream)));
-  for (int i = 0; i < iters; ++i)
-    if ((rc = run_conv(L, S(stream))) != ISR_OK) return rc;
-  ISR_CUDA(cudaEventRecord(e1, S(stream)));
-  ISR_CUDA(cudaEventSynchronize(e1));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
   float t = 0.f;
-  ISR_CUDA(cudaEventElapsedTime(&t, e0, e1));
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
+  auto body = [&]() -> int {
+    if (net->tun.dbg & 32) {   // bench experiment: cycles of the MMA issue loop (clock64 in the issuing warp)
+      ISR_CUDA(cudaMalloc(&cyc, 256 * sizeof(unsigned long long)));
+      ISR_CUDA(cudaMemset(cyc, 0, 256 * sizeof(unsigned long long)));
+      L.p.dbg_cycles = cyc;
+    }
+    ISR_CUDA(cudaEventCreate(&e0));
+    ISR_CUDA(cudaEventCreate(&e1));
+    int r;
+    if ((r = run_conv(L, S(stream))) != ISR_OK) return r;  // warm-up
+    ISR_CUDA(cudaEventRecord(e0, S(stream)));
+    for (int i = 0; i < iters; ++i)
+      if ((r = run_conv(L, S(stream))) != ISR_OK) return r;
+    ISR_CUDA(cudaEventRecord(e1, S(stream)));
+    ISR_CUDA(cudaEventSynchronize(e1));
+    ISR_CUDA(cudaEventElapsedTime(&t, e0, e1));
+    return ISR_OK;
+  };
+  rc = body();
+  if (e0 != nullptr) cudaEventDestroy(e0);   // also on the error paths
+  if (e1 != nullptr) cudaEventDestroy(e1);
+  if (rc != ISR_OK) {
+    if (cyc != nullptr) cudaFree(cyc);
+    return rc;
+  }
   *ms = t / iters;
   if (cyc != nullptr) {
     unsigned long long hc[256];
-    ISR_CUDA(cudaMemcpy(hc, cyc, sizeof hc, cudaMemcpyDeviceToHost));
+    const cudaError_t ce = cudaMemcpy(hc, cyc, sizeof hc, cudaMemcpyDeviceToHost);
     cudaFree(cyc);
+    if (ce != cudaSuccess) return fail(ISR_ERR_CUDA, "time_conv: %s", cudaGetErrorString(ce));
     unsigned long long mx = 0, sum = 0; int n = 0;
     for (int i = 0; i < 128; ++i) if (hc[i]) { mx = hc[i] > mx ? hc[i] : mx; sum += hc[i]; ++n; }
     const double mmas = static_cast<double>((L.p.num_tiles + 1) / 2) / (L.grid / 2) * 36.0 * (L.p.n_act_parts == 2 ? 2.0 : 1.0);
@@ -1353,7 +1424,12 @@ int isr_debug_conv3x3(const float *x, const float *weight, const float *bias, co
   if (bias != nullptr) ISR_CUDA(cudaMemcpyAsync(bias_d, bias, cout * sizeof(float), cudaMemcpyDeviceToDevice, s));
   const size_t per_fmt = static_cast<size_t>(2) * 9 * npad * 64;
   ConvLaunch L;
-  rc = init_conv(&L, npad, in16, B, H, W, n_act_parts, wp + (is_bf16 ? 0 : per_fmt), 2 * 9 * npad, 0, npad, n_w_parts,
+  Tunables tun;
+  {
+    std::lock_guard<std::mutex> lock(g_tun_mutex);
+    tun = g_tun;
+  }
+  rc = init_conv(tun, &L, npad, in16, B, H, W, n_act_parts, wp + (is_bf16 ? 0 : per_fmt), 2 * 9 * npad, 0, npad, n_w_parts,
                  is_bf16);
   if (rc != ISR_OK) return rc;
   if (cout == 64) {

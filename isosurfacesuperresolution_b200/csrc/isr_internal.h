@@ -10,6 +10,9 @@ void count_launch();
 cudaError_t launch_flatten_high(const float *in, float *out, int B, int C, int H, int W, int r, cudaStream_t s);
 cudaError_t launch_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
                                 int special_mask, int align_corners, cudaStream_t s);
+cudaError_t launch_temporal_blend(const float *prev, const float *flow, const float *cur, float *out, int B, int C, int h,
+                                  int w, int r, float fa, float fb, cudaStream_t s);
+cudaError_t launch_f32_to_f16(const float *in, void *out, size_t n, cudaStream_t s);
 cudaError_t launch_initial_image(const float *in, float *out, int B, int Cin, int h, int w, int channels, int mode,
                                  int ao_inverted, int r, cudaStream_t s);
 cudaError_t launch_postprocess(const float *in, float *out, int B, int C, int H, int W, int unshaded, cudaStream_t s);

@@ -166,6 +166,42 @@ __global__ void warp_upscale_kernel(const float *__restrict__ prev, const float 
   }
 }
 
+// Temporal post-smoothing of the displayed frame (mainGUI.py:834-849): out = factor * warp_upscale(prev_rgb, flow) +
+// (1 - factor) * cur, the warp with special_mask = False.  fa = fp32(factor), fb = fp32(1 - factor) come from the host
+// (the reference multiplies an fp32 tensor by a Python float: separate fp32 multiplies, then one add).
+__global__ void temporal_blend_kernel(const float *__restrict__ prev, const float *__restrict__ flow,
+                                      const float *__restrict__ cur, float *__restrict__ out, int B, int C, int h, int w,
+                                      int r, float fa, float fb) {
+  const int H = h * r, W = w * r;
+  const size_t plane = static_cast<size_t>(H) * W;
+  const int y = blockIdx.x % H, b = blockIdx.x / H;
+  for (int x = threadIdx.x; x < W; x += blockDim.x) {
+    const WarpTaps t = warp_taps(flow + static_cast<size_t>(b) * 2 * h * w, h, w, r, y, x, 0);
+    for (int c = 0; c < C; ++c) {
+      const size_t o = (static_cast<size_t>(b) * C + c) * plane + static_cast<size_t>(y) * W + x;
+      const float wv = warp_gather(prev + (static_cast<size_t>(b) * C + c) * plane, W, t, false);
+      out[o] = fa * wv + fb * __ldg(cur + o);
+    }
+  }
+}
+
+// fp32 -> fp16 (round to nearest even), 8 elements per thread: the 16-bit form of the prediction for the host link
+__global__ void f32_to_f16_kernel(const float *__restrict__ in, __half *__restrict__ out, size_t n8, size_t n) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n8;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const float4 a = __ldcs(reinterpret_cast<const float4 *>(in) + 2 * i);
+    const float4 b = __ldcs(reinterpret_cast<const float4 *>(in) + 2 * i + 1);
+    __half2 h0 = __floats2half2_rn(a.x, a.y), h1 = __floats2half2_rn(a.z, a.w);
+    __half2 h2 = __floats2half2_rn(b.x, b.y), h3 = __floats2half2_rn(b.z, b.w);
+    uint4 v;
+    v.x = *reinterpret_cast<uint32_t *>(&h0); v.y = *reinterpret_cast<uint32_t *>(&h1);
+    v.z = *reinterpret_cast<uint32_t *>(&h2); v.w = *reinterpret_cast<uint32_t *>(&h3);
+    __stcs(reinterpret_cast<uint4 *>(out) + i, v);
+  }
+  if (blockIdx.x == 0)
+    for (size_t i = 8 * n8 + threadIdx.x; i < n; i += blockDim.x) out[i] = __float2half_rn(in[i]);
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // Network-input packing for the recurrent form: cat(low, flatten_high(warp_upscale(prev, flow))) written directly as
 // NHWC 16-bit hi|lo planes in 64-channel groups (videotools.py:8-25,49-87 + mainVideoUnshaded.py:441-445 fused).
@@ -713,6 +749,21 @@ cudaError_t launch_flatten_high(const float *in, float *out, int B, int C, int H
 cudaError_t launch_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
                                 int special_mask, int align_corners, cudaStream_t s) {
   warp_upscale_kernel<<<B * h * r, 256, 0, s>>>(prev, flow, out, B, C, h, w, r, special_mask, align_corners);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_temporal_blend(const float *prev, const float *flow, const float *cur, float *out, int B, int C, int h,
+                                  int w, int r, float fa, float fb, cudaStream_t s) {
+  temporal_blend_kernel<<<B * h * r, 256, 0, s>>>(prev, flow, cur, out, B, C, h, w, r, fa, fb);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_f32_to_f16(const float *in, void *out, size_t n, cudaStream_t s) {
+  const size_t n8 = n / 8;
+  size_t blocks = (n8 + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks == 0) blocks = 1;
+  f32_to_f16_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(in, static_cast<__half *>(out), n8, n);
   count_launch();
   return cudaGetLastError();
 }

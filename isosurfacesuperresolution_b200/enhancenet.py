@@ -25,8 +25,19 @@ STATE_DICT_KEYS = (
 
 
 class EnhanceNet(nn.Module):
-    # tensor-core operand scheme of the CUDA path (include/isr.h); "hybrid" meets the 1e-2 / 50 dB parity bar
+    # tensor-core operand scheme of the CUDA path (include/isr.h); "hybrid" meets the 1e-2 / 50 dB parity bar per frame
+    # (given the same inputs); how every scheme behaves over a free-running 10-frame recurrence is measured in
+    # profiles/r02_recurrence_drift.json
     precision = "hybrid"
+    # class-level defaults: an instance un-pickled from a REFERENCE checkpoint (models.enhancenet.EnhanceNet resolved to
+    # this class by compat/, or by LoadedModel's unpickler) never ran this __init__
+    _handle = None
+    _handle_key = None
+    _generation = 0
+    # checkpoints prior to unshaded networks lack these two attributes; same fallback as enhancenet.py:57-61
+    channel_mask = [0, 1, 2]
+    output_channels = 3
+    use_bn = False
 
     def __init__(self, upscale_factor, input_channels, channel_mask, output_channels, opt):
         super().__init__()
@@ -38,8 +49,7 @@ class EnhanceNet(nn.Module):
         self.channel_mask = channel_mask
         self.input_channels = input_channels
         self.output_channels = output_channels
-        if self.use_bn:
-            raise NotImplementedError("useBN=True is not supported by the B200 path: fold BatchNorm into the convs first")
+        self._up(2)                                          # refuse unsupported upsample modes at construction
         self._build(input_channels, output_channels)
         self._init_weights()
         self._handle = None
@@ -47,14 +57,22 @@ class EnhanceNet(nn.Module):
 
     # ---- module tree (enhancenet.py:92-125) -------------------------------------------------------------------
     def _up(self, factor):
-        if self.upsample in ("nearest", "bilinear", "bicubic"):
+        # enhancenet.py:40-48 also accepts 'bicubic' (and has a dead 'pixelShuffle' branch); the B200 kernels implement the
+        # two modes the reference's scripts use, and refuse the rest here rather than at the first forward
+        if self.upsample in ("nearest", "bilinear"):
             return nn.Upsample(scale_factor=factor, mode=self.upsample)
-        raise ValueError("unsupported upsample mode " + str(self.upsample))
+        raise ValueError("the B200 EnhanceNet supports upsample = 'nearest' | 'bilinear', got " + repr(self.upsample))
 
     def _build(self, cin, cout):
         self.preblock = nn.Sequential(nn.Conv2d(cin, 64, 3, padding=1), nn.ReLU())
-        self.blocks = nn.ModuleList(
-            [nn.Sequential(nn.Conv2d(64, 64, 3, padding=1), nn.ReLU(), nn.Conv2d(64, 64, 3, padding=1)) for _ in range(10)])
+        if self.use_bn:                                      # enhancenet.py:99-105
+            self.blocks = nn.ModuleList(
+                [nn.Sequential(nn.Conv2d(64, 64, 3, padding=1), nn.BatchNorm2d(64), nn.ReLU(),
+                               nn.Conv2d(64, 64, 3, padding=1), nn.BatchNorm2d(64)) for _ in range(10)])
+        else:
+            self.blocks = nn.ModuleList(
+                [nn.Sequential(nn.Conv2d(64, 64, 3, padding=1), nn.ReLU(), nn.Conv2d(64, 64, 3, padding=1))
+                 for _ in range(10)])
         self.postblock = nn.Sequential(
             self._up(2), nn.Conv2d(64, 64, 3, padding=1), nn.ReLU(),
             self._up(2), nn.Conv2d(64, 64, 3, padding=1), nn.ReLU(),
@@ -72,40 +90,69 @@ class EnhanceNet(nn.Module):
     # ---- pickling: drop the native handle -------------------------------------------------------------------
     def __getstate__(self):
         st = dict(self.__dict__)
-        st["_handle"] = None
-        st["_handle_key"] = None
+        for k in ("_handle", "_handle_key", "_generation"):    # class-level defaults take over after un-pickling
+            st.pop(k, None)
         return st
 
     @classmethod
     def from_reference(cls, module):
         """Builds a drop-in from a reference ``EnhanceNet`` instance (e.g. un-pickled from a checkpoint)."""
         from argparse import Namespace
-        opt = Namespace(upsample=module.upsample, reconType=module.recon_type, useBN=module.use_bn)
+        opt = Namespace(upsample=module.upsample, reconType=module.recon_type, useBN=getattr(module, "use_bn", False))
         mask = getattr(module, "channel_mask", None)
         cin = module.preblock[0].in_channels
         cout = module.postblock[8].out_channels
-        if mask is None:                                   # old checkpoints (enhancenet.py:57-61)
-            mask = list(range(min(cin, cout)))
+        if mask is None:                                   # checkpoints prior to unshaded networks (enhancenet.py:57-61)
+            mask = [0, 1, 2]
         net = cls(module.upscale_factor, cin, mask, cout, opt)
         net.load_state_dict(module.state_dict())
         return net.to(module.preblock[0].weight.device).train(module.training)
 
     # ---- CUDA path ------------------------------------------------------------------------------------------
+    def _convs(self):
+        """The 25 convolutions in execution order, each with the BatchNorm2d that follows it (or None)."""
+        out = [(self.preblock[0], None)]
+        for block in self.blocks:
+            if getattr(self, "use_bn", False):
+                out += [(block[0], block[1]), (block[3], block[4])]
+            else:
+                out += [(block[0], None), (block[2], None)]
+        out += [(self.postblock[j], None) for j in (1, 4, 6, 8)]
+        return out
+
     def _params(self):
-        sd = dict(self.named_parameters())
-        return [sd[k] for k in STATE_DICT_KEYS]
+        """50 tensors (weight, bias per conv) as the kernels consume them.  An eval-mode BatchNorm2d is an affine map
+        per channel and folds exactly into the conv in front of it:
+        w' = w * g / sqrt(var + eps),  b' = (b - mean) * g / sqrt(var + eps) + beta."""
+        out = []
+        for conv, bn in self._convs():
+            w, b = conv.weight.detach(), conv.bias.detach()
+            if bn is not None:
+                scale = bn.weight.detach() / torch.sqrt(bn.running_var + bn.eps)
+                w = w * scale.view(-1, 1, 1, 1)
+                b = (b - bn.running_mean) * scale + bn.bias.detach()
+            out += [w, b]
+        return out
+
+    def invalidate(self):
+        """Forces a re-pack of the weights at the next forward.  Needed only after in-place updates that bypass autograd's
+        version counter (``p.data.mul_()``, ``p.data.copy_()``): ordinary optimiser steps, ``load_state_dict`` and
+        ``.to()`` are detected automatically."""
+        self._generation += 1
 
     def _native(self):
-        params = self._params()
-        dev = params[0].device
-        key = (str(dev), self.upsample, self.recon_type, tuple(p._version for p in params),
-               tuple(p.data_ptr() for p in params))
+        tensors = [t for conv, bn in self._convs() for t in
+                   ((conv.weight, conv.bias) if bn is None else
+                    (conv.weight, conv.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var))]
+        dev = tensors[0].device
+        key = (str(dev), self.upsample, self.recon_type, self._generation, tuple(t._version for t in tensors),
+               tuple(t.data_ptr() for t in tensors))
         if self._handle is None or self._handle_key != key:
             if self._handle is None or self._handle_key[:3] != key[:3]:
                 n_mask = len(self.channel_mask) if self.recon_type == "residual" else 0
-                self._handle = ops.NetHandle(self.input_channels, self.output_channels, n_mask, self.upsample,
+                self._handle = ops.NetHandle(self.preblock[0].in_channels, self.output_channels, n_mask, self.upsample,
                                              self.recon_type == "residual", dev)
-            self._handle.load_weights(params)
+            self._handle.load_weights(self._params())
             self._handle_key = key
         return self._handle
 
@@ -120,9 +167,12 @@ class EnhanceNet(nn.Module):
         needs_grad = torch.is_grad_enabled() and (
             inputs.requires_grad or any(p.requires_grad for p in self.parameters()))
         if needs_grad:
-            return self._forward_autograd(inputs, previous_output, flow, special_mask)
+            return self._forward_autograd(inputs, previous_output, flow, special_mask, return_state)
         if not inputs.is_cuda:
             raise RuntimeError("EnhanceNet (B200 build): inference needs CUDA tensors; there is no CPU fallback")
+        if getattr(self, "use_bn", False) and self.training:
+            raise RuntimeError("EnhanceNet (B200 build): BatchNorm in training mode uses batch statistics and cannot be "
+                               "folded into the convolutions; call .eval() / .train(False) for inference")
         h = self._native()
         unshaded = self.output_channels == 6
         if previous_output is None:
@@ -138,7 +188,7 @@ class EnhanceNet(nn.Module):
         return recon, raw
 
     # ---- training path (differentiable torch ops on the same parameters) --------------------------------------
-    def _forward_autograd(self, inputs, previous_output, flow, special_mask):
+    def _forward_autograd(self, inputs, previous_output, flow, special_mask, return_state=False):
         if previous_output is not None:
             from .videotools import VideoTools
             if flow is not None:
@@ -153,6 +203,19 @@ class EnhanceNet(nn.Module):
             n = len(self.channel_mask)
             resized = F.interpolate(inputs[:, 0:n, :, :], size=[outputs.shape[2], outputs.shape[3]], mode=self.upsample)
             if n == self.output_channels:
-                return resized + outputs, outputs
-            return torch.cat([resized + outputs[:, 0:n, :, :], outputs[:, n:, :, :]], dim=1), outputs
-        return outputs, outputs
+                recon = resized + outputs
+            else:
+                recon = torch.cat([resized + outputs[:, 0:n, :, :], outputs[:, n:, :, :]], dim=1)
+        else:
+            recon = outputs
+        if return_state:
+            return recon, outputs, self._state_autograd(recon)
+        return recon, outputs
+
+    def _state_autograd(self, pred):
+        """Inter-frame post-processing (mainVideoUnshaded.py:460-465 / mainVideo.py:416) with differentiable ops."""
+        if self.output_channels == 6:
+            n = pred[:, 1:4]
+            n = n / torch.clamp(torch.norm(n, p=2, dim=1, keepdim=True), min=1e-7)
+            return torch.cat([torch.clamp(pred[:, 0:1], -1, 1), n, torch.clamp(pred[:, 4:], 0, 1)], dim=1)
+        return torch.clamp(pred, 0, 1)

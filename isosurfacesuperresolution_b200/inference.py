@@ -12,6 +12,29 @@ from .initial_image import initialImage
 from .shading import ScreenSpaceShading
 
 
+def _checkpoint_pickle_module():
+    """``pickle`` with one change: ``models.enhancenet.EnhanceNet`` -- the class path inside the reference's whole-module
+    checkpoints (mainVideoUnshaded.py:799-811) -- resolves to the drop-in when no ``models`` package is importable (with
+    compat/ or the reference tree on sys.path the normal lookup wins)."""
+    import pickle
+    import types
+
+    class Unpickler(pickle.Unpickler):
+        def find_class(self, module, name):
+            if module == "models.enhancenet" and name == "EnhanceNet":
+                try:
+                    return super().find_class(module, name)
+                except (ImportError, AttributeError):
+                    return EnhanceNet
+            return super().find_class(module, name)
+
+    mod = types.ModuleType("isr_checkpoint_pickle")
+    mod.__dict__.update({k: getattr(pickle, k) for k in dir(pickle) if not k.startswith("__")})
+    mod.Unpickler = Unpickler
+    mod.load = lambda f, **kw: Unpickler(f, **kw).load()
+    return mod
+
+
 def _as_dropin(model):
     if isinstance(model, EnhanceNet):
         return model
@@ -30,7 +53,8 @@ class LoadedModel:
         if isinstance(name, (str, bytes, os.PathLike)):
             self.name = os.path.splitext(os.path.basename(name))[0]
             # whole-module pickles (mainVideoUnshaded.py:799-811) need weights_only=False; only for trusted files
-            checkpoint = torch.load(name, map_location="cpu", weights_only=False)
+            checkpoint = torch.load(name, map_location="cpu", weights_only=False,
+                                    pickle_module=_checkpoint_pickle_module())
         else:
             self.name = "model"
             checkpoint = name if isinstance(name, dict) else {"model": name}
@@ -140,6 +164,16 @@ def compose_frame(image_low, image_raw, shading=None, masking=False, background=
                        float(background[0]))
 
 
+def temporal_smoothing(previous_rgb, flow, image_rgb, factor, upscale_factor=4):
+    """The GUI's temporal post-smoothing (mainGUI.py:834-849) as one kernel: the previously DISPLAYED RGB frame is warped
+    by the (in-painted) flow with ``special_mask=False`` and blended, ``factor * warped + (1 - factor) * image_rgb``
+    (``factor`` = slider / 100).  ``previous_rgb is None`` or ``factor == 0`` returns ``image_rgb`` (mainGUI.py:835-838)."""
+    from . import ops
+    if previous_rgb is None or factor == 0:
+        return image_rgb
+    return ops.temporal_blend(previous_rgb, flow, image_rgb, float(factor), upscale_factor)
+
+
 class SequenceRunner:
     """Forward-only frame recurrence over a batch of independent sequences (mainVideoUnshaded.py:417-465).
 
@@ -184,4 +218,4 @@ class SequenceRunner:
         return preds, rgbs, state
 
 
-__all__ = ["LoadedModel", "SequenceRunner", "ScreenSpaceShading", "compose_frame"]
+__all__ = ["LoadedModel", "SequenceRunner", "ScreenSpaceShading", "compose_frame", "temporal_smoothing"]

@@ -55,6 +55,20 @@ def warp_upscale(image_high, flow_low, upscale_factor, special_mask=False, align
     return out
 
 
+def temporal_blend(prev_rgb, flow_low, cur_rgb, factor, upscale_factor=4):
+    """Temporal post-smoothing of the displayed frame (mainGUI.py:834-849) in one pass:
+    ``factor * warp_upscale(prev_rgb, flow, special_mask=False) + (1 - factor) * cur_rgb``."""
+    prev, flow, cur = _prep(prev_rgb, "prev_rgb"), _prep(flow_low, "flow_low"), _prep(cur_rgb, "cur_rgb")
+    B, C, H, W = cur.shape
+    r = int(upscale_factor)
+    assert tuple(prev.shape) == tuple(cur.shape) and tuple(flow.shape) == (B, 2, H // r, W // r) and H % r == 0 and W % r == 0
+    out = torch.empty_like(cur)
+    with torch.cuda.device(cur.device):
+        check(lib().isr_temporal_blend(_p(prev), _p(flow), _p(cur), _p(out), B, C, H // r, W // r, r, float(factor),
+                                       _stream()))
+    return out
+
+
 def initial_image(current_input, channels, mode, ao_inverted, upscaling=4):
     """initialImage (utils/initial_image.py:5-54)."""
     if mode not in INITIAL:
@@ -273,7 +287,11 @@ class NetHandle:
         with torch.cuda.device(self.device):
             check(lib().isr_net_create(ctypes.byref(self._net), self.cin, self.cout, int(n_mask), UPSAMPLE[upsample],
                                        int(bool(recon_residual))))
-        self._ws = {}
+        self._ws = {}          # (B, h, w, precision) -> (tensor, aligned pointer, bytes), least recently used first
+
+    def set_tunable(self, key, value):
+        """Changes a tunable of THIS handle (include/isr.h isr_net_set_tunable); returns the previous value."""
+        return check(lib().isr_net_set_tunable(self._net, key.encode(), int(value)))
 
     def __del__(self):
         try:
@@ -292,13 +310,19 @@ class NetHandle:
 
     def workspace(self, B, h, w, precision):
         key = (B, h, w, precision)
-        if key not in self._ws:
-            n = ctypes.c_size_t(0)
-            check(lib().isr_net_workspace_bytes(self._net, B, h, w, PREC[precision], ctypes.byref(n)))
-            if len(self._ws) >= 4:
-                self._ws.clear()
-            buf, ptr = _workspace(self.device, n.value)
-            self._ws[key] = (buf, ptr, n.value)
+        if key in self._ws:
+            self._ws[key] = self._ws.pop(key)            # most recently used last
+            return self._ws[key]
+        n = ctypes.c_size_t(0)
+        check(lib().isr_net_workspace_bytes(self._net, B, h, w, PREC[precision], ctypes.byref(n)))
+        if len(self._ws) >= 4:
+            # evict the least recently used block -- only after every stream of the device has drained: kernels of a
+            # forward issued on a non-current stream may still be using it, and torch's caching allocator would hand the
+            # block to the next tensor of the current stream at once.  (RecurrentPipeline keeps its own reference.)
+            torch.cuda.synchronize(self.device)
+            self._ws.pop(next(iter(self._ws)))
+        buf, ptr = _workspace(self.device, n.value)
+        self._ws[key] = (buf, ptr, n.value)
         return self._ws[key]
 
     def forward(self, inputs, precision="hybrid", want_raw=True, want_state=False, state_unshaded=True):
@@ -355,7 +379,9 @@ class RecurrentPipeline:
             raise ValueError("unknown input mode: " + str(initial_mode))
         self.handle, self.B, self.h, self.w, self.c_low = handle, int(B), int(h), int(w), int(c_low)
         dev = handle.device
-        _, ws_ptr, ws_bytes = handle.workspace(B, h, w, precision)
+        # the pipeline launches on its own streams: it owns a reference to the workspace tensor (an eviction from the
+        # handle's cache must not free it under running kernels) and allocates nothing from the caching allocator later
+        self._ws_tensor, ws_ptr, ws_bytes = handle.workspace(B, h, w, precision)
         n = ctypes.c_size_t(0)
         check(lib().isr_pipe_staging_floats(handle._net, c_low, B, h, w, depth, ctypes.byref(n)))
         self.state = torch.zeros((B, c_prev, 4 * h, 4 * w), device=dev, dtype=torch.float32)
@@ -400,6 +426,37 @@ class RecurrentPipeline:
         with torch.cuda.device(self.handle.device):
             check(lib().isr_pipe_submit_display(self._pipe, lo, fl, ctypes.c_void_p(rgb8_host.data_ptr())))
 
+    def set_state(self, state):
+        """Use another recurrent-state tensor (B x c_prev x 4h x 4w, CUDA fp32) for the frames submitted from now on: one
+        pipeline serves several chunks of independent sequences in turn (configs[4]: 64 sequences as 16 chunks of 4)."""
+        if (not isinstance(state, torch.Tensor) or not state.is_cuda or state.dtype != torch.float32
+                or tuple(state.shape) != tuple(self.state.shape) or not state.is_contiguous()):
+            raise TypeError("state: expected a contiguous CUDA float32 tensor of shape " + str(tuple(self.state.shape)))
+        if not hasattr(self, "_states"):
+            self._states = [self.state]        # frames in flight on the pipeline's own streams may still use them
+        if all(t is not state for t in self._states):
+            self._states.append(state)
+        self.state = state
+        check(lib().isr_pipe_set_state(self._pipe, _p(state)))
+
+    def enable_f16(self):
+        """Switch on the 16-bit form: ``submit_f16`` returns the full prediction rounded to fp16 (half the D2H bytes)."""
+        n = 1
+        for d in self.out_shape:
+            n *= d
+        nbytes = 8 * n * 2                                            # room for depth <= 8
+        self._f16 = torch.empty(nbytes, device=self.handle.device, dtype=torch.uint8)
+        check(lib().isr_pipe_enable_f16(self._pipe, _p(self._f16), nbytes))
+
+    def submit_f16(self, low_host, flow_host, recon_f16_host):
+        lo = self._host(low_host, "low_host", (self.B, self.c_low, self.h, self.w))
+        fl = self._host(flow_host, "flow_host", (self.B, 2, self.h, self.w)) if flow_host is not None else ctypes.c_void_p(0)
+        if (not isinstance(recon_f16_host, torch.Tensor) or recon_f16_host.is_cuda or recon_f16_host.dtype != torch.float16
+                or tuple(recon_f16_host.shape) != tuple(self.out_shape) or not recon_f16_host.is_contiguous()):
+            raise TypeError("recon_f16_host: expected a contiguous float16 CPU tensor of the prediction's shape (pinned for overlap)")
+        with torch.cuda.device(self.handle.device):
+            check(lib().isr_pipe_submit_f16(self._pipe, lo, fl, ctypes.c_void_p(recon_f16_host.data_ptr())))
+
     def wait(self):
         check(lib().isr_pipe_wait(self._pipe))
 
@@ -415,5 +472,5 @@ class RecurrentPipeline:
             pass
 
 
-__all__ = ["RecurrentPipeline", "compose", "flatten_high", "warp_upscale", "initial_image", "postprocess", "shade", "debug_conv3x3", "NetHandle",
+__all__ = ["RecurrentPipeline", "compose", "temporal_blend", "flatten_high", "warp_upscale", "initial_image", "postprocess", "shade", "debug_conv3x3", "NetHandle",
            "IsrError", "PREC"]

@@ -73,7 +73,7 @@ class DenseGridRenderer:
         self.camera_light, self.light_direction = True, [0.0, 0.0, 0.0]
         self.ao_samples, self.ao_radius, self.ao_bias = 32, 0.01, 1e-3
         self.step, self.binary_steps = 0.05, 10           # SetSteps(0.05, ...), :365; binarySearchSteps, render_kernel.cu:21
-        self._last = None                                 # (origin, look_at) of the previous frame
+        self._last = None                                 # proj @ view of the previous frame (flow is computed against it)
         self.hemisphere, self.rotations = ops.raycast_ao_tables()
 
     # -- DirectRenderer interface ---------------------------------------------------------------------------------
@@ -122,14 +122,16 @@ class DenseGridRenderer:
         voxel = self.world_size / max(nx, ny, nz)
         P = np.zeros(RC_PARAMS, np.float32)
         view, proj, S, U, V = camera_matrices(self.origin, self.look_at, self.up, self.fov, W / H)
-        lo, ll = self._last if self._last is not None else (self.origin, self.look_at)
-        view_n, proj_n, _, _, _ = camera_matrices(lo, ll, self.up, self.fov, W / H)
+        # the previous frame's full view-projection matrix: a change of cameraUp, fov or resolution between two frames
+        # moves the projection as much as a change of origin / look-at does
+        vp_cur = proj @ view
+        vp_last = self._last if self._last is not None else vp_cur
         P[RC_CAM_POS:RC_CAM_POS + 3] = self.origin
         P[RC_CAM_U:RC_CAM_U + 3], P[RC_CAM_V:RC_CAM_V + 3], P[RC_CAM_S:RC_CAM_S + 3] = U, V, S
         P[RC_BOX_MIN:RC_BOX_MIN + 3] = [-0.5 * nx * voxel, -0.5 * ny * voxel, -0.5 * nz * voxel]
         P[RC_VOXEL], P[RC_ISO], P[RC_STEP] = voxel, self.isovalue, self.step
-        P[RC_VIEW_CUR:RC_VIEW_CUR + 16] = (proj @ view).reshape(-1)
-        P[RC_VIEW_NEXT:RC_VIEW_NEXT + 16] = (proj_n @ view_n).reshape(-1)
+        P[RC_VIEW_CUR:RC_VIEW_CUR + 16] = vp_cur.reshape(-1)
+        P[RC_VIEW_NEXT:RC_VIEW_NEXT + 16] = vp_last.reshape(-1)
         P[RC_NORMAL_MAT:RC_NORMAL_MAT + 16] = view.reshape(-1)
         light = (np.asarray(self.look_at, np.float64) - np.asarray(self.origin, np.float64)) if self.camera_light \
             else np.asarray(self.light_direction, np.float64)
@@ -150,7 +152,7 @@ class DenseGridRenderer:
                         binary_steps=self.binary_steps, viewport=self.viewport, skip=self.skip)
         torch.cuda.synchronize(self.device)
         self.time = time.perf_counter() - t0
-        self._last = (list(self.origin), list(self.look_at))
+        self._last = P[RC_VIEW_CUR:RC_VIEW_CUR + 16].reshape(4, 4).copy()
         return self.time
 
     def get_time(self):

@@ -91,7 +91,12 @@ class ScreenSpaceShading(nn.Module):
         if torch.is_grad_enabled() and input.requires_grad:
             return self._forward_autograd(input)
         if not input.is_cuda:
-            raise RuntimeError("ScreenSpaceShading (B200 build): needs a CUDA tensor; there is no CPU fallback")
+            # several reference scripts shade `.cpu()` copies with ScreenSpaceShading('cpu') (mainPSNR2_AllAngles.py:188,
+            # mainDatasetViewer.py:115, mainComparisonImages.py:189).  There is still no CPU arithmetic
+            # here: the tensor is shaded by the CUDA kernel and the result is returned on the caller's device.
+            if not torch.cuda.is_available():
+                raise RuntimeError("ScreenSpaceShading (B200 build): needs a CUDA device; there is no CPU fallback")
+            return ops.shade(input.cuda(), self.params22()).to(input.device)
         return ops.shade(input, self.params22())
 
     def _forward_autograd(self, x):

@@ -228,8 +228,149 @@ def unshaded_sequence(state_dict, low, flow, upsample_mode="bilinear", initial="
     return preds, rgbs
 
 
-# Synthetic inputs live in the package's numpy-only generator so that bench / tests / oracle agree bit for bit.
-from isosurfacesuperresolution_b200.synthetic import shading_params, synthetic_gbuffer  # noqa: E402,F401
+# The same recurrence written ONLY with torch ops, so that it can run on any torch device: on "cpu" it is the reference's
+# CPU arithmetic (ATen / oneDNN), on "cuda" (TF32 off) it is what the reference computes on a GPU (ATen / cuDNN fp32).
+# The difference between the two is the noise floor SURVEY.md 8(c) asks to record: no implementation can be closer to
+# "the reference" than the reference's two own back ends are to each other.
+def unshaded_sequence_torch(state_dict, low, flow, device="cpu", upsample_mode="bilinear", initial="input",
+                            teacher=None):
+    """Returns the list of T predictions (numpy).  ``teacher``: optional list of previous-frame predictions to use as
+    the state instead of the run's own (teacher forcing)."""
+    dev = torch.device(device)
+    if dev.type == "cuda":
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+    t = [torch.from_numpy(_f32(state_dict[k])).to(dev) for k in STATE_DICT_KEYS]
+    tl, tf = torch.from_numpy(_f32(low)).to(dev), torch.from_numpy(_f32(flow)).to(dev)
+    B, T, _, h, w = tl.shape
+    H, W = 4 * h, 4 * w
+
+    def net(x):
+        f = F.relu(F.conv2d(x, t[0], t[1], padding=1))
+        pi = 2
+        for _ in range(10):
+            u = F.conv2d(F.relu(F.conv2d(f, t[pi], t[pi + 1], padding=1)), t[pi + 2], t[pi + 3], padding=1)
+            f = f + u
+            pi += 4
+        for _ in range(2):
+            f = F.interpolate(f, scale_factor=2, mode=upsample_mode)
+            f = F.relu(F.conv2d(f, t[pi], t[pi + 1], padding=1)); pi += 2
+        f = F.relu(F.conv2d(f, t[pi], t[pi + 1], padding=1)); pi += 2
+        raw = F.conv2d(f, t[pi], t[pi + 1], padding=1)
+        sk = F.interpolate(x[:, 0:5], size=[H, W], mode=upsample_mode)
+        return torch.cat([sk + raw[:, 0:5], raw[:, 5:]], dim=1)
+
+    def post(p):                                               # mainVideoUnshaded.py:460-465, shading.py:193-207
+        n = p[:, 1:4]
+        n = n / torch.clamp(torch.norm(n, p=2, dim=1, keepdim=True), min=1e-7)
+        return torch.cat([torch.clamp(p[:, 0:1], -1, 1), n, torch.clamp(p[:, 4:5], 0, 1), torch.clamp(p[:, 5:6], 0, 1)], 1)
+
+    gh = torch.linspace(-1, 1, H, device=dev).unsqueeze(1)
+    gw = torch.linspace(-1, 1, W, device=dev).unsqueeze(0)
+    offs = torch.stack(torch.broadcast_tensors(gw, gh), dim=2).unsqueeze(0)
+    preds = []
+    prev = None
+    with torch.no_grad():
+        for j in range(T):
+            inp = tl[:, j]
+            if j == 0:
+                assert initial == "input"                      # initial_image.py:39-52
+                up = F.interpolate(inp, scale_factor=4, mode="bilinear")
+                warped = torch.cat([up, torch.ones(B, 1, H, W, device=dev)], dim=1)
+            else:
+                if teacher is not None:
+                    prev = post(torch.from_numpy(_f32(teacher[j - 1])).to(dev))
+                f2 = torch.cat((tf[:, j - 1, 0:1] * -2.0, tf[:, j - 1, 1:2] * 2.0), dim=1)
+                grid = offs + F.interpolate(f2, scale_factor=4, mode="bilinear").permute(0, 2, 3, 1)
+                pm = torch.cat([prev[:, 0:1] * 0.5 + 0.5, prev[:, 1:]], dim=1)
+                o = F.grid_sample(pm, grid, mode="bilinear", padding_mode="zeros", align_corners=False)
+                warped = torch.cat([o[:, 0:1] * 2 - 1, o[:, 1:]], dim=1)
+            pred = net(torch.cat((inp, F.pixel_unshuffle(warped, 4)), dim=1))
+            preds.append(pred.cpu().numpy())
+            prev = post(pred)
+    return preds
+
+
+# mainVideo.py:383-434 in the form the inference facade runs it (loadedmodel.py:97-119): shaded (RGB) network, previous
+# RGB frame warped with special_mask=False, clamp(pred, 0, 1) as the state, zero initial image
+def shaded_sequence(state_dict, inputs, flow, upsample_mode="bilinear", backend="torch"):
+    """inputs: B x T x c_low x h x w (RGB, mask in [0,1][, normal][, depth]), flow: B x T x 2 x h x w
+    -> list of T (unclamped) predictions B x 3 x 4h x 4w."""
+    inputs, flow = _f32(inputs), _f32(flow)
+    B, T, _, h, w = inputs.shape
+    preds = []
+    prev = None
+    for j in range(T):
+        inp = inputs[:, j]
+        if j == 0:
+            warped = initial_image(inp, 3, "zero", False, 4)                      # mainVideo.py:385-388
+        else:
+            warped = warp_upscale(prev, flow[:, j - 1], 4, special_mask=False, backend=backend)
+        single = np.concatenate([inp, flatten_high(warped, 4, backend=backend)], axis=1)
+        recon, _ = enhancenet_forward(state_dict, single, upsample_mode, "residual", 3, backend=backend)
+        preds.append(recon)
+        prev = postprocess(recon, unshaded=False)                                 # mainVideo.py:416
+    return preds
+
+
+# inference/loadedmodel.py:70-121 (one frame of the facade, including its host-side OpenCV flow in-painting -- third
+# party, opencv-python, pinned 4.0.1 by the reference's Requirements.txt, 4.13 installed here)
+def loadedmodel_inference(state_dict, current_low, prev_high, unshaded, initial_mode, has_normal=True, has_depth=True,
+                          backend="torch"):
+    import cv2 as cv
+    x = _f32(current_low)
+    B = x.shape[0]
+    flow = np.empty((B, 2) + x.shape[2:], np.float32)
+    for b in range(B):                                        # the reference handles batch 1 only ([0], :77)
+        hole = np.uint8(x[b, 3] == 0)
+        flow[b, 0] = cv.inpaint(x[b, 8], hole, 3, cv.INPAINT_NS)
+        flow[b, 1] = cv.inpaint(x[b, 9], hole, 3, cv.INPAINT_NS)
+    if unshaded:
+        inp = np.concatenate([x[:, 3:4] * np.float32(2) - np.float32(1), x[:, 4:8]], axis=1)
+        if prev_high is None:
+            warped = initial_image(inp, 6, initial_mode, False, 4)
+        else:
+            warped = warp_upscale(prev_high, flow, 4, special_mask=True, backend=backend)
+        n_mask = 5
+    else:
+        if has_normal and has_depth:
+            inp = np.clip(x[:, 0:8], 0, 1)
+        elif has_normal:
+            inp = x[:, 0:7]
+        elif has_depth:
+            inp = np.concatenate([x[:, 0:4], x[:, 7:8]], axis=1)
+        else:
+            inp = x[:, 0:4]
+        if prev_high is None:
+            prev_high = initial_image(inp, 3, initial_mode, False, 4)             # :110
+        warped = warp_upscale(prev_high, flow, 4, special_mask=False, backend=backend)
+        n_mask = 3
+    single = np.concatenate([_f32(inp), flatten_high(warped, 4, backend=backend)], axis=1)
+    return enhancenet_forward(state_dict, single, "bilinear", "residual", n_mask, backend=backend)[0]
+
+
+# mainGUI.py:834-849: temporal post-smoothing of the displayed RGB frame -- the previous displayed frame warped by the
+# (in-painted) flow with special_mask=False, exponentially blended with the current one.  `factor` is a Python float in
+# the reference; torch multiplies an fp32 tensor by fp32(factor) and by fp32(1 - factor) (1 - factor taken in double).
+def temporal_blend(prev_rgb, flow, cur_rgb, factor):
+    warped = warp_upscale(prev_rgb, flow, 4, special_mask=False, backend="c")
+    a, b = np.float32(factor), np.float32(1.0 - float(factor))
+    return (a * warped).astype(np.float32) + (b * _f32(cur_rgb)).astype(np.float32)
+
+
+# Synthetic inputs come from the package's numpy-only generator so that bench / tests / oracle agree bit for bit.  The
+# FILE is loaded by path: importing the package would dlopen libisr.so, and the oracle must not touch the product.
+def _load_synthetic():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        "isr_synthetic", os.path.join(os.path.dirname(_HERE), "isosurfacesuperresolution_b200", "synthetic.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+_syn = _load_synthetic()
+shading_params, synthetic_gbuffer = _syn.shading_params, _syn.synthetic_gbuffer
 
 
 # mainGUI.py:603-608,615-636 (GUI.performSuperresolution, composition part; the method itself needs tkinter and cannot be

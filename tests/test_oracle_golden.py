@@ -86,3 +86,71 @@ def test_sequence_recurrence(golden, weights):
     for j in range(3):
         assert maxabs(preds[j], g[f"pred_{j}"]) <= 1e-4
         assert maxabs(rgbs[j], g[f"rgb_{j}"]) <= 1e-4
+
+
+# ---- round-2 fixtures (oracle/gen_golden_r02.py, live reference) -----------------------------------------------------
+def test_sequence_recurrence_10_frames(golden, weights):
+    """configs[1] runs 10-frame sequences: the oracle follows the live reference over all ten (free-running on both
+    sides; fp32 vs fp32, so the feedback loop only amplifies summation-order noise)."""
+    g = golden("sequence_unshaded_10")
+    preds, _ = orc.unshaded_sequence(weights, g["low"], g["flow"], "bilinear", "input", backend="torch")
+    assert len(preds) == 10
+    for j in range(10):
+        assert maxabs(preds[j], g[f"pred_{j}"]) <= 2e-3, j
+    assert maxabs(preds[0], g["pred_0"]) <= 1e-5
+
+
+def _seeded_reference_weights(cin, cout, seed):
+    """The reference constructor's weights under torch.manual_seed(seed), rebuilt without the reference: the same
+    sequence of nn.Conv2d constructions (default init) and the orthogonal re-init of the 20 block convs
+    (models/enhancenet.py:92-133) draws the same random numbers.  Pinned by the fixtures' checksums."""
+    import torch
+    import torch.nn as nn
+    torch.manual_seed(seed)
+    convs = [nn.Conv2d(cin, 64, 3, padding=1)] + [nn.Conv2d(64, 64, 3, padding=1) for _ in range(20)]
+    convs += [nn.Conv2d(64, 64, 3, padding=1) for _ in range(3)] + [nn.Conv2d(64, cout, 3, padding=1)]
+    for c in convs[1:21]:
+        nn.init.orthogonal_(c.weight, nn.init.calculate_gain("relu"))
+    sd = {}
+    for key, c in zip(orc.STATE_DICT_KEYS[0::2], convs):
+        sd[key] = c.weight.detach().numpy()
+        sd[key.replace("weight", "bias")] = c.bias.detach().numpy()
+    return sd
+
+
+def _weight_sum(sd):
+    return [float(sum(np.asarray(v, np.float64).sum() for v in sd.values())),
+            float(sum(np.abs(np.asarray(v, np.float64)).sum() for v in sd.values()))]
+
+
+def test_sequence_shaded(golden):
+    """Shaded (RGB) recurrence, mainVideo.py:383-434 / loadedmodel.py:97-119: 56 -> 3, special_mask=False, clamp state."""
+    g = golden("sequence_shaded")
+    sd = _seeded_reference_weights(56, 3, 1234)
+    assert np.allclose(_weight_sum(sd), g["weight_sum"], rtol=1e-9)
+    preds = orc.shaded_sequence(sd, g["input"], g["flow"], "bilinear", backend="torch")
+    for j in range(g["input"].shape[1]):
+        assert maxabs(preds[j], g[f"pred_{j}"]) <= 1e-4, j
+
+
+@pytest.mark.parametrize("seed", [1, 7, 42, 2024, 31337])
+def test_enhancenet_more_seeds(golden, seed):
+    g = golden("enhancenet_seeds")
+    sd = _seeded_reference_weights(101, 6, seed)
+    assert np.allclose(_weight_sum(sd), g[f"weight_sum_{seed}"], rtol=1e-9)
+    for kind in ("uniform", "gbuffer"):
+        recon, _ = orc.enhancenet_forward(sd, g[f"x_{kind}"], "bilinear", "residual", 5, backend="torch")
+        assert maxabs(recon, g[f"recon_{kind}_{seed}"]) <= 1e-5
+
+
+def test_loadedmodel_facade_oracle(golden, weights):
+    """The oracle's restatement of LoadedModel.inference against the reference's own facade (un-pickled checkpoint,
+    OpenCV in-painting included), unshaded and shaded, first and second frame."""
+    g = golden("loadedmodel")
+    sd_s = _seeded_reference_weights(56, 3, 1234)
+    for tag, sd, unshaded, init in (("unshaded", weights, True, "input"), ("shaded", sd_s, False, "zero")):
+        p0 = orc.loadedmodel_inference(sd, g["render_0"], None, unshaded, init)
+        assert maxabs(p0, g[f"{tag}_p0"]) <= 1e-5
+        assert maxabs(orc.postprocess(g[f"{tag}_p0"], unshaded=unshaded), g[f"{tag}_state0"]) <= 1e-6
+        p1 = orc.loadedmodel_inference(sd, g["render_1"], g[f"{tag}_state0"], unshaded, init)
+        assert maxabs(p1, g[f"{tag}_p1"]) <= 1e-5
