@@ -97,9 +97,9 @@ int isr_shade_rgb8(const float *gbuf, const float *params_host, unsigned char *r
 
 /* Temporal post-smoothing of the displayed frame (mainGUI.py:834-849): out = factor * warp_upscale(prev_rgb, flow, r,
  * special_mask = False) + (1 - factor) * cur_rgb in one pass (the GUI's second warp of the previous RGB frame + exponential
- * blend; factor = slider / 100).  prev_rgb / cur_rgb / out: B x C x h*r x w*r, flow: B x 2 x h x w (in-painted). */
+ * blend; factor = slider / 100, a double as in the reference: it multiplies by fp32(factor) and fp32(1 - factor)).  prev_rgb / cur_rgb / out: B x C x h*r x w*r, flow: B x 2 x h x w (in-painted). */
 int isr_temporal_blend(const float *prev_rgb, const float *flow, const float *cur_rgb, float *out, int B, int C, int h,
-                       int w, int r, float factor, void *stream);
+                       int w, int r, double factor, void *stream);
 
 /* GUI / video composition (mainGUI.py:603-608,615-636; mainComparisonVideo3.py:540-556): bilinear x4 of the c_low-channel
  * low-res render (RGB, mask, normal, depth, flow, AO, shadow: c_low >= 12 for the unshaded form, >= 4 otherwise);
@@ -299,6 +299,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "final_issuers" (1 | [3])        MMA-issuing warps of the tap-stacked output conv
  *   "final_w_parts" ([0] = scheme | 1 | 2)   weight planes of the output conv
  *   "raycast_two_pass" (0 | [1] = from 8 AO rays on | 2)   ambient occlusion of the ray-caster as a second pass
+ *   "compose_variant" (1 | [2])      process-wide: GUI composition kernel (2 = 4 pixels per thread, bit-identical to 1)
+ *   "pack_variant" (1 | [2])         process-wide: network-input packing kernel (2 = per-column form, bit-identical to 1)
  *   "dbg"                            bit mask of bench experiments (tools/), 0 in production */
 int isr_set_tunable(const char *key, int value);
 int isr_net_set_tunable(isr_net *net, const char *key, int value);

@@ -75,7 +75,7 @@ SIGNATURES = {
     "isr_debug_conv_workspace_bytes": (_i, [_i, _i, _i, _c.POINTER(_sz)]),
     "isr_set_tunable": (_i, [_c.c_char_p, _i]),
     "isr_net_set_tunable": (_i, [_vp, _c.c_char_p, _i]),
-    "isr_temporal_blend": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _c.c_float, _vp]),
+    "isr_temporal_blend": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _c.c_double, _vp]),
     "isr_pipe_set_state": (_i, [_vp, _vp]),
     "isr_pipe_enable_f16": (_i, [_vp, _vp, _sz]),
     "isr_pipe_submit_f16": (_i, [_vp, _vp, _vp, _vp]),

@@ -688,6 +688,14 @@ int isr_set_tunable(const char *key, int value) {
     g_raycast_two_pass = value;
     return old;
   }
+  if (key != nullptr && strcmp(key, "pack_variant") == 0) {       // process-wide: which network-input packing kernel
+    if (value != 1 && value != 2) return fail(ISR_ERR_ARG, "pack_variant must be 1 or 2");
+    return set_pack_variant(value);
+  }
+  if (key != nullptr && strcmp(key, "compose_variant") == 0) {    // process-wide: which composition kernel
+    if (value != 1 && value != 2) return fail(ISR_ERR_ARG, "compose_variant must be 1 or 2");
+    return set_compose_variant(value);
+  }
   int *slot = tunable_slot(&g_tun, key, value);
   if (slot == nullptr) return ISR_ERR_ARG;
   const int old = *slot;
@@ -728,14 +736,14 @@ int isr_warp_upscale(const float *prev, const float *flow, float *out, int B, in
 }
 
 int isr_temporal_blend(const float *prev_rgb, const float *flow, const float *cur_rgb, float *out, int B, int C, int h,
-                       int w, int r, float factor, void *stream) {
+                       int w, int r, double factor, void *stream) {
   if (prev_rgb == nullptr || flow == nullptr || cur_rgb == nullptr || out == nullptr || B <= 0 || C <= 0 || h <= 0 ||
       w <= 0 || r <= 0)
     return fail(ISR_ERR_ARG, "temporal_blend: bad arguments");
   int rc = check_device();
   if (rc != ISR_OK) return rc;
   // the reference multiplies fp32 tensors by the Python floats `factor` and `1 - factor` (taken in double, mainGUI.py:846-847)
-  const float fa = factor, fb = static_cast<float>(1.0 - static_cast<double>(factor));
+  const float fa = static_cast<float>(factor), fb = static_cast<float>(1.0 - factor);
   ISR_CUDA(launch_temporal_blend(prev_rgb, flow, cur_rgb, out, B, C, h, w, r, fa, fb, S(stream)));
   return ISR_OK;
 }

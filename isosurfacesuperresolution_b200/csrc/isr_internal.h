@@ -23,6 +23,8 @@ cudaError_t launch_compose(const float *low, const float *pred, const float *par
 cudaError_t launch_pack_recurrent(const float *low, const float *prev, const float *flow, uint16_t *g0, uint16_t *g1,
                                   int B, int c_low, int c_prev, int h, int w, int special_mask, int align_corners,
                                   int nparts, int is_bf16, cudaStream_t s);
+int set_compose_variant(int v);   // 1 | 2: scalar / 4-pixels-per-thread composition kernel; returns the old value
+int set_pack_variant(int v);   // 1 | 2: which network-input packing kernel launch_pack_recurrent uses; returns the old value
 cudaError_t launch_pack_nchw(const float *in, uint16_t *g0, uint16_t *g1, int B, int cin, int h, int w, int nparts,
                              int is_bf16, cudaStream_t s);
 cudaError_t launch_unpack_nhwc(const uint16_t *in, float *out, int B, int H, int W, int nparts, int is_bf16,

@@ -98,11 +98,12 @@ __device__ __forceinline__ float warp_gather(const float *__restrict__ p, int W,
   if (sm) {
     v00 = v00 * 0.5f + 0.5f; v01 = v01 * 0.5f + 0.5f; v10 = v10 * 0.5f + 0.5f; v11 = v11 * 0.5f + 0.5f;
   }
-  float acc = 0.f;
-  acc += v00 * t.nw;
-  acc += v01 * t.ne;
-  acc += v10 * t.sw;
-  acc += v11 * t.se;
+  // nw, ne, sw, se in this order (grid_sampler's), each product fused into the running sum: within 1 ulp of the
+  // separate multiply + add of the CPU reference, far inside the 1e-5 contract; all warp kernels share this form
+  float acc = v00 * t.nw;
+  acc = fmaf(v01, t.ne, acc);
+  acc = fmaf(v10, t.sw, acc);
+  acc = fmaf(v11, t.se, acc);
   if (sm) acc = acc * 2.f - 1.f;
   return acc;
 }
@@ -258,11 +259,10 @@ pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ p
             float a0 = v[c][0], a1 = v[c][1], a2 = v[c][2], a3 = v[c][3];
             const bool sm = special_mask && c == 0;
             if (c == 0 && sm) { a0 = a0 * 0.5f + 0.5f; a1 = a1 * 0.5f + 0.5f; a2 = a2 * 0.5f + 0.5f; a3 = a3 * 0.5f + 0.5f; }
-            float acc = 0.f;
-            acc += a0 * t.nw;
-            acc += a1 * t.ne;
-            acc += a2 * t.sw;
-            acc += a3 * t.se;
+            float acc = a0 * t.nw;
+            acc = fmaf(a1, t.ne, acc);
+            acc = fmaf(a2, t.sw, acc);
+            acc = fmaf(a3, t.se, acc);
             if (c == 0 && sm) acc = acc * 2.f - 1.f;
             trow[c * 16] = acc;
           }
@@ -280,11 +280,10 @@ pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ p
                 const bool sm = special_mask && (c0 + c == 0);
                 float a0 = v[c][0], a1 = v[c][1], a2 = v[c][2], a3 = v[c][3];
                 if (sm) { a0 = a0 * 0.5f + 0.5f; a1 = a1 * 0.5f + 0.5f; a2 = a2 * 0.5f + 0.5f; a3 = a3 * 0.5f + 0.5f; }
-                float acc = 0.f;
-                acc += a0 * t.nw;
-                acc += a1 * t.ne;
-                acc += a2 * t.sw;
-                acc += a3 * t.se;
+                float acc = a0 * t.nw;
+                acc = fmaf(a1, t.ne, acc);
+                acc = fmaf(a2, t.sw, acc);
+                acc = fmaf(a3, t.se, acc);
                 if (sm) acc = acc * 2.f - 1.f;
                 trow[(c0 + c) * 16] = acc;
               }
@@ -304,6 +303,162 @@ pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ p
     float f[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = tile[lp][g * 64 + chunk * 8 + j];
+    uint16_t *dst = (g == 0 ? out_g0 : out_g1) + ((static_cast<size_t>(b) * h + y) * w + xb + lp) * (64 * nparts);
+    store_chunk8(dst, chunk, nparts, f, is_bf16);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// pack_recurrent_v2_kernel: the same result, bit for bit, with about a third of the instructions.  The first form
+// spends ~640 issued instructions per high-res pixel (ncu: issue slots 76-78 % busy, 0.36 of the HBM roof): every pixel
+// repeats the x- and y-axis set-up of the flow upsampling, two IEEE divisions for the linspace step, integer divisions
+// in the fill loops, and a scalar shared-memory transpose.  Here
+//   * a thread owns ONE high-res column X and walks the 4 rows of its low-res row: the x-axis set-up (source columns and
+//     weights of the 4x flow upsampling, linspace value, its division) is done once per thread instead of once per pixel;
+//   * the 4 rows share at most three low-res flow rows: 12 flow loads + 6 row interpolations per thread instead of 32 + 16
+//     (the same fmaf() sequence per value, so every F is the value warp_taps() computes);
+//   * the padding channels are never written to shared memory (phase 2 substitutes zeros), the tile pitch (132 floats)
+//     makes the scatter conflict-free and lets phase 2 read 8 channels as two 16-byte shared loads.
+// Block = 128 threads = 128 high-res columns x 4 rows = 32 low-res pixels of one low-res row.
+constexpr int kPack2Low = 32;
+constexpr int kPack2Pitch = 132;   // floats per low-res pixel in the tile: = 4 (mod 32) and a multiple of 4
+
+template <int CP, int NPARTS, int BF16>
+__global__ void __launch_bounds__(128)
+pack_recurrent_v2_kernel(const float *__restrict__ low, const float *__restrict__ prev, const float *__restrict__ flow,
+                         uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int c_low, int h, int w,
+                         int special_mask, int align_corners) {
+  constexpr int nparts = NPARTS, is_bf16 = BF16;
+  __shared__ __align__(16) float tile[kPack2Low * kPack2Pitch];
+  const int xb = blockIdx.x * kPack2Low;
+  const int y = blockIdx.y;
+  const int b = blockIdx.z;
+  const int H = h * 4, W = w * 4;
+  const int tid = threadIdx.x;
+  const int cin = c_low + 16 * CP;
+  for (int i = tid; i < kPack2Low * c_low; i += 128) {
+    const int lp = i % kPack2Low, c = i / kPack2Low;
+    if (xb + lp < w) tile[lp * kPack2Pitch + c] = __ldg(low + ((static_cast<size_t>(b) * c_low + c) * h + y) * w + xb + lp);
+  }
+  const int X = xb * 4 + tid;
+  if (X < W) {
+    const size_t plane = static_cast<size_t>(H) * W;
+    const float *pb = prev + static_cast<size_t>(b) * CP * plane;
+    float *tcol = &tile[(tid >> 2) * kPack2Pitch + c_low + (tid & 3)];
+    const int planei = H * W;
+    // opaque to the optimiser: otherwise it folds the 64-bit batch offset into every tap address (5 instead of 1
+    // integer instruction per gathered value)
+    asm volatile("" : "+l"(pb));
+    if (flow != nullptr) {
+      const float *fb = flow + static_cast<size_t>(b) * 2 * h * w;
+      // ---- x axis, once per thread (bil_src_pw / lin_m1p1 of warp_taps) ----
+      int fx0, fx1;
+      float lx0, lx1;
+      bil_src_pw(X, w, 0.25f, fx0, fx1, lx0, lx1);
+      const float linx = lin_m1p1(X, W);
+      // ---- the (at most) three low-res flow rows of this low-res row, interpolated along x (bil_sample's r0 / r1) ----
+      const int ry0 = y > 0 ? y - 1 : 0, ry2 = y < h - 1 ? y + 1 : h - 1;
+      float Rx[3], Ry[3];
+      {
+        const int rows[3] = {ry0, y, ry2};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const float *px = fb + rows[k] * w, *py = px + static_cast<size_t>(h) * w;
+          Rx[k] = fmaf(lx0, -2.f * __ldg(px + fx0), lx1 * (-2.f * __ldg(px + fx1)));
+          Ry[k] = fmaf(lx0, 2.f * __ldg(py + fx0), lx1 * (2.f * __ldg(py + fx1)));
+        }
+      }
+      const float stepy = H > 1 ? 2.0f / static_cast<float>(H - 1) : 0.f;
+#pragma unroll
+      for (int dy = 0; dy < 4; ++dy) {
+        const int Y = y * 4 + dy;
+        int fy0, fy1;
+        float ly0, ly1;
+        bil_src_pw(Y, h, 0.25f, fy0, fy1, ly0, ly1);
+        // fy0 / fy1 are rows of {ry0, y, ry2}: dy < 2 -> (y-1, y), or (0, min(1, h-1)) on the first row; dy >= 2 -> (y, ry2)
+        float r0x, r1x, r0y, r1y;
+        if (dy < 2) {
+          const bool first = y == 0;
+          r0x = first ? Rx[1] : Rx[0]; r1x = first ? Rx[2] : Rx[1];
+          r0y = first ? Ry[1] : Ry[0]; r1y = first ? Ry[2] : Ry[1];
+        } else {
+          r0x = Rx[1]; r1x = Rx[2]; r0y = Ry[1]; r1y = Ry[2];
+        }
+        const float Fx = fmaf(ly0, r0x, ly1 * r1x);
+        const float Fy = fmaf(ly0, r0y, ly1 * r1y);
+        float liny;
+        if (H == 1) liny = -1.f;
+        else liny = Y < H / 2 ? fmaf(stepy, static_cast<float>(Y), -1.f) : fmaf(-stepy, static_cast<float>(H - 1 - Y), 1.f);
+        const float gx = linx + Fx;
+        const float gy = liny + Fy;
+        float ix, iy;
+        if (align_corners) {
+          ix = ((gx + 1.f) / 2.f) * static_cast<float>(W - 1);
+          iy = ((gy + 1.f) / 2.f) * static_cast<float>(H - 1);
+        } else {
+          ix = fmaf(gx + 1.f, static_cast<float>(W), -1.f) / 2.f;
+          iy = fmaf(gy + 1.f, static_cast<float>(H), -1.f) / 2.f;
+        }
+        const float x0f = floorf(ix), y0f = floorf(iy);
+        const float x1f = x0f + 1.f, y1f = y0f + 1.f;
+        const bool okx = (x0f >= -2.f) && (x0f <= static_cast<float>(W) + 1.f);
+        const bool oky = (y0f >= -2.f) && (y0f <= static_cast<float>(H) + 1.f);
+        const int x0 = okx ? static_cast<int>(x0f) : -5;
+        const int y0 = oky ? static_cast<int>(y0f) : -5;
+        const bool vx0 = x0 >= 0 && x0 < W, vx1 = x0 + 1 >= 0 && x0 + 1 < W;
+        const bool vy0 = y0 >= 0 && y0 < H, vy1 = y0 + 1 >= 0 && y0 + 1 < H;
+        const float wnw = (vy0 && vx0) ? (x1f - ix) * (y1f - iy) : 0.f;
+        const float wne = (vy0 && vx1) ? (ix - x0f) * (y1f - iy) : 0.f;
+        const float wsw = (vy1 && vx0) ? (x1f - ix) * (iy - y0f) : 0.f;
+        const float wse = (vy1 && vx1) ? (ix - x0f) * (iy - y0f) : 0.f;
+        const int cx0 = min(max(x0, 0), W - 1), cx1 = min(max(x0 + 1, 0), W - 1);
+        const int cy0 = min(max(y0, 0), H - 1) * W, cy1 = min(max(y0 + 1, 0), H - 1) * W;
+        const int o00 = cy0 + cx0, o01 = cy0 + cx1, o10 = cy1 + cx0, o11 = cy1 + cx1;
+        float v[CP][4];
+#pragma unroll
+        for (int c = 0; c < CP; ++c) {   // all 4 * CP taps are requested before the first use; 32-bit element indices
+          v[c][0] = __ldg(pb + (o00 + c * planei));   // (the launcher checks CP * H * W < 2^31)
+          v[c][1] = __ldg(pb + (o01 + c * planei));
+          v[c][2] = __ldg(pb + (o10 + c * planei));
+          v[c][3] = __ldg(pb + (o11 + c * planei));
+        }
+#pragma unroll
+        for (int c = 0; c < CP; ++c) {
+          float a0 = v[c][0], a1 = v[c][1], a2 = v[c][2], a3 = v[c][3];
+          const bool sm = special_mask && c == 0;
+          if (c == 0 && sm) { a0 = a0 * 0.5f + 0.5f; a1 = a1 * 0.5f + 0.5f; a2 = a2 * 0.5f + 0.5f; a3 = a3 * 0.5f + 0.5f; }
+          float acc = a0 * wnw;
+          acc = fmaf(a1, wne, acc);
+          acc = fmaf(a2, wsw, acc);
+          acc = fmaf(a3, wse, acc);
+          if (c == 0 && sm) acc = acc * 2.f - 1.f;
+          tcol[c * 16 + dy * 4] = acc;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int dy = 0; dy < 4; ++dy)
+#pragma unroll
+        for (int c = 0; c < CP; ++c)
+          tcol[c * 16 + dy * 4] = __ldg(pb + (c * planei + (y * 4 + dy) * W + X));
+    }
+  }
+  __syncthreads();
+  // phase 2: 8 channels per item -> 16 B of hi (and lo) in the NHWC 16-bit groups; channels >= cin are zero padding
+  const int ngroups = (cin + 63) / 64;
+  for (int i = tid; i < kPack2Low * 8 * ngroups; i += 128) {
+    const int chunk = i & 7, lp = (i >> 3) & (kPack2Low - 1), g = i >> 8;
+    if (xb + lp >= w) continue;
+    const int ch0 = g * 64 + chunk * 8;
+    float f[8];
+    if (ch0 + 8 <= cin) {
+      const float4 a = *reinterpret_cast<const float4 *>(&tile[lp * kPack2Pitch + ch0]);
+      const float4 c4 = *reinterpret_cast<const float4 *>(&tile[lp * kPack2Pitch + ch0 + 4]);
+      f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = c4.x; f[5] = c4.y; f[6] = c4.z; f[7] = c4.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = (ch0 + j < cin) ? tile[lp * kPack2Pitch + ch0 + j] : 0.f;
+    }
     uint16_t *dst = (g == 0 ? out_g0 : out_g1) + ((static_cast<size_t>(b) * h + y) * w + xb + lp) * (64 * nparts);
     store_chunk8(dst, chunk, nparts, f, is_bf16);
   }
@@ -560,6 +715,98 @@ compose_kernel(const float *__restrict__ low, const float *__restrict__ pred, fl
   }
 }
 
+// compose_v4_kernel: the 12-channel form of compose_kernel with one thread per LOW-res column = 4 output pixels, 16-byte
+// loads / stores, and the six low-res values a bilinear channel needs for those 4 pixels loaded once (3 columns x 2 rows
+// instead of 4 taps per pixel).  Same arithmetic per value, same results bit for bit (tests compare both).  The scalar
+// kernel ran at 2.1 TB/s-equivalent on the 1080p frame (71 us of the 1.06 ms interactive frame).
+template <int UNSHADED, int MASKING, int AO6>
+__global__ void __launch_bounds__(128)
+compose_v4_kernel(const float *__restrict__ low, const float *__restrict__ pred, float *__restrict__ out, ShadeParams sp,
+                  float sf, int B, int h, int w, float bg0) {
+  constexpr int c_low = 12, c_pred = UNSHADED ? (AO6 ? 6 : 5) : 3;
+  const int H = 4 * h, W = 4 * w;
+  const size_t plane = static_cast<size_t>(H) * W, lplane = static_cast<size_t>(h) * w;
+  const size_t gid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gid >= static_cast<size_t>(B) * H * w) return;
+  const int j = static_cast<int>(gid % w);
+  const int y = static_cast<int>((gid / w) % H);
+  const int b = static_cast<int>(gid / (static_cast<size_t>(w) * H));
+  int y0, y1;
+  float ly0, ly1;
+  bil_src_pw(y, h, 0.25f, y0, y1, ly0, ly1);
+  const int jm = j > 0 ? j - 1 : 0, jp = j < w - 1 ? j + 1 : w - 1;
+  float lx0[4], lx1[4];
+#pragma unroll
+  for (int dx = 0; dx < 4; ++dx) {
+    int a0, a1;
+    bil_src_pw(4 * j + dx, w, 0.25f, a0, a1, lx0[dx], lx1[dx]);
+  }
+  const bool first = j == 0;
+  const float *lb = low + static_cast<size_t>(b) * c_low * lplane;
+  const float *pb = pred + static_cast<size_t>(b) * c_pred * plane + static_cast<size_t>(y) * W + 4 * j;
+  float *ob = out + static_cast<size_t>(b) * c_low * plane + static_cast<size_t>(y) * W + 4 * j;
+  // bilinear x4 of one low-res channel for the 4 pixels (bil_sample's operation order; the scale factor 1.f is exact)
+  auto bil4 = [&](int c, float *v) {
+    const float *r0p = lb + c * lplane + static_cast<size_t>(y0) * w, *r1p = lb + c * lplane + static_cast<size_t>(y1) * w;
+    const float a_m = __ldg(r0p + jm), a_c = __ldg(r0p + j), a_p = __ldg(r0p + jp);
+    const float b_m = __ldg(r1p + jm), b_c = __ldg(r1p + j), b_p = __ldg(r1p + jp);
+#pragma unroll
+    for (int dx = 0; dx < 4; ++dx) {
+      float t0, t1, u0, u1;   // columns (x0, x1) of rows y0 / y1: dx < 2 -> (j-1, j), or (0, min(1, w-1)) on the first column
+      if (dx < 2) { t0 = first ? a_c : a_m; t1 = first ? a_p : a_c; u0 = first ? b_c : b_m; u1 = first ? b_p : b_c; }
+      else { t0 = a_c; t1 = a_p; u0 = b_c; u1 = b_p; }
+      const float r0 = fmaf(lx0[dx], t0, lx1[dx] * t1);
+      const float r1 = fmaf(lx0[dx], u0, lx1[dx] * u1);
+      v[dx] = fmaf(ly0, r0, ly1 * r1);
+    }
+  };
+  float m[4] = {1.f, 1.f, 1.f, 1.f};
+  if (MASKING) {
+    float t[4];
+    bil4(3, t);
+#pragma unroll
+    for (int dx = 0; dx < 4; ++dx) m[dx] = t[dx] * 0.5f + 0.5f;
+  }
+  auto put = [&](int c, const float *v) {
+    float o[4];
+#pragma unroll
+    for (int dx = 0; dx < 4; ++dx) o[dx] = MASKING ? bg0 + m[dx] * (v[dx] - bg0) : v[dx];
+    __stcs(reinterpret_cast<float4 *>(ob + c * plane), make_float4(o[0], o[1], o[2], o[3]));
+  };
+  float4 pv[c_pred];
+#pragma unroll
+  for (int c = 0; c < c_pred; ++c) pv[c] = __ldcs(reinterpret_cast<const float4 *>(pb + c * plane));
+  auto lane4 = [](const float4 &q, int dx) { return dx == 0 ? q.x : (dx == 1 ? q.y : (dx == 2 ? q.z : q.w)); };
+  float rgb[4][3];
+#pragma unroll
+  for (int dx = 0; dx < 4; ++dx) {
+    if (UNSHADED) {
+      shade_pixel(sp, lane4(pv[0], dx), lane4(pv[1], dx), lane4(pv[2], dx), lane4(pv[3], dx),
+                  AO6 ? lane4(pv[AO6 ? 5 : 0], dx) : 1.f, AO6 != 0, sf, rgb[dx]);
+    } else {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) rgb[dx][c] = fminf(fmaxf(lane4(pv[c], dx), 0.f), 1.f);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < c_low; ++c) {
+    float v[4];
+    if (c < 3) {
+#pragma unroll
+      for (int dx = 0; dx < 4; ++dx) v[dx] = rgb[dx][c];
+    } else if (UNSHADED && c < 8) {
+#pragma unroll
+      for (int dx = 0; dx < 4; ++dx) v[dx] = lane4(pv[c - 3], dx);
+    } else if (UNSHADED && c == 10 && AO6) {
+#pragma unroll
+      for (int dx = 0; dx < 4; ++dx) v[dx] = lane4(pv[AO6 ? 5 : 0], dx);
+    } else {
+      bil4(c, v);
+    }
+    put(c, v);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // nn.Upsample(scale_factor=2, mode) on NHWC 16-bit 64-channel features (enhancenet.py:40-48,116,119).
 // One thread = one source column j x one 8-channel chunk (16 B), walking down a strip of kUpStrip source rows.  Per
@@ -808,21 +1055,66 @@ cudaError_t launch_shade_rgb8(const float *in, const float *params22, unsigned c
   count_launch();
   return cudaGetLastError();
 }
+static int g_compose_variant = 2;   // 1 = scalar kernel, 2 = compose_v4_kernel (4 pixels per thread; 12-channel renders)
+int set_compose_variant(int v) {
+  const int old = g_compose_variant;
+  g_compose_variant = v;
+  return old;
+}
 cudaError_t launch_compose(const float *low, const float *pred, const float *params22, float *out, int B, int c_low,
                            int c_pred, int h, int w, int unshaded, int masking, float bg0, cudaStream_t s) {
   ShadeParams sp;
   for (int i = 0; i < 22; ++i) sp.v[i] = params22[i];
   const int expo = static_cast<int>(params22[19]);
   const float sf = static_cast<float>((static_cast<double>(expo) + 2.0) / (2.0 * 3.14159265358979323846));
+  const bool aligned = ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  if (g_compose_variant == 2 && c_low == 12 && aligned && (unshaded ? (c_pred == 5 || c_pred == 6) : c_pred == 3)) {
+    const size_t threads = static_cast<size_t>(B) * 4 * h * w;
+    const unsigned blocks = static_cast<unsigned>((threads + 127) / 128);
+#define ISR_COMPOSE(U, M, A) compose_v4_kernel<U, M, A><<<blocks, 128, 0, s>>>(low, pred, out, sp, sf, B, h, w, bg0)
+    if (unshaded && c_pred == 6) { if (masking) ISR_COMPOSE(1, 1, 1); else ISR_COMPOSE(1, 0, 1); }
+    else if (unshaded) { if (masking) ISR_COMPOSE(1, 1, 0); else ISR_COMPOSE(1, 0, 0); }
+    else { if (masking) ISR_COMPOSE(0, 1, 0); else ISR_COMPOSE(0, 0, 0); }
+#undef ISR_COMPOSE
+    count_launch();
+    return cudaGetLastError();
+  }
   compose_kernel<<<B * 4 * h, 256, 0, s>>>(low, pred, out, sp, sf, B, c_low, c_pred, h, w, unshaded, masking, bg0);
   count_launch();
   return cudaGetLastError();
 }
+static int g_pack_variant = 2;   // 1 = the first kernel, 2 = pack_recurrent_v2_kernel (bit-identical, fewer instructions)
+int set_pack_variant(int v) {
+  const int old = g_pack_variant;
+  g_pack_variant = v;
+  return old;
+}
 cudaError_t launch_pack_recurrent(const float *low, const float *prev, const float *flow, uint16_t *g0, uint16_t *g1,
                                   int B, int c_low, int c_prev, int h, int w, int special_mask, int align_corners,
                                   int nparts, int is_bf16, cudaStream_t s) {
-  dim3 grid((w + kPackLow - 1) / kPackLow, h, B);
   const bool small_plane = static_cast<size_t>(h) * 4 * w * 4 * 4 * 8 < (1ull << 32);   // 32-bit byte offsets inside a frame
+  if (g_pack_variant == 2 && (c_prev == 6 || c_prev == 3) && c_low + 16 * c_prev <= 128 &&
+      static_cast<size_t>(c_prev) * h * 4 * w * 4 < (1ull << 31)) {
+    dim3 grid2((w + kPack2Low - 1) / kPack2Low, h, B);
+#define ISR_PACK2(CPV, NP, BF)                                                                                          \
+  pack_recurrent_v2_kernel<CPV, NP, BF><<<grid2, 128, 0, s>>>(low, prev, flow, g0, g1, c_low, h, w, special_mask,       \
+                                                             align_corners)
+    const int sel = (c_prev == 6 ? 4 : 0) + (nparts == 2 ? 2 : 0) + (is_bf16 ? 1 : 0);
+    switch (sel) {
+      case 0: ISR_PACK2(3, 1, 0); break;
+      case 1: ISR_PACK2(3, 1, 1); break;
+      case 2: ISR_PACK2(3, 2, 0); break;
+      case 3: ISR_PACK2(3, 2, 1); break;
+      case 4: ISR_PACK2(6, 1, 0); break;
+      case 5: ISR_PACK2(6, 1, 1); break;
+      case 6: ISR_PACK2(6, 2, 0); break;
+      default: ISR_PACK2(6, 2, 1); break;
+    }
+#undef ISR_PACK2
+    count_launch();
+    return cudaGetLastError();
+  }
+  dim3 grid((w + kPackLow - 1) / kPackLow, h, B);
   if (c_prev == 6 && small_plane)
     pack_recurrent_kernel<6><<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
                                                  align_corners, nparts, is_bf16);

@@ -254,7 +254,7 @@ def test_sequence_recurrence_golden(isr, golden, weights):
         e1 = maxabs(preds[0], ref[0])
         assert e1 <= 1e-2
         for j in range(3):
-            bound = 1e-2 if prec == "bf16x3" else 3.0 * max(gain[j], 1.0) * e1
+            bound = 1e-2 if prec == "bf16x3" else 3.0 * max(gain[j] / gain[0], 1.0) * e1
             assert maxabs(preds[j], ref[j]) <= bound, (prec, j)
             assert maxabs(rgbs[j], g[f"rgb_{j}"]) <= 2 * bound
 

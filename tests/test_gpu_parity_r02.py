@@ -113,30 +113,31 @@ def _amplification(weights, low, flow, ref, eps=1e-4, seed=0):
 
 
 def test_sequence_unshaded_10_frames_free_running(isr, golden, weights):
-    """Free-running over 10 frames the random-init network amplifies ANY per-frame difference (measured here on the fp32
-    oracle itself, and for stock torch-CUDA fp32 against torch-CPU fp32 in profiles/r02_recurrence_drift.json): the bound
-    of frame j is therefore not a constant but  k * gain[j] * (the scheme's own per-frame error e1),  gain[j] = measured
-    amplification of a per-frame input perturbation by the oracle's feedback loop, k = 3 (the perturbation enters at the
-    input, rounding enters at every layer).  No implementation of the recurrence -- the reference's own CUDA path
-    included -- can stay within a fixed 1e-2 of the CPU result for an expanding loop."""
+    """Free-running over 10 frames the random-init network EXPANDS any per-frame difference.  The noise floor is measured
+    right here: the reference's own arithmetic on CUDA (stock torch / cuDNN fp32, TF32 off) against the same arithmetic
+    on the CPU drifts from 1.4e-5 at frame 0 to 3e-4 at frame 9 on this 16x24 fixture, and from 2.5e-5 to 1.1e-2 -- past
+    the 1e-2 bar -- on 256x256 crops (profiles/r02_recurrence_drift.json).  A fixed bound on a free-running frame is
+    therefore meaningless; what an implementation can be held to is that its deviation grows no faster than the
+    reference's own:   err[j] <= k * growth[j] * err[0],   growth[j] = max(torch-CUDA drift[j] / drift[0], amplification
+    of a per-frame input perturbation by the fp32 CPU oracle[j] / [0]),  k = 3,  err[0] = the scheme's single-frame error
+    (frame 0 has no feedback), itself held to the 1e-2 bar."""
     g = golden("sequence_unshaded_10")
     ref = [g[f"pred_{j}"] for j in range(10)]
     gain = _amplification(weights, g["low"], g["flow"], ref)
-    # the reference's own arithmetic on CUDA (TF32 off) as the noise floor
     cuda_ref = orc.unshaded_sequence_torch(weights, g["low"], g["flow"], "cuda")
     floor = [maxabs(cuda_ref[j], ref[j]) for j in range(10)]
+    assert 0 < floor[0] <= 1e-4                        # the two back ends of the reference differ already at frame 0
+    growth = [max(floor[j] / floor[0], gain[j] / gain[0], 1.0) for j in range(10)]
     net = _net(isr, weights)
     K = 3.0
     for prec in ("hybrid", "bf16x3"):
         net.precision = prec
         preds, _, _ = isr.SequenceRunner(net, initial_image="input").run(cu(g["low"]), cu(g["flow"]))
         err = [maxabs(preds[j], ref[j]) for j in range(10)]
-        e1 = err[0]                                    # frame 0 has no feedback: the scheme's single-frame error
-        assert e1 <= 1e-2
+        assert err[0] <= 1e-2
         for j in range(10):
-            assert err[j] <= K * max(gain[j], 1.0) * e1 + 10 * floor[j], (prec, j, err, gain, floor)
-        # and it must not be WORSE than the expansion explains: bf16x3 stays inside the fixed bar over all ten frames
-        if prec == "bf16x3":
+            assert err[j] <= K * growth[j] * err[0], (prec, j, err, growth)
+        if prec == "bf16x3":                           # on this fixture the split scheme stays inside the fixed bar
             assert max(err) <= 1e-2, err
 
 
@@ -358,3 +359,56 @@ def test_inpaint_flow_bound_against_opencv(isr):
         # both extrapolate the field into the hole; against the TRUE smooth field neither is far off
         assert float(np.abs(out - f)[inside].mean()) / rng_f <= 0.25
     assert worst_mean <= 0.15 and worst_max <= 0.8, (worst_mean, worst_max)
+
+
+# ---- round-2 kernel variants: bit-identical to the first forms ------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(2, 24, 40), (1, 19, 27), (1, 33, 130), (1, 270, 480)])
+@pytest.mark.parametrize("c_prev", [6, 3])
+def test_pack_recurrent_v2_equals_v1(isr, weights, shape, c_prev):
+    """pack_recurrent_v2_kernel (one thread per high-res column, flow rows shared by the 4 rows of a low-res row) writes
+    the same network operand as the first kernel, bit for bit: the network output is compared (all planes feed it), for
+    the unshaded (special mask) and the shaded (3-channel) form, on ragged widths, with flows that leave the image."""
+    B, h, w = shape
+    if c_prev == 6:
+        net, c_low, sm = _net(isr, weights), 5, True
+    else:
+        torch.manual_seed(1234)
+        net, c_low, sm = _net(isr, None, cin=56, cout=3, mask=(0, 1, 2)), 8, False
+    g = torch.Generator(device="cuda").manual_seed(h * 100 + w)
+    low = torch.rand(B, c_low, h, w, device="cuda", generator=g) * 2 - 1
+    prev = torch.rand(B, c_prev, 4 * h, 4 * w, device="cuda", generator=g) * 2 - 1
+    flow = (torch.rand(B, 2, h, w, device="cuda", generator=g) - 0.5) * 0.08
+    flow[:, :, : h // 3] *= 20                                # far outside the image: zero / -1 padding taps
+    outs = {}
+    try:
+        for variant in (1, 2):
+            isr._lib.set_tunable("pack_variant", variant)
+            with torch.no_grad():
+                outs[variant] = [net(low, prev, flow, special_mask=sm)[0].clone(), net(low, prev, None)[0].clone()]
+    finally:
+        isr._lib.set_tunable("pack_variant", 2)
+    assert torch.equal(outs[1][0], outs[2][0]) and torch.equal(outs[1][1], outs[2][1])
+    assert torch.isfinite(outs[2][0]).all()
+
+
+@pytest.mark.parametrize("masking", [False, True])
+@pytest.mark.parametrize("shape", [(1, 54, 96), (2, 19, 27), (1, 270, 480)])
+def test_compose_v4_equals_scalar(isr, masking, shape):
+    """compose_v4_kernel (4 output pixels per thread, 16-byte accesses) against the scalar kernel: bit-identical, for the
+    unshaded 6- and 5-channel state and the shaded RGB form."""
+    from test_gpu_parity import _shading_from_params
+    B, h, w = shape
+    g = torch.Generator(device="cuda").manual_seed(h + w)
+    img = torch.rand(B, 12, h, w, device="cuda", generator=g) * 2 - 1
+    shd = _shading_from_params(isr, orc.shading_params(material=(1.0, 0.3, 0.0), ao_strength=0.5, background=(0.2, 0.3, 0.4)))
+    preds = [torch.rand(B, c, 4 * h, 4 * w, device="cuda", generator=g) * 2.4 - 1.2 for c in (6, 5, 3)]
+    outs = {}
+    try:
+        for variant in (1, 2):
+            isr._lib.set_tunable("compose_variant", variant)
+            outs[variant] = [isr.compose_frame(img, p, shd if p.shape[1] >= 5 else None, masking=masking,
+                                               background=(0.2, 0.3, 0.4)).clone() for p in preds]
+    finally:
+        isr._lib.set_tunable("compose_variant", 2)
+    for a, b in zip(outs[1], outs[2]):
+        assert torch.equal(a, b)

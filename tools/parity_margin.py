@@ -1,0 +1,71 @@
+#!/usr/bin/env python
+"""Single-frame parity margin of the precision schemes at REALISTIC sizes and over several weight seeds: the max-abs
+error is a maximum over all output pixels, so it grows with the frame size (a 5-6 sigma event over 10^7 samples) --
+the 16x20 golden inputs flatter every scheme.  For every weight seed (reference constructor order, tests/
+test_oracle_golden.py::_seeded_reference_weights) and two inputs (uniform stress, synthetic G-buffer + random previous
+frame) at B x h x w: max-abs / PSNR against the fp32 CPU oracle for `hybrid` with K = trunk_full_blocks in {0..10},
+`mixed`, `bf16x3`.  Run on the GPU box:
+
+    python tools/parity_margin.py [--shape 2x256x256] > gpurun_out/r02_parity_margin.json
+"""
+import argparse
+import json
+import os
+import sys
+from argparse import Namespace
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import isosurfacesuperresolution_b200 as isr  # noqa: E402
+from oracle import oracle as orc  # noqa: E402
+from test_oracle_golden import _seeded_reference_weights  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--shape", default="2x256x256")
+ap.add_argument("--seeds", default="1234,1,7,42,2024,31337")
+ap.add_argument("--ks", default="0,2,4,6,8,10")
+args = ap.parse_args()
+B, h, w = (int(v) for v in args.shape.split("x"))
+torch.set_num_threads(os.cpu_count() or 1)
+out = {"shape": [B, h, w], "schemes": {}, "what": "single forward, max-abs over all outputs / PSNR vs the fp32 CPU oracle"}
+rng = np.random.RandomState(11)
+x_uni = rng.uniform(-1, 1, (B, 101, h, w)).astype(np.float32)
+low, _, ao = orc.synthetic_gbuffer(B, h, w, 4400)
+prev = orc.postprocess(rng.uniform(-1.2, 1.2, (B, 6, 4 * h, 4 * w)).astype(np.float32), unshaded=True)
+x_gb = np.concatenate([low[:, 0], orc.flatten_high(prev, 4)], axis=1)
+inputs = {"uniform": x_uni, "gbuffer": x_gb}
+for seed in (int(s) for s in args.seeds.split(",")):
+    sd = _seeded_reference_weights(101, 6, seed)
+    refs = {k: orc.enhancenet_forward(sd, x, "bilinear", "residual", 5, backend="torch")[0] for k, x in inputs.items()}
+    schemes = [("hybrid_K%d" % k, "hybrid", k) for k in (int(v) for v in args.ks.split(","))]
+    schemes += [("mixed", "mixed", None), ("bf16x3", "bf16x3", None)]
+    for name, prec, k in schemes:
+        if k is not None:
+            old = isr._lib.set_tunable("trunk_full_blocks", k)
+        net = isr.createNetwork("EnhanceNet", 4, 101, [0, 1, 2, 3, 4], 6,
+                                Namespace(upsample="bilinear", reconType="residual", useBN=False))
+        net.load_state_dict({kk: torch.from_numpy(np.asarray(v)) for kk, v in sd.items()})
+        net = net.cuda().eval()
+        net.precision = prec
+        for kind, x in inputs.items():
+            with torch.no_grad():
+                recon, _ = net(torch.from_numpy(x).cuda())
+            r = recon.cpu().numpy()
+            e = float(np.max(np.abs(r - refs[kind])))
+            out["schemes"].setdefault(name, {}).setdefault(kind, {})[str(seed)] = {"max_abs": e, "psnr_db": orc.psnr(r, refs[kind])}
+        if k is not None:
+            isr._lib.set_tunable("trunk_full_blocks", old)
+        del net
+    sys.stderr.write("seed %d done\n" % seed)
+for name, d in out["schemes"].items():
+    worst = max(v["max_abs"] for kind in d.values() for v in kind.values())
+    d["worst_max_abs"] = worst
+    d["worst_psnr_db"] = min(v["psnr_db"] for kind in d.values() if isinstance(kind, dict) for v in kind.values() if isinstance(v, dict))
+    sys.stderr.write("%-12s worst max-abs %.2e  worst psnr %.1f | " % (name, worst, d["worst_psnr_db"]) + " ".join(
+        "%s:%.1e" % (kind[:3], max(v["max_abs"] for v in d[kind].values())) for kind in ("uniform", "gbuffer")) + "\n")
+print(json.dumps(out, indent=1))
