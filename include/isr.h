@@ -294,7 +294,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "stack_w" (0 | [1])              hi/lo weight planes as one N=128 B operand
  *   "pdl" (0 | [1])                  programmatic dependent launch between consecutive convs
  *   "fuse_up" (0 | [1])              bilinear 2x upsample fused into the following conv (four phase convolutions)
- *   "trunk_full_blocks" (0..10, [4]) residual blocks of ISR_PREC_HYBRID that run fully split
+ *   "trunk_full_blocks" (0..10, [10]) residual blocks of ISR_PREC_HYBRID that run fully split (4 is 11 % faster per
+ *                                    step and misses the 1e-2 bar at full frame sizes: profiles/r02_parity_margin.json)
  *   "final_stacked" (0 | [1] | 2)    output conv: generic / tap-stacked / CTA-pair N=16
  *   "final_issuers" (1 | [3])        MMA-issuing warps of the tap-stacked output conv
  *   "final_w_parts" ([0] = scheme | 1 | 2)   weight planes of the output conv

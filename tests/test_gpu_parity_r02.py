@@ -225,7 +225,7 @@ def test_tunables_are_per_handle(isr, golden, weights):
         a._native().set_tunable("final_w_parts", 0)
         assert torch.equal(a(x)[0], ra0)
         # process defaults: existing handles keep their snapshot, new handles see the change
-        prev = isr._lib.set_tunable("trunk_full_blocks", 10)
+        prev = isr._lib.set_tunable("trunk_full_blocks", 4)
         try:
             assert torch.equal(b(x)[0], rb0)
             c = _net(isr, weights)

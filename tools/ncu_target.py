@@ -22,7 +22,11 @@ ap.add_argument("--shape", default="4x512x512")
 ap.add_argument("--frames", type=int, default=3)
 ap.add_argument("--precision", default="hybrid")
 ap.add_argument("--compose", action="store_true")
+ap.add_argument("--tunable", action="append", default=[], help="key=value, process-wide tunable set before the net is built")
 args = ap.parse_args()
+for kv in args.tunable:
+    k, v = kv.split("=")
+    isr._lib.set_tunable(k, int(v))
 B, h, w = (int(v) for v in args.shape.split("x"))
 weights = dict(np.load(os.path.join(ROOT, "tests", "golden", "enhancenet_weights_unshaded_seed1234.npz")))
 net = isr.createNetwork("EnhanceNet", 4, 101, [0, 1, 2, 3, 4], 6, Namespace(upsample="bilinear", reconType="residual", useBN=False))
