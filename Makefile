@@ -7,7 +7,7 @@ NVFLAGS = $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xptxas -v
 LIB = $(PKG)/libisr.so
 
 all: $(LIB) oracle
-$(CSRC)/isr_api.o: $(CSRC)/isr_api.cu $(CSRC)/isr_conv.cuh $(CSRC)/isr_conv_final.cuh $(CSRC)/isr_conv_pair.cuh $(CSRC)/isr_ptx.cuh $(CSRC)/isr_internal.h include/isr.h
+$(CSRC)/isr_api.o: $(CSRC)/isr_api.cu $(CSRC)/isr_conv.cuh $(CSRC)/isr_conv_final.cuh $(CSRC)/isr_conv_final2.cuh $(CSRC)/isr_conv_pair.cuh $(CSRC)/isr_ptx.cuh $(CSRC)/isr_internal.h include/isr.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(CSRC)/isr_pointwise.o: $(CSRC)/isr_pointwise.cu $(CSRC)/isr_internal.h
 	$(NVCC) $(NVFLAGS) -fmad=false -c $< -o $@

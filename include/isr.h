@@ -296,7 +296,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "fuse_up" (0 | [1])              bilinear 2x upsample fused into the following conv (four phase convolutions)
  *   "trunk_full_blocks" (0..10, [10]) residual blocks of ISR_PREC_HYBRID that run fully split (4 is 11 % faster per
  *                                    step and misses the 1e-2 bar at full frame sizes: profiles/r02_parity_margin.json)
- *   "final_stacked" (0 | [1] | 2)    output conv: generic / tap-stacked / CTA-pair N=16
+ *   "final_stacked" (0 | 1 | 2 | [3]) output conv: generic / tap-stacked (shared-memory gather) / CTA-pair N=16 /
+ *                                    column-stacked with a register gather (isr_conv_final2.cuh)
  *   "final_issuers" (1 | [3])        MMA-issuing warps of the tap-stacked output conv
  *   "final_w_parts" ([0] = scheme | 1 | 2)   weight planes of the output conv
  *   "raycast_two_pass" (0 | [1] = from 8 AO rays on | 2)   ambient occlusion of the ray-caster as a second pass

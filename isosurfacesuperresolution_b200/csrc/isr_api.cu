@@ -17,6 +17,7 @@
 #include "../../include/isr.h"
 #include "isr_conv.cuh"
 #include "isr_conv_final.cuh"
+#include "isr_conv_final2.cuh"
 #include "isr_conv_pair.cuh"
 #include "isr_internal.h"
 
@@ -33,12 +34,14 @@ struct Tunables {
   int max_ctas = 0;
   int dbg = 0;             // ConvParams::dbg of isr_net_time_conv launches (bench experiments)
   int cta_pair = 1;        // 64-wide convs: CTA-pair kernel (tcgen05 cta_group::2, isr_conv_pair.cuh)
-  int final_stacked = 1;   // output conv: 2 = CTA-pair N=16 kernel (measured slower: 1.24 vs 0.92 ms), 1 = tap-stacked kernel
-                           // (isr_conv_final.cuh, Cout <= 8), 0 = generic single-CTA N=16 kernel
+  int final_stacked = 3;   // output conv (Cout <= 8): 3 = column-stacked kernel with the register gather (isr_conv_final2.cuh),
+                           // 1 = tap-stacked kernel with the shared-memory gather (isr_conv_final.cuh), 2 = CTA-pair N=16
+                           // kernel (measured slower: 1.24 vs 0.92 ms), 0 = generic single-CTA N=16 kernel
   int stack_w = 1;         // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
   int fuse_up = 1;         // bilinear nets: upsample + conv run as one phase-decomposed kernel (isr_up2.cu)
   int final_w_parts = 0;   // output conv weight planes: 0 = the scheme's choice, 1 = single, 2 = hi + lo
   int final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
+  int final_groups = 3;    // column-stacked output conv: epilogue groups (3 | 4)
   int pdl = 1;             // CTA-pair convs are launched with programmatic stream serialization
   int trunk_full_blocks = 10;  // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3).  10 = the whole
                                // trunk: at realistic frame sizes K = 4 does NOT keep the 1e-2 bar (1.04e-2 on frame 0 of a
@@ -122,6 +125,8 @@ struct ConvLaunch {
   ConvParams p;
   int n;  // 64 (EPI_STORE16) or 16 (EPI_FINAL)
   int cp = 0;  // > 0: tap-stacked output conv (conv3x3_final_kernel<cp>)
+  int final2 = 0;  // 1: column-stacked output conv (conv3x3_final2_kernel<cp>)
+  int groups = 3;  // conv3x3_final2_kernel: epilogue groups (= accumulator buffers = MMA-issuing warps), 3 | 4
   int pair = 0;  // 1: CTA-pair kernel (conv3x3_pair_kernel)
   int ph = 1;    // 4: fused upsample + conv (four output phases per low-res tile)
   int stack = 0; // split weights stacked as one N=128 operand
@@ -173,6 +178,13 @@ static int setup_kernel_attrs() {
   ISR_CUDA(set_max_smem(conv3x3_final_kernel<4>));
   ISR_CUDA(set_max_smem(conv3x3_final_kernel<6>));
   ISR_CUDA(set_max_smem(conv3x3_final_kernel<8>));
+  ISR_CUDA(set_max_smem((conv3x3_final2_kernel<4, 0, 3>)));
+  ISR_CUDA(set_max_smem((conv3x3_final2_kernel<6, 0, 3>)));
+  ISR_CUDA(set_max_smem((conv3x3_final2_kernel<8, 0, 3>)));
+  ISR_CUDA(set_max_smem((conv3x3_final2_kernel<4, 1, 3>)));
+  ISR_CUDA(set_max_smem((conv3x3_final2_kernel<6, 1, 3>)));
+  ISR_CUDA(set_max_smem((conv3x3_final2_kernel<4, 1, 4>)));
+  ISR_CUDA(set_max_smem((conv3x3_final2_kernel<6, 1, 4>)));
   done[dev] = true;
   return ISR_OK;
 }
@@ -194,6 +206,7 @@ static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act,
   p.is_bf16 = is_bf16;
   p.w_row0 = w_row0;
   p.w_row_stride = w_row_stride;
+  L->final2 = 0;
   L->pair = ((n == 64 && tun.cta_pair) || (n == 16 && tun.final_stacked == 2)) ? 1 : 0;
   const bool stack = n_w_parts == 2 && tun.stack_w;
   L->stack = stack ? 1 : 0;
@@ -230,7 +243,7 @@ static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act,
 static int init_conv_up2(const Tunables &tun, ConvLaunch *L, const void *act, int B, int hl, int wl, int tensor_parts,
                          const void *wpacked, int is_bf16) {
   memset(&L->p, 0, sizeof L->p);
-  L->n = 64; L->cp = 0; L->pair = 1; L->ph = 4; L->stack = 0; L->pdl = tun.pdl;
+  L->n = 64; L->cp = 0; L->final2 = 0; L->pair = 1; L->ph = 4; L->stack = 0; L->pdl = tun.pdl;
   ConvParams &p = L->p;
   p.B = B; p.H = hl; p.W = wl;
   p.tiles_x = (wl + kTileW - 1) / kTileW;
@@ -269,6 +282,7 @@ static int init_conv_final(const Tunables &tun, ConvLaunch *L, int cp, const voi
   const int nrows = final_rows(cp);
   L->n = nrows;
   L->cp = cp;
+  L->final2 = 0;
   L->pair = 0; L->ph = 1; L->stack = 0; L->pdl = tun.pdl;
   ConvParams &p = L->p;
   p.B = B; p.H = H; p.W = W;
@@ -300,7 +314,69 @@ static int init_conv_final(const Tunables &tun, ConvLaunch *L, int cp, const voi
   return make_w_map(&L->tmW, wpacked, 2 * nrows, nrows, is_bf16);
 }
 
+static int final2_nk(int cp) { return (3 * cp + 15) / 16 * 16; }
+
+// column-stacked output conv (isr_conv_final2.cuh): wpacked = [ky 3][part 2][nk][64] of the chosen format
+static int init_conv_final2(const Tunables &tun, ConvLaunch *L, int cp, const void *act, int B, int H, int W,
+                            int n_act_parts, const void *wpacked, int n_w_parts, int is_bf16) {
+  memset(&L->p, 0, sizeof L->p);
+  const int nk = final2_nk(cp);
+  L->n = nk;
+  L->cp = cp;
+  L->final2 = 1;
+  // four groups only exist for the specialised epilogues (the generic one needs more than the 96 registers 21 warps leave)
+  L->groups = (tun.final_groups == 4 && (cp == 6 || cp == 4)) ? 4 : 3;
+  L->pair = 0; L->ph = 1; L->stack = 0; L->pdl = tun.pdl;
+  ConvParams &p = L->p;
+  p.B = B; p.H = H; p.W = W;
+  p.tiles_x = (W + kGTileW - 1) / kGTileW;
+  p.tiles_y = (H + kGTileH - 1) / kGTileH;
+  p.num_tiles = p.tiles_x * p.tiles_y * B;
+  p.n_act_parts = n_act_parts;
+  p.n_w_parts = n_w_parts;
+  p.is_bf16 = is_bf16;
+  p.w_row0 = 0;
+  p.w_row_stride = nk;
+  const size_t w_bytes = align_up(static_cast<size_t>(3) * n_w_parts * nk * 128, 1024);
+  p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kGStageRows) * 128, 1024));
+  const size_t fixed = 1024 + w_bytes + kG2MaxGroups * 2 * kGScratch + 256;
+  int stages = static_cast<int>((kSmemLimit - kStaticSmem - fixed) / p.stage_bytes);
+  if (stages > 8) stages = 8;
+  if (stages < 2) return fail(ISR_ERR_UNSUPPORTED, "final2 conv smem plan: fewer than 2 halo stages fit");
+  p.issuers = 1;
+  if (tun.final_issuers == 3 && stages >= L->groups * n_act_parts) {   // one issuing warp per accumulator buffer
+    stages -= stages % (L->groups * n_act_parts);
+    p.issuers = L->groups;
+  }
+  p.num_stages = stages;
+  L->smem = fixed + static_cast<size_t>(stages) * p.stage_bytes;
+  int cap = tun.max_ctas > 0 ? tun.max_ctas : num_sms();
+  L->grid = p.num_tiles < cap ? p.num_tiles : cap;
+  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * n_act_parts, kGPitch, kGHaloH, is_bf16);
+  if (rc != ISR_OK) return rc;
+  return make_w_map(&L->tmW, wpacked, 3 * 2 * nk, nk, is_bf16);
+}
+
 static int run_conv(const ConvLaunch &L, cudaStream_t s) {
+  if (L.final2) {
+    // the compile-time specialised epilogues: the unshaded (6 / 5 / normalise state) and the shaded (3 / 3 / clamp) network
+    const ConvParams &q = L.p;
+    const bool fast6 = L.cp == 6 && q.cout == 6 && q.n_mask == 5 && q.recon_residual && q.out_raw == nullptr &&
+                       (q.out_state == nullptr || q.state_unshaded);
+    const bool fast4 = L.cp == 4 && q.cout == 3 && q.n_mask == 3 && q.recon_residual && q.out_raw == nullptr &&
+                       (q.out_state == nullptr || !q.state_unshaded);
+    const int thr = g2_threads(L.groups);
+    if (fast6 && L.groups == 4) conv3x3_final2_kernel<6, 1, 4><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else if (fast4 && L.groups == 4) conv3x3_final2_kernel<4, 1, 4><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else if (fast6) conv3x3_final2_kernel<6, 1, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else if (fast4) conv3x3_final2_kernel<4, 1, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else if (L.cp == 4) conv3x3_final2_kernel<4, 0, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else if (L.cp == 6) conv3x3_final2_kernel<6, 0, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    else conv3x3_final2_kernel<8, 0, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    count_launch();
+    ISR_CUDA(cudaGetLastError());
+    return ISR_OK;
+  }
   if (L.cp > 0) {
     if (L.cp == 4) conv3x3_final_kernel<4><<<L.grid, kFinalThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
     else if (L.cp == 6) conv3x3_final_kernel<6><<<L.grid, kFinalThreads, L.smem, s>>>(L.tmA, L.tmW, L.p);
@@ -375,6 +451,7 @@ struct Layer {
   uint16_t *packed = nullptr;  // [fmt 2][part 2][tap 9][G][npad][64]
   float *bias = nullptr;       // npad floats, zero padded
   uint16_t *packed_fin = nullptr;  // output conv only: tap-stacked [fmt 2][part 2][nrows][64]
+  uint16_t *packed_fin2 = nullptr; // output conv only: column-stacked [fmt 2][ky 3][part 2][nk][64] (isr_conv_final2.cuh)
   uint16_t *packed_up = nullptr;   // layers 21, 22: composite weights of the fused upsample + conv [fmt 2][phase 4][tap 9][64][64]
   size_t per_fmt() const { return static_cast<size_t>(2) * 9 * G * npad * 64; }
   int rows() const { return 2 * 9 * G * npad; }
@@ -558,7 +635,11 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   Scheme Fs = Hs;
   if (pl->fin_nw > 0) Fs.nw = pl->fin_nw;
   if (tun.final_w_parts > 0) Fs.nw = tun.final_w_parts;
-  if (net->layers[24].packed_fin != nullptr && tun.final_stacked == 1) {
+  if (net->layers[24].packed_fin2 != nullptr && tun.final_stacked == 3) {
+    const int cp = final_cp(net->cout), nk = final2_nk(cp);
+    const uint16_t *wb = net->layers[24].packed_fin2 + (Fs.bf16 ? 0 : static_cast<size_t>(3) * 2 * nk * 64);
+    if ((rc = init_conv_final2(tun, &L, cp, pl->u4, B, 4 * h, 4 * w, Fs.na, wb, Fs.nw, Fs.bf16)) != ISR_OK) return rc;
+  } else if (net->layers[24].packed_fin != nullptr && (tun.final_stacked == 1 || tun.final_stacked == 3)) {
     const int cp = final_cp(net->cout), nrows = final_rows(cp);
     const uint16_t *wb = net->layers[24].packed_fin + (Fs.bf16 ? 0 : static_cast<size_t>(2) * nrows * 64);
     if ((rc = init_conv_final(tun, &L, cp, pl->u4, B, 4 * h, 4 * w, Fs.na, wb, Fs.nw, Fs.bf16)) != ISR_OK) return rc;
@@ -671,11 +752,13 @@ static int *tunable_slot(Tunables *t, const char *key, int value) {
   if (strcmp(key, "dbg") == 0) return &t->dbg;
   if (strcmp(key, "cta_pair") == 0) return (value == 0 || value == 1) ? &t->cta_pair : bad("cta_pair must be 0 or 1");
   if (strcmp(key, "final_stacked") == 0)
-    return (value >= 0 && value <= 2) ? &t->final_stacked : bad("final_stacked must be 0 (generic), 1 (tap-stacked) or 2 (CTA pair)");
+    return (value >= 0 && value <= 3) ? &t->final_stacked
+                                      : bad("final_stacked must be 0 (generic), 1 (tap-stacked), 2 (CTA pair) or 3 (column-stacked)");
   if (strcmp(key, "trunk_full_blocks") == 0)
     return (value >= 0 && value <= 10) ? &t->trunk_full_blocks : bad("trunk_full_blocks must be in [0, 10]");
   if (strcmp(key, "fuse_up") == 0) return (value == 0 || value == 1) ? &t->fuse_up : bad("fuse_up must be 0 or 1");
   if (strcmp(key, "final_issuers") == 0) return (value == 1 || value == 3) ? &t->final_issuers : bad("final_issuers must be 1 or 3");
+  if (strcmp(key, "final_groups") == 0) return (value == 3 || value == 4) ? &t->final_groups : bad("final_groups must be 3 or 4");
   if (strcmp(key, "final_w_parts") == 0)
     return (value >= 0 && value <= 2) ? &t->final_w_parts : bad("final_w_parts must be 0 (scheme), 1 or 2");
   if (strcmp(key, "pdl") == 0) return (value == 0 || value == 1) ? &t->pdl : bad("pdl must be 0 or 1");
@@ -1042,7 +1125,9 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
     }
   if (output_channels <= 8) {
     const int nrows = final_rows(final_cp(output_channels));
-    if (cudaMalloc(&net->layers[24].packed_fin, static_cast<size_t>(4) * nrows * 64 * sizeof(uint16_t)) != cudaSuccess) {
+    const int nk = final2_nk(final_cp(output_channels));
+    if (cudaMalloc(&net->layers[24].packed_fin, static_cast<size_t>(4) * nrows * 64 * sizeof(uint16_t)) != cudaSuccess ||
+        cudaMalloc(&net->layers[24].packed_fin2, static_cast<size_t>(2) * 3 * 2 * nk * 64 * sizeof(uint16_t)) != cudaSuccess) {
       isr_net_destroy(net);
       return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
     }
@@ -1058,6 +1143,7 @@ void isr_net_destroy(isr_net *net) {
     if (net->layers[i].packed) cudaFree(net->layers[i].packed);
     if (net->layers[i].bias) cudaFree(net->layers[i].bias);
     if (net->layers[i].packed_fin) cudaFree(net->layers[i].packed_fin);
+    if (net->layers[i].packed_fin2) cudaFree(net->layers[i].packed_fin2);
     if (net->layers[i].packed_up) cudaFree(net->layers[i].packed_up);
   }
   delete net;
@@ -1074,6 +1160,9 @@ int isr_net_load_weights(isr_net *net, const float *const *params, int n_params,
     if (ly.packed_fin != nullptr)
       ISR_CUDA(launch_pack_weights_final(params[2 * i], ly.packed_fin, ly.cout, final_cp(ly.cout),
                                          final_rows(final_cp(ly.cout)), S(stream)));
+    if (ly.packed_fin2 != nullptr)
+      ISR_CUDA(launch_pack_weights_final2(params[2 * i], ly.packed_fin2, ly.cout, final_cp(ly.cout),
+                                          final2_nk(final_cp(ly.cout)), S(stream)));
     ISR_CUDA(cudaMemsetAsync(ly.bias, 0, 64 * sizeof(float), S(stream)));
     ISR_CUDA(cudaMemcpyAsync(ly.bias, params[2 * i + 1], ly.cout * sizeof(float), cudaMemcpyDeviceToDevice, S(stream)));
   }

@@ -1,0 +1,350 @@
+// isr_conv_final2.cuh -- the network's output convolution (64 -> Cout <= 8, 3x3, pad 1) with its fused epilogue
+// (/root/reference/SuperresolutionNetwork/models/enhancenet.py:124 postblock[8], :51-90 _recon_image;
+//  mainVideoUnshaded.py:460-465 clamp / normalise), second form: COLUMN-STACKED implicit GEMM with a register gather.
+//
+// isr_conv_final.cuh stacks all nine taps along N over the un-shifted halo and sums the nine shifted partial results per
+// output pixel through a shared-memory gather buffer; ncu (profiles/r02_ncu_conv_full_a.json) shows that gather to be the
+// bound: LSU data pipe 68 % busy, tensor pipe 31 %, 0.87 ms where the HBM traffic (2.2 GB read + 0.78 GB written) needs
+// 0.45 ms.  Here only the three taps of a kernel ROW (kx = 0, 1, 2) are stacked along N; the three kernel rows (ky) are
+// three A windows of the same halo tile, shifted by whole halo rows through the shared-memory descriptor, accumulating
+// into the same TMEM columns:
+//     D[m, kx*CP + co] = sum_ky sum_ci halo[m + ky*pitch][ci] * W[co, ci, ky, kx]        (m = linear halo pixel index)
+//     out[(y, x), co]  = bias + D[m][co] + D[m + 1][CP + co] + D[m + 2][2 CP + co],        m = y * pitch + x
+// so the gather is a horizontal 3-term sum over NEIGHBOURING GEMM rows = neighbouring lanes of the epilogue warp: two
+// warp shuffles per channel (the two lanes at a warp boundary fetch three short vectors of the next warp from a 384-byte
+// exchange buffer).  No gather buffer, no 40 KB of shared-memory writes + 27 KB of reads per tile.
+//
+// Tile = 16 px x 7 rows: its 18 x 9 halo is 162 contiguous 128-byte rows, ONE M = 128 row group covers the 7 x 18 = 126
+// linear positions (112 of them are output pixels).  MMAs per tile and pass: 3 ky x 4 k16-steps = 12 with N = 3 CP padded
+// to 16 (x2 stacked along N when the weights carry a lo plane: one MMA computes A x [W_hi ; W_lo]^T), against 2 x 4 with
+// N = 9 CP before: more tensor time (0.36 ms at configs[1] sizes), still under the HBM time, and no LSU-bound phase.
+#pragma once
+#include "isr_conv_final.cuh"
+
+namespace isr {
+
+constexpr int kGTileW = 16, kGTileH = 7, kGPitch = kGTileW + 2, kGHaloH = kGTileH + 2;
+static_assert(kGPitch * kGTileH <= 126, "rows m, m+1, m+2 of every output pixel must lie inside the M = 128 row group");
+constexpr int kGStageRows = 128 + 2 * kGPitch;   // rows an A window may touch (the last two belong to no output pixel)
+constexpr int kGScratch = 2048;                  // per group and parity: exchange vectors (512 B) + skip patch (768 B)
+// FOUR epilogue groups (one accumulator buffer and one MMA-issuing warp each): the epilogue is a serial chain per tile and
+// group, so its throughput scales with the number of groups until the registers run out (21 warps -> 96 per thread)
+constexpr int kG2MaxGroups = 4;
+__host__ __device__ constexpr int g2_threads(int groups) { return (4 * groups + 1 + groups) * 32; }
+
+template <int CP>
+struct Final2Cfg {
+  static constexpr int kCols = 3 * CP;                       // useful accumulator columns per weight part
+  static constexpr int kNK = (kCols + 15) / 16 * 16;         // UMMA N of one part
+  static constexpr int kLd = (kCols + 7) / 8 * 8;            // columns fetched from TMEM (x8 loads)
+  static constexpr uint32_t kTmemCols = (kG2MaxGroups * 2 * kNK <= 128) ? 128 : 256;
+};
+
+// FAST = 1: the two shapes the reference's networks have -- unshaded (Cout 6, 5 skip channels, clamp / normalise state) for
+// CP = 6, shaded (Cout 3, 3 skip channels, clamp state) for CP = 4 -- with residual reconstruction and no raw output: channel
+// counts are compile-time constants, so the per-channel predicates of the generic epilogue disappear.  The epilogue is a
+// serial chain of ~500 instructions per warp and tile and IS the bound of this kernel (tools/final_experiments2.py: the
+// same time with every store redirected to one cached address), so its instruction count is the launch time.
+template <int CP, int FAST, int G>
+__global__ void __launch_bounds__(g2_threads(G), 1)
+conv3x3_final2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                      const ConvParams p) {
+  using C = Final2Cfg<CP>;
+  static_assert(!FAST || CP == 6 || CP == 4, "fast epilogues exist for the unshaded (CP 6) and shaded (CP 4) networks");
+  constexpr int kFastCout = CP == 6 ? 6 : 3, kFastMask = CP == 6 ? 5 : 3;
+  constexpr int NK = C::kNK;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  constexpr uint32_t kPartBytes = NK * 128;                  // one (ky, part) block: NK rows of 64 16-bit
+  const uint32_t w_bytes = 3 * p.n_w_parts * kPartBytes;
+  const uint32_t s_w = smem_base;
+  const uint32_t s_scr = s_w + ((w_bytes + 1023u) & ~1023u);
+  const uint32_t s_stage0 = s_scr + G * 2 * kGScratch;
+  const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
+  const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
+                 b_tempty = b_tfull + 8 * G, s_tptr = b_tempty + 8 * G;
+  __shared__ float s_bias[8];
+  if (threadIdx.x < 8) s_bias[threadIdx.x] = (p.bias != nullptr && threadIdx.x < p.cout) ? p.bias[threadIdx.x] : 0.f;
+
+  constexpr int kTmaWarp = 4 * G, kMmaWarp = 4 * G + 1;
+  if (warp == kTmaWarp && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmW);
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(b_full + 8 * s, 1);
+      mbar_init(b_empty + 8 * s, 1);
+    }
+    mbar_init(b_w, 1);
+    for (int a = 0; a < G; ++a) {
+      mbar_init(b_tfull + 8 * a, 1);
+      mbar_init(b_tempty + 8 * a, 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == kMmaWarp) tmem_alloc(s_tptr, C::kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(s_tptr));
+
+  const int my_tiles = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                       static_cast<int>(gridDim.x);
+  // Tile t = blockIdx.x + i * gridDim.x.  Every role walks its tiles with a (tx, ty, b) counter advanced by a constant
+  // step instead of dividing t: the per-tile work of the single-thread roles is a serial dependency chain, and with 112
+  // pixels per tile (1000 tiles per SM at configs[1] sizes) three integer divisions per tile were a measurable part of
+  // the launch (tools/final_experiments2.py).
+  struct TileCursor {
+    int tx, ty, b, dx, dy, db, tiles_x, tiles_y;
+    __device__ __forceinline__ void init(int t, int step, int txs, int tys) {
+      tiles_x = txs; tiles_y = tys;
+      tx = t % txs; ty = (t / txs) % tys; b = t / (txs * tys);
+      dx = step % txs; dy = (step / txs) % tys; db = step / (txs * tys);
+    }
+    __device__ __forceinline__ void advance() {
+      tx += dx; ty += dy; b += db;
+      if (tx >= tiles_x) { tx -= tiles_x; ++ty; }
+      if (ty >= tiles_y) { ty -= tiles_y; ++b; }
+    }
+  };
+
+  if (warp == kTmaWarp) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      mbar_arrive_expect_tx(b_w, w_bytes);
+      for (int ky = 0; ky < 3; ++ky)
+        for (int wp = 0; wp < p.n_w_parts; ++wp)   // global rows: [ky][part 2][NK]; shared: [ky][part n_w_parts][NK]
+          tma_load_2d(s_w + (ky * p.n_w_parts + wp) * kPartBytes, &tmW, b_w, 0, p.w_row0 + (ky * 2 + wp) * NK);
+    }
+    __syncwarp();
+    uint32_t it = 0;
+    TileCursor cur;
+    cur.init(blockIdx.x, gridDim.x, p.tiles_x, p.tiles_y);
+    for (int i = 0; i < my_tiles; ++i, cur.advance()) {
+      const int tx = cur.tx, ty = cur.ty, b = cur.b;
+      for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
+        const uint32_t s = it % p.num_stages;
+        const uint32_t ph = (it / p.num_stages) & 1;
+        mbar_wait_parked(b_empty + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(b_full + 8 * s, kGPitch * kGHaloH * 128);
+          tma_load_4d(s_stage0 + s * p.stage_bytes, &tmA, b_full + 8 * s, ap * 64, tx * kGTileW - 1, ty * kGTileH - 1, b);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= kMmaWarp) {
+    // ===================== MMA issuers: one warp per accumulator buffer (see isr_conv_final.cuh) =====================
+    const int mw = warp - kMmaWarp;
+    const uint32_t idesc_all = make_idesc_f16(128, p.n_w_parts * NK, p.is_bf16);   // A x [W_hi ; W_lo]^T
+    const uint32_t idesc_hi = make_idesc_f16(128, NK, p.is_bf16);                   // A_lo x W_hi^T
+    const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
+    mbar_wait(b_w, 0);
+    for (int i = mw; i < my_tiles && mw < p.issuers; i += p.issuers) {
+      const uint32_t acc = i % G;
+      const uint32_t acc_ph = (i / G) & 1;
+      // every waiting warp is parked in hardware (suspend-time hint): a spinning warp takes issue slots from the epilogue
+      // warps of its scheduler, and the epilogue (about 600 instructions per pixel row and tile) is what bounds this kernel
+      mbar_wait_parked(b_tempty + 8 * acc, acc_ph ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * (2 * NK);
+      for (int ap = 0; ap < p.n_act_parts; ++ap) {
+        const uint32_t it = static_cast<uint32_t>(i) * p.n_act_parts + ap;
+        const uint32_t s = it % p.num_stages;
+        const uint32_t ph = (it / p.num_stages) & 1;
+        mbar_wait_parked(b_full + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t a_base = s_stage0 + s * p.stage_bytes;
+        if (elect_one()) {
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky) {
+            // halo rows are contiguous 128-byte rows (canonical K-major SW128, 8-row groups 1024 B apart); kernel row ky
+            // = the same 128 rows, kGPitch rows further down
+            const uint64_t adesc = make_smem_desc_sw128(a_base + ky * kGPitch * 128, 1024, 0);
+            const uint64_t bdesc = b_desc_base + static_cast<uint64_t>((ky * p.n_w_parts * kPartBytes) >> 4);
+            umma_f16_k64(d_tmem, adesc, bdesc, ap == 0 ? idesc_all : idesc_hi, (ap == 0 && ky == 0) ? 0u : 1u);
+          }
+          umma_commit(b_empty + 8 * s);
+          if (ap == p.n_act_parts - 1) umma_commit(b_tfull + 8 * acc);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== epilogue warps: group g handles tiles g, g+G, ... =====================
+    const int grp = warp >> 2, q = warp & 3;
+    const int row = q * 32 + lane;                    // GEMM row m = linear halo position of this thread
+    const int py = row / kGPitch, px = row % kGPitch;
+    const bool is_px = py < kGTileH && px < kGTileW;  // 112 of the 128 rows are output pixels
+    int n_local = 0;
+    const int cout = FAST ? kFastCout : p.cout;
+    const int n_mask = FAST ? kFastMask : p.n_mask;
+    const bool want_skip = FAST ? true : (p.recon_residual != 0);
+    // skip patch elements this thread stages (loop-invariant): element e = row + 128 k -> (channel, patch row, patch col)
+    const int nm = n_mask > 0 ? (n_mask < 8 ? n_mask : 8) : 1;
+    const int n_skip = want_skip ? nm * 24 : 0;
+    int e_c[2], e_r[2], e_cc[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int e = row + 128 * k;
+      e_c[k] = e / 24; e_r[k] = (e % 24) / 6; e_cc[k] = (e % 24) % 6;
+    }
+    TileCursor cur;
+    cur.init(blockIdx.x + grp * gridDim.x, G * gridDim.x, p.tiles_x, p.tiles_y);
+    for (int i = grp; i < my_tiles; i += G, ++n_local, cur.advance()) {
+      const int tx = cur.tx, ty = cur.ty, b = cur.b;
+      const uint32_t acc = grp;
+      const uint32_t acc_ph = (i / G) & 1;
+      const uint32_t taddr = tmem_base + acc * (2 * NK) + (static_cast<uint32_t>(q * 32) << 16);
+      float *scr = reinterpret_cast<float *>(smem_raw + (s_scr - smem_u32(smem_raw)) +
+                                             (grp * 2 + (n_local & 1)) * kGScratch);
+      float *X = scr;            // [warp 4][3 * 8]: lane 0's kx = 1 and kx = 2 vectors, lane 1's kx = 2 vector
+      float *S = scr + 256;      // low-res skip patch: [channel <= 8][4 rows][6 cols]
+      const int y = ty * kGTileH + py, x = tx * kGTileW + px;
+      const bool inb = is_px && (y < p.H) && (x < p.W);
+      // Skip connection (_recon_image, enhancenet.py:67-71): 4x bilinear / nearest upsample of the low-res input.  The
+      // tile's 16 x 7 pixels read a 6 x 4 (cols x rows) low-res patch per channel, origin (by, bx), indices clamped.
+      float lx0 = 1.f, lx1 = 0.f, ly0 = 1.f, ly1 = 0.f;
+      int o00 = 0, o01 = 0, o10 = 0, o11 = 0;   // offsets of this pixel's four taps inside one channel of the patch
+      float sv[2] = {0.f, 0.f};
+      if (want_skip) {
+        const int Y0 = ty * kGTileH;
+        const int by = (2 * Y0 - 3) >> 3, bx = 4 * tx - 1;   // floor(0.25 * (Y0 + 0.5) - 0.5), unclamped
+        const float *sb = p.skip_src + b * p.skip_bstride;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          if (row + 128 * k < n_skip) {
+            const int yy = min(max(by + e_r[k], 0), p.h_low - 1), xx = min(max(bx + e_cc[k], 0), p.w_low - 1);
+            sv[k] = __ldg(sb + (static_cast<size_t>(e_c[k]) * p.h_low + yy) * p.w_low + xx);
+          }
+        }
+        int x0, x1, y0, y1;
+        if (p.upsample == 1) {
+          bil_src(x, p.w_low, 0.25f, x0, x1, lx0, lx1);
+          bil_src(y, p.h_low, 0.25f, y0, y1, ly0, ly1);
+        } else {
+          x0 = x1 = min(x >> 2, p.w_low - 1);
+          y0 = y1 = min(y >> 2, p.h_low - 1);
+        }
+        const int pr0 = min(max(y0 - by, 0), 3) * 6, pr1 = min(max(y1 - by, 0), 3) * 6;
+        const int pc0 = min(max(x0 - bx, 0), 5), pc1 = min(max(x1 - bx, 0), 5);
+        o00 = pr0 + pc0; o01 = pr0 + pc1; o10 = pr1 + pc0; o11 = pr1 + pc1;
+      }
+      mbar_wait_parked(b_tfull + 8 * acc, acc_ph);
+      tc_fence_after();
+      // ---- accumulator row -> registers: d[kx * CP + co] (hi + lo weight parts summed) ----
+      float d[C::kLd];
+      {
+        uint32_t v[C::kLd];
+#pragma unroll
+        for (int c8 = 0; c8 < C::kLd / 8; ++c8) tmem_ld8(taddr + 8 * c8, v + 8 * c8);
+        if (p.n_w_parts == 2) {
+          uint32_t v2[C::kLd];
+#pragma unroll
+          for (int c8 = 0; c8 < C::kLd / 8; ++c8) tmem_ld8(taddr + NK + 8 * c8, v2 + 8 * c8);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < C::kLd; ++c) d[c] = __uint_as_float(v[c]) + __uint_as_float(v2[c]);
+        } else {
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < C::kLd; ++c) d[c] = __uint_as_float(v[c]);
+        }
+      }
+      // the accumulator buffer is free as soon as it is in registers
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(b_tempty + 8 * acc);
+      // ---- horizontal gather: rows m + 1 (kx = 1) and m + 2 (kx = 2) live in lanes + 1, + 2 ----
+      float t1[CP], t2[CP];
+#pragma unroll
+      for (int c = 0; c < CP; ++c) {
+        t1[c] = __shfl_down_sync(0xffffffffu, d[CP + c], 1);
+        t2[c] = __shfl_down_sync(0xffffffffu, d[2 * CP + c], 2);
+      }
+      if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < CP; ++c) { X[q * 24 + c] = d[CP + c]; X[q * 24 + 8 + c] = d[2 * CP + c]; }
+      } else if (lane == 1) {
+#pragma unroll
+        for (int c = 0; c < CP; ++c) X[q * 24 + 16 + c] = d[2 * CP + c];
+      }
+      if (row < n_skip) S[row] = sv[0];
+      if (row + 128 < n_skip) S[row + 128] = sv[1];
+      named_bar_sync(1 + grp, 128);   // exchange vectors and skip patch visible; the scratch block alternates per tile
+      if (q < 3 && lane >= 30) {
+        const float *Xn = X + (q + 1) * 24;
+#pragma unroll
+        for (int c = 0; c < CP; ++c) {
+          if (lane == 31) { t1[c] = Xn[c]; t2[c] = Xn[16 + c]; }
+          else t2[c] = Xn[8 + c];
+        }
+      }
+      float rec[CP];
+#pragma unroll
+      for (int c = 0; c < CP; ++c) rec[c] = ((s_bias[c] + d[c]) + t1[c]) + t2[c];
+      if (inb && !((p.dbg & 64) && rec[0] != 12345.678f)) {   // dbg bit6: bench experiment without the global stores
+        // dbg bit9: the whole epilogue arithmetic, but every store lands on one dummy address per thread (no DRAM stream)
+        const bool fake = (p.dbg & 512) != 0;
+        const size_t plane = fake ? 0 : static_cast<size_t>(p.H) * p.W;
+        const size_t o0 = fake ? static_cast<size_t>(blockIdx.x) * 512 + threadIdx.x
+                               : static_cast<size_t>(b) * cout * plane + static_cast<size_t>(y) * p.W + x;
+        if (!FAST && p.out_raw != nullptr) {
+#pragma unroll
+          for (int c = 0; c < CP; ++c)
+            if (c < cout) __stcs(p.out_raw + o0 + c * plane, rec[c]);
+        }
+        if (want_skip) {
+          // _recon_image (enhancenet.py:67-71): bilinear (x first, then y) or nearest 4x skip + raw
+          const bool bil = p.upsample == 1;
+#pragma unroll
+          for (int c = 0; c < CP; ++c) {
+            if (c < n_mask) {
+              const float *sc = S + c * 24;
+              const float t00 = sc[o00], t01 = sc[o01], t10 = sc[o10], t11 = sc[o11];
+              const float r0 = fmaf(lx0, t00, lx1 * t01);
+              const float r1 = fmaf(lx0, t10, lx1 * t11);
+              rec[c] = (bil ? fmaf(ly0, r0, ly1 * r1) : t00) + rec[c];
+            }
+          }
+        }
+        if (p.out_recon != nullptr) {
+          float *pr = p.out_recon + o0;
+#pragma unroll
+          for (int c = 0; c < CP; ++c)
+            if (c < cout) __stcs(pr + c * plane, rec[c]);
+        }
+        if (p.out_state != nullptr && !(p.dbg & 256)) {   // dbg bit8: bench experiment without the state stores
+          float *ps = p.out_state + o0;
+          if ((FAST ? CP == 6 : (p.state_unshaded && cout >= 5))) {
+            if constexpr (CP >= 6) {
+              // mainVideoUnshaded.py:460-465: clamp mask, normalise normal (shading.py:193-207), clamp depth / ao
+              __stcs(ps, fminf(fmaxf(rec[0], -1.f), 1.f));
+              float len = sqrtf(rec[1] * rec[1] + rec[2] * rec[2] + rec[3] * rec[3]);
+              len = fmaxf(len, 1e-7f);
+              __stcs(ps + plane, rec[1] / len);
+              __stcs(ps + 2 * plane, rec[2] / len);
+              __stcs(ps + 3 * plane, rec[3] / len);
+#pragma unroll
+              for (int c = 4; c < CP; ++c)
+                if (c < cout) __stcs(ps + c * plane, fminf(fmaxf(rec[c], 0.f), 1.f));
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < CP; ++c)
+              if (c < cout) __stcs(ps + c * plane, fminf(fmaxf(rec[c], 0.f), 1.f));
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, C::kTmemCols);
+}
+
+}  // namespace isr

@@ -36,6 +36,9 @@ cudaError_t launch_pack_weights(const float *w, uint16_t *out, int cout, int cin
 // tap-stacked output-conv weights: [fmt 2][part 2][nrows (n = tap*cp + co)][64]
 cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s);
 
+// column-stacked output-conv weights (isr_conv_final2.cuh): [fmt 2][ky 3][part 2][nk (n = kx*cp + co)][64]
+cudaError_t launch_pack_weights_final2(const float *w, uint16_t *out, int cout, int cp, int nk, cudaStream_t s);
+
 cudaError_t launch_shade_rgb8(const float *in, const float *params22, unsigned char *out, int B, int C, int H, int W,
                               cudaStream_t s);
 // isr_ingest.cu

@@ -980,6 +980,27 @@ __global__ void pack_weights_final_kernel(const float *__restrict__ w, uint16_t 
   }
 }
 
+// column-stacked weights of the output conv, second form (isr_conv_final2.cuh): fp32 OIHW [cout][64][3][3] ->
+// [fmt 2 (bf16, fp16)][ky 3][part 2 (hi, lo)][n = kx*cp + co, padded to nk][64] 16-bit
+__global__ void pack_weights_final2_kernel(const float *__restrict__ w, uint16_t *__restrict__ out, int cout, int cp,
+                                           int nk) {
+  const int per_fmt = 3 * 2 * nk * 64;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * nk * 64; i += gridDim.x * blockDim.x) {
+    const int k = i & 63, n = (i >> 6) % nk, ky = i / (64 * nk);
+    const int kx = n / cp, co = n % cp;
+    const float v = (kx < 3 && co < cout) ? w[(static_cast<size_t>(co) * 64 + k) * 9 + ky * 3 + kx] : 0.f;
+    const __nv_bfloat16 bh = __float2bfloat16_rn(v);
+    const __nv_bfloat16 bl = __float2bfloat16_rn(v - __bfloat162float(bh));
+    const __half hh = __float2half_rn(v);
+    const __half hl = __float2half_rn(v - __half2float(hh));
+    const int o = ((ky * 2) * nk + n) * 64 + k;
+    out[o] = *reinterpret_cast<const uint16_t *>(&bh);
+    out[o + nk * 64] = *reinterpret_cast<const uint16_t *>(&bl);
+    out[per_fmt + o] = *reinterpret_cast<const uint16_t *>(&hh);
+    out[per_fmt + o + nk * 64] = *reinterpret_cast<const uint16_t *>(&hl);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // host launchers
 static inline int grid_for(size_t total, int block) {
@@ -1167,6 +1188,11 @@ cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, i
 }
 cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s) {
   pack_weights_final_kernel<<<(nrows * 64 + 255) / 256, 256, 0, s>>>(w, out, cout, cp, nrows);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_pack_weights_final2(const float *w, uint16_t *out, int cout, int cp, int nk, cudaStream_t s) {
+  pack_weights_final2_kernel<<<(3 * nk * 64 + 255) / 256, 256, 0, s>>>(w, out, cout, cp, nk);
   count_launch();
   return cudaGetLastError();
 }

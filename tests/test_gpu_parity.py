@@ -339,7 +339,7 @@ def test_output_conv_tap_stacked_equals_generic(isr, golden, weights, prec):
     x = cu(g["x"])
     outs = {}
     try:
-        for fin, stk in ((2, 1), (2, 0), (1, 1), (0, 1), (1, 0), (0, 0)):
+        for fin, stk in ((3, 1), (2, 1), (2, 0), (1, 1), (0, 1), (1, 0), (0, 0)):
             _lib.set_tunable("final_stacked", fin)
             _lib.set_tunable("stack_w", stk)
             net = _net(isr, weights)
@@ -347,8 +347,10 @@ def test_output_conv_tap_stacked_equals_generic(isr, golden, weights, prec):
             with torch.no_grad():
                 outs[(fin, stk)] = net(x)[0].clone()
     finally:
-        _lib.set_tunable("final_stacked", 1)
+        _lib.set_tunable("final_stacked", 3)
         _lib.set_tunable("stack_w", 1)
+    # column-stacked output conv with the register gather (isr_conv_final2.cuh, the default) vs the generic kernel
+    assert maxabs(outs[(3, 1)], outs[(0, 1)]) <= 5e-5
     # tap-stacked vs generic output conv: same products, different fp32 summation order
     assert maxabs(outs[(1, 1)], outs[(0, 1)]) <= 5e-5 and maxabs(outs[(1, 0)], outs[(0, 0)]) <= 5e-5
     # CTA-pair output conv (tunable final_stacked=2) vs the generic single-CTA kernel

@@ -412,3 +412,38 @@ def test_compose_v4_equals_scalar(isr, masking, shape):
         isr._lib.set_tunable("compose_variant", 2)
     for a, b in zip(outs[1], outs[2]):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("shape", [(1, 16, 20), (2, 19, 27), (1, 33, 130), (1, 270, 480)])
+@pytest.mark.parametrize("variant", ["unshaded", "shaded", "nearest", "bf16x3"])
+def test_output_conv_column_stacked_equals_tap_stacked(isr, weights, shape, variant):
+    """conv3x3_final2_kernel (three kernel rows through shifted A windows, three kernel columns stacked along N, gather by
+    warp shuffles; 16 x 7 tiles) against conv3x3_final_kernel (nine taps stacked, shared-memory gather; 16 x 8 tiles):
+    the same products in a different fp32 summation order, prediction AND fused recurrent state, ragged sizes, Cout 6 / 3,
+    bilinear / nearest skip, single and split activations."""
+    B, h, w = shape
+    g = torch.Generator(device="cuda").manual_seed(3 * h + w)
+    if variant == "shaded":
+        torch.manual_seed(1234)
+        mk = lambda: _net(isr, None, cin=56, cout=3, mask=(0, 1, 2))
+        cin = 56
+    else:
+        mk = lambda: _net(isr, weights, ups="nearest" if variant == "nearest" else "bilinear")
+        cin = 101
+    x = torch.rand(B, cin, h, w, device="cuda", generator=g) * 2 - 1
+    outs = {}
+    try:
+        for fin in (3, 1):
+            isr._lib.set_tunable("final_stacked", fin)
+            if variant == "shaded":
+                torch.manual_seed(1234)
+            net = mk()
+            net.precision = "bf16x3" if variant == "bf16x3" else "hybrid"
+            with torch.no_grad():
+                h_ = net._native()
+                outs[fin] = h_.forward(x, net.precision, want_raw=True, want_state=True, state_unshaded=(variant != "shaded"))
+    finally:
+        isr._lib.set_tunable("final_stacked", 3)
+    for a, b in zip(outs[3], outs[1]):
+        assert torch.isfinite(a).all()
+        assert maxabs(a, b) <= 5e-5
