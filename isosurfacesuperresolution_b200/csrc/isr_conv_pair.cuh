@@ -90,6 +90,21 @@ __device__ __forceinline__ void umma2_commit_multicast(uint32_t bar) {
       : "memory");
 }
 
+// (tx, ty, b) of tile t, advanced by a constant step without divisions (one division set per role and launch)
+struct PairTileCursor {
+  int tx, ty, b, dx, dy, db, tiles_x, tiles_y;
+  __device__ __forceinline__ void init(int t, int step, int txs, int tys) {
+    tiles_x = txs; tiles_y = tys;
+    tx = t % txs; ty = (t / txs) % tys; b = t / (txs * tys);
+    dx = step % txs; dy = (step / txs) % tys; db = step / (txs * tys);
+  }
+  __device__ __forceinline__ void advance() {
+    tx += dx; ty += dy; b += db;
+    if (tx >= tiles_x) { tx -= tiles_x; ++ty; }
+    if (ty >= tiles_y) { ty -= tiles_y; ++b; }
+  }
+};
+
 // Two epilogue groups of four warps and FOUR accumulator buffers in TMEM: tile i uses buffer i % 4 and is drained by
 // group i % 2 (so a group only ever waits on its own two buffers and observes every phase of their barriers).  With two
 // buffers the epilogue of tile i had to finish within the MMA time of tile i+1 (~1500 cycles) or the issuer stalled;
@@ -184,16 +199,24 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     __syncwarp();
     pdl_wait();   // the activations are the previous kernel's output
-    uint32_t it = 0;
-    for (int i = 0; i < my_iters; ++i) {
-      const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
-      const bool valid = t < p.num_tiles;
-      const int tx = t % p.tiles_x;
-      const int ty = (t / p.tiles_x) % p.tiles_y;
-      const int b = valid ? t / (p.tiles_x * p.tiles_y) : p.B;   // invalid tile: fully out of bounds = zero fill
+    // Per-tile bookkeeping without integer divisions (a division by a run-time value is ~30 dependent instructions in a
+    // single-thread role whose per-tile chain is on the critical path: the output conv lost 7 % to three of them per tile,
+    // tools/final_experiments2.py): the tile coordinates and the stage ring are counters advanced by constant steps.
+    uint32_t it = 0, s = 0, ph = 0;
+    PairTileCursor cur;
+    cur.init(2 * pair_id + static_cast<int>(rank), 2 * num_pairs, p.tiles_x, p.tiles_y);
+    for (int i = 0; i < my_iters; ++i, cur.advance()) {
+      bool valid = cur.b < p.B;
+      int tx = cur.tx, ty = cur.ty;
+      int b = valid ? cur.b : p.B;   // invalid tile: fully out of bounds = zero fill
+      if (p.dbg & 1024) {   // bench experiment: the divisions of the first form
+        const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
+        valid = t < p.num_tiles; tx = t % p.tiles_x; ty = (t / p.tiles_x) % p.tiles_y;
+        b = valid ? t / (p.tiles_x * p.tiles_y) : p.B;
+      }
       for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
-        const uint32_t s = it % p.num_stages;
-        const uint32_t ph = (it / p.num_stages) & 1;
+        if (it != 0 && ++s == static_cast<uint32_t>(p.num_stages)) { s = 0; ph ^= 1; }
+        if (p.dbg & 1024) { s = it % p.num_stages; ph = (it / p.num_stages) & 1; }
         mbar_wait_parked(b_empty + 8 * s, ph ^ 1);
         if (elect_one()) {
           const uint32_t lead_full = mapa_shared(b_full + 8 * s, 0);
@@ -281,13 +304,23 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ===================== epilogue warps: group g = warp/4 drains tiles g, g+G, ... =====================
     const int grp = warp >> 2, q = warp & 3;
     pdl_wait();   // addend reads / output writes must not overtake the previous kernel
+    PairTileCursor cur;
+    int cur_i = -1;
     for (int v = grp; v < my_iters * PH; v += G) {
       const int i = v / PH, phase = v % PH;
-      const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
-      const bool valid = t < p.num_tiles;
-      const int tx = t % p.tiles_x;
-      const int ty = (t / p.tiles_x) % p.tiles_y;
-      const int b = valid ? t / (p.tiles_x * p.tiles_y) : 0;
+      if (cur_i < 0) {
+        cur.init(2 * (pair_id + i * num_pairs) + static_cast<int>(rank), 2 * num_pairs, p.tiles_x, p.tiles_y);
+        cur_i = i;
+      }
+      for (; cur_i < i; ++cur_i) cur.advance();   // G / PH tiles (PH = 1) or none (the next phase of the same tile)
+      bool valid = cur.b < p.B;
+      int tx = cur.tx, ty = cur.ty;
+      int b = valid ? cur.b : 0;
+      if (p.dbg & 1024) {   // bench experiment: the divisions of the first form
+        const int t = 2 * (pair_id + i * num_pairs) + static_cast<int>(rank);
+        valid = t < p.num_tiles; tx = t % p.tiles_x; ty = (t / p.tiles_x) % p.tiles_y;
+        b = valid ? t / (p.tiles_x * p.tiles_y) : 0;
+      }
       const uint32_t acc = v % NB;
       const uint32_t acc_ph = (v / NB) & 1;
       const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
