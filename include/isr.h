@@ -302,7 +302,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "final_w_parts" ([0] = scheme | 1 | 2)   weight planes of the output conv
  *   "raycast_two_pass" (0 | [1] = from 8 AO rays on | 2)   ambient occlusion of the ray-caster as a second pass
  *   "compose_variant" (1 | [2])      process-wide: GUI composition kernel (2 = 4 pixels per thread, bit-identical to 1)
- *   "pack_variant" (1 | [2])         process-wide: network-input packing kernel (2 = per-column form, bit-identical to 1)
+ *   "pack_variant" (1 | [2] | 3)     process-wide: network-input packing kernel (2 = per-column form, bit-identical to 1;
+ *                                    3 = the same with 16-byte tap loads, measured slower)
  *   "dbg"                            bit mask of bench experiments (tools/), 0 in production */
 int isr_set_tunable(const char *key, int value);
 int isr_net_set_tunable(isr_net *net, const char *key, int value);

@@ -775,7 +775,7 @@ int isr_set_tunable(const char *key, int value) {
     return old;
   }
   if (key != nullptr && strcmp(key, "pack_variant") == 0) {       // process-wide: which network-input packing kernel
-    if (value != 1 && value != 2) return fail(ISR_ERR_ARG, "pack_variant must be 1 or 2");
+    if (value < 1 || value > 3) return fail(ISR_ERR_ARG, "pack_variant must be 1, 2 or 3");
     return set_pack_variant(value);
   }
   if (key != nullptr && strcmp(key, "compose_variant") == 0) {    // process-wide: which composition kernel

@@ -323,7 +323,7 @@ pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ p
 constexpr int kPack2Low = 32;
 constexpr int kPack2Pitch = 132;   // floats per low-res pixel in the tile: = 4 (mod 32) and a multiple of 4
 
-template <int CP, int NPARTS, int BF16>
+template <int CP, int NPARTS, int BF16, int VEC4>
 __global__ void __launch_bounds__(128)
 pack_recurrent_v2_kernel(const float *__restrict__ low, const float *__restrict__ prev, const float *__restrict__ flow,
                          uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int c_low, int h, int w,
@@ -413,14 +413,51 @@ pack_recurrent_v2_kernel(const float *__restrict__ low, const float *__restrict_
         const float wse = (vy1 && vx1) ? (ix - x0f) * (iy - y0f) : 0.f;
         const int cx0 = min(max(x0, 0), W - 1), cx1 = min(max(x0 + 1, 0), W - 1);
         const int cy0 = min(max(y0, 0), H - 1) * W, cy1 = min(max(y0 + 1, 0), H - 1) * W;
-        const int o00 = cy0 + cx0, o01 = cy0 + cx1, o10 = cy1 + cx0, o11 = cy1 + cx1;
         float v[CP][4];
+        if constexpr (VEC4) {
+          // The kernel is bound by the L1 data pipe (98 % of peak: the noisy synthetic flow sends every lane of a warp to
+          // its own row, 17.6 sectors per request), so the two taps of a row -- neighbours in memory -- are fetched with ONE
+          // aligned 16-byte load (plus a second one for the quarter of the lanes whose pair straddles the 16-byte
+          // boundary) instead of two 4-byte loads: 1.25 instead of 2 scattered requests per row and channel.
+          const int a0 = cx0 & ~3;                       // W % 4 == 0 and cx0 <= W - 1, so a0 + 3 is inside the row
+          const int k0 = cx0 - a0, k1 = cx1 - a0;        // 0..3 and 0..4 (cx1 is cx0 or cx0 + 1)
+          const bool need2 = k1 == 4;
+          const bool b0 = (k0 & 1) != 0, b1 = (k0 & 2) != 0, c0 = (k1 & 1) != 0, c1 = (k1 & 2) != 0;
+          const int r0 = cy0 + a0, r1 = cy1 + a0;
+          float4 q0[CP], q1[CP], e0[CP], e1[CP];
 #pragma unroll
-        for (int c = 0; c < CP; ++c) {   // all 4 * CP taps are requested before the first use; 32-bit element indices
-          v[c][0] = __ldg(pb + (o00 + c * planei));   // (the launcher checks CP * H * W < 2^31)
-          v[c][1] = __ldg(pb + (o01 + c * planei));
-          v[c][2] = __ldg(pb + (o10 + c * planei));
-          v[c][3] = __ldg(pb + (o11 + c * planei));
+          for (int c = 0; c < CP; ++c) {
+            q0[c] = __ldg(reinterpret_cast<const float4 *>(pb + (r0 + c * planei)));
+            q1[c] = __ldg(reinterpret_cast<const float4 *>(pb + (r1 + c * planei)));
+          }
+#pragma unroll
+          for (int c = 0; c < CP; ++c) {
+            e0[c] = q0[c]; e1[c] = q1[c];
+            if (need2) {
+              e0[c] = __ldg(reinterpret_cast<const float4 *>(pb + (r0 + 4 + c * planei)));
+              e1[c] = __ldg(reinterpret_cast<const float4 *>(pb + (r1 + 4 + c * planei)));
+            }
+          }
+#pragma unroll
+          for (int c = 0; c < CP; ++c) {
+            const float lo0 = b0 ? q0[c].y : q0[c].x, hi0 = b0 ? q0[c].w : q0[c].z;
+            const float lo1 = b0 ? q1[c].y : q1[c].x, hi1 = b0 ? q1[c].w : q1[c].z;
+            v[c][0] = b1 ? hi0 : lo0;
+            v[c][2] = b1 ? hi1 : lo1;
+            const float m0 = c0 ? q0[c].y : q0[c].x, n0 = c0 ? q0[c].w : q0[c].z;
+            const float m1 = c0 ? q1[c].y : q1[c].x, n1 = c0 ? q1[c].w : q1[c].z;
+            v[c][1] = need2 ? e0[c].x : (c1 ? n0 : m0);
+            v[c][3] = need2 ? e1[c].x : (c1 ? n1 : m1);
+          }
+        } else {
+          const int o00 = cy0 + cx0, o01 = cy0 + cx1, o10 = cy1 + cx0, o11 = cy1 + cx1;
+#pragma unroll
+          for (int c = 0; c < CP; ++c) {   // all 4 * CP taps are requested before the first use; 32-bit element indices
+            v[c][0] = __ldg(pb + (o00 + c * planei));   // (the launcher checks CP * H * W < 2^31)
+            v[c][1] = __ldg(pb + (o01 + c * planei));
+            v[c][2] = __ldg(pb + (o10 + c * planei));
+            v[c][3] = __ldg(pb + (o11 + c * planei));
+          }
         }
 #pragma unroll
         for (int c = 0; c < CP; ++c) {
@@ -1104,7 +1141,8 @@ cudaError_t launch_compose(const float *low, const float *pred, const float *par
   count_launch();
   return cudaGetLastError();
 }
-static int g_pack_variant = 2;   // 1 = the first kernel, 2 = pack_recurrent_v2_kernel (bit-identical, fewer instructions)
+static int g_pack_variant = 2;   // 1 = the first kernel, 2 = pack_recurrent_v2_kernel (bit-identical, fewer instructions),
+                                 // 3 = v2 with 16-byte tap loads (experiment: slower)
 int set_pack_variant(int v) {
   const int old = g_pack_variant;
   g_pack_variant = v;
@@ -1114,12 +1152,22 @@ cudaError_t launch_pack_recurrent(const float *low, const float *prev, const flo
                                   int B, int c_low, int c_prev, int h, int w, int special_mask, int align_corners,
                                   int nparts, int is_bf16, cudaStream_t s) {
   const bool small_plane = static_cast<size_t>(h) * 4 * w * 4 * 4 * 8 < (1ull << 32);   // 32-bit byte offsets inside a frame
-  if (g_pack_variant == 2 && (c_prev == 6 || c_prev == 3) && c_low + 16 * c_prev <= 128 &&
+  if (g_pack_variant >= 2 && (c_prev == 6 || c_prev == 3) && c_low + 16 * c_prev <= 128 &&
       static_cast<size_t>(c_prev) * h * 4 * w * 4 < (1ull << 31)) {
     dim3 grid2((w + kPack2Low - 1) / kPack2Low, h, B);
+    // 16-byte tap loads need 16-byte aligned rows: base pointer aligned, W a multiple of 4 (always: W = 4 w)
+    // (measured SLOWER on the noisy synthetic flow: 563 vs 442 us per configs[4] chunk -- a divergent 16-byte load costs
+    // more L1 wavefronts than two divergent 4-byte loads; kept as the opt-in pack_variant 3)
+    const bool vec4 = g_pack_variant == 3 && (reinterpret_cast<uintptr_t>(prev) & 15) == 0 && flow != nullptr;
 #define ISR_PACK2(CPV, NP, BF)                                                                                          \
-  pack_recurrent_v2_kernel<CPV, NP, BF><<<grid2, 128, 0, s>>>(low, prev, flow, g0, g1, c_low, h, w, special_mask,       \
-                                                             align_corners)
+  do {                                                                                                                  \
+    if (vec4)                                                                                                           \
+      pack_recurrent_v2_kernel<CPV, NP, BF, 1><<<grid2, 128, 0, s>>>(low, prev, flow, g0, g1, c_low, h, w, special_mask, \
+                                                                    align_corners);                                     \
+    else                                                                                                                \
+      pack_recurrent_v2_kernel<CPV, NP, BF, 0><<<grid2, 128, 0, s>>>(low, prev, flow, g0, g1, c_low, h, w, special_mask, \
+                                                                    align_corners);                                     \
+  } while (0)
     const int sel = (c_prev == 6 ? 4 : 0) + (nparts == 2 ? 2 : 0) + (is_bf16 ? 1 : 0);
     switch (sel) {
       case 0: ISR_PACK2(3, 1, 0); break;

@@ -381,13 +381,21 @@ def test_pack_recurrent_v2_equals_v1(isr, weights, shape, c_prev):
     flow[:, :, : h // 3] *= 20                                # far outside the image: zero / -1 padding taps
     outs = {}
     try:
-        for variant in (1, 2):
+        for variant in (1, 2, 3):         # 2 = v2 (default), 3 = v2 with 16-byte tap loads (experiment)
             isr._lib.set_tunable("pack_variant", variant)
             with torch.no_grad():
                 outs[variant] = [net(low, prev, flow, special_mask=sm)[0].clone(), net(low, prev, None)[0].clone()]
+        # a previous frame that is not 16-byte aligned takes the 4-byte path on its own
+        isr._lib.set_tunable("pack_variant", 3)
+        big = torch.empty(prev.numel() + 1, device="cuda")
+        prev_u = big[1:].view_as(prev)
+        prev_u.copy_(prev)
+        with torch.no_grad():
+            outs["unaligned"] = [net(low, prev_u, flow, special_mask=sm)[0].clone()]
     finally:
         isr._lib.set_tunable("pack_variant", 2)
     assert torch.equal(outs[1][0], outs[2][0]) and torch.equal(outs[1][1], outs[2][1])
+    assert torch.equal(outs[1][0], outs[3][0]) and torch.equal(outs[1][0], outs["unaligned"][0])
     assert torch.isfinite(outs[2][0]).all()
 
 
