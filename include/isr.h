@@ -301,6 +301,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "final_issuers" (1 | [3])        MMA-issuing warps of the tap-stacked output conv
  *   "final_w_parts" ([0] = scheme | 1 | 2)   weight planes of the output conv
  *   "raycast_two_pass" (0 | [1] = from 8 AO rays on | 2)   ambient occlusion of the ray-caster as a second pass
+ *   "pdl_small" ([0] | 1)            process-wide: packing / band / shading / composition kernels launched programmatically
+ *                                    too (measured 8 % slower per step: tools/pdl_experiments.py)
  *   "compose_variant" (1 | [2])      process-wide: GUI composition kernel (2 = 4 pixels per thread, bit-identical to 1)
  *   "pack_variant" (1 | [2] | 3)     process-wide: network-input packing kernel (2 = per-column form, bit-identical to 1;
  *                                    3 = the same with 16-byte tap loads, measured slower)

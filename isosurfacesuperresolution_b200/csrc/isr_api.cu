@@ -365,14 +365,23 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
                        (q.out_state == nullptr || q.state_unshaded);
     const bool fast4 = L.cp == 4 && q.cout == 3 && q.n_mask == 3 && q.recon_residual && q.out_raw == nullptr &&
                        (q.out_state == nullptr || !q.state_unshaded);
-    const int thr = g2_threads(L.groups);
-    if (fast6 && L.groups == 4) conv3x3_final2_kernel<6, 1, 4><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else if (fast4 && L.groups == 4) conv3x3_final2_kernel<4, 1, 4><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else if (fast6) conv3x3_final2_kernel<6, 1, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else if (fast4) conv3x3_final2_kernel<4, 1, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else if (L.cp == 4) conv3x3_final2_kernel<4, 0, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else if (L.cp == 6) conv3x3_final2_kernel<6, 0, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
-    else conv3x3_final2_kernel<8, 0, 3><<<L.grid, thr, L.smem, s>>>(L.tmA, L.tmW, L.p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(L.grid);
+    cfg.blockDim = dim3(g2_threads(L.groups));
+    cfg.dynamicSmemBytes = L.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = L.pdl ? 1 : 0;   // follows a CTA-pair conv: its CTAs cannot become resident before that kernel's exit
+    if (fast6 && L.groups == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_final2_kernel<6, 1, 4>, L.tmA, L.tmW, L.p));
+    else if (fast4 && L.groups == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_final2_kernel<4, 1, 4>, L.tmA, L.tmW, L.p));
+    else if (fast6) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_final2_kernel<6, 1, 3>, L.tmA, L.tmW, L.p));
+    else if (fast4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_final2_kernel<4, 1, 3>, L.tmA, L.tmW, L.p));
+    else if (L.cp == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_final2_kernel<4, 0, 3>, L.tmA, L.tmW, L.p));
+    else if (L.cp == 6) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_final2_kernel<6, 0, 3>, L.tmA, L.tmW, L.p));
+    else ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_final2_kernel<8, 0, 3>, L.tmA, L.tmW, L.p));
     count_launch();
     ISR_CUDA(cudaGetLastError());
     return ISR_OK;
@@ -777,6 +786,12 @@ int isr_set_tunable(const char *key, int value) {
   if (key != nullptr && strcmp(key, "pack_variant") == 0) {       // process-wide: which network-input packing kernel
     if (value < 1 || value > 3) return fail(ISR_ERR_ARG, "pack_variant must be 1, 2 or 3");
     return set_pack_variant(value);
+  }
+  if (key != nullptr && strcmp(key, "pdl_small") == 0) {          // process-wide: programmatic launch of the small kernels
+    if (value != 0 && value != 1) return fail(ISR_ERR_ARG, "pdl_small must be 0 or 1");
+    const int old = g_pdl_small;
+    g_pdl_small = value;
+    return old;
   }
   if (key != nullptr && strcmp(key, "compose_variant") == 0) {    // process-wide: which composition kernel
     if (value != 1 && value != 2) return fail(ISR_ERR_ARG, "compose_variant must be 1 or 2");

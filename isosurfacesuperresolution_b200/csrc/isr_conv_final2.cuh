@@ -91,6 +91,9 @@ conv3x3_final2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(s_tptr));
 
+  // Programmatic dependent launch: everything above (barriers, TMEM, tensor-map prefetch) and the weight load below do not
+  // depend on the previous kernel; the warps that touch activations or write outputs call pdl_wait() first.
+  pdl_launch_dependents();
   const int my_tiles = (p.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                        static_cast<int>(gridDim.x);
   // Tile t = blockIdx.x + i * gridDim.x.  Every role walks its tiles with a (tx, ty, b) counter advanced by a constant
@@ -120,6 +123,7 @@ conv3x3_final2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           tma_load_2d(s_w + (ky * p.n_w_parts + wp) * kPartBytes, &tmW, b_w, 0, p.w_row0 + (ky * 2 + wp) * NK);
     }
     __syncwarp();
+    pdl_wait();   // the activations are the previous kernel's output
     uint32_t it = 0;
     TileCursor cur;
     cur.init(blockIdx.x, gridDim.x, p.tiles_x, p.tiles_y);
@@ -180,6 +184,7 @@ conv3x3_final2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int py = row / kGPitch, px = row % kGPitch;
     const bool is_px = py < kGTileH && px < kGTileW;  // 112 of the 128 rows are output pixels
     int n_local = 0;
+    pdl_wait();   // output / state writes must not overtake the kernels that still read those buffers
     const int cout = FAST ? kFastCout : p.cout;
     const int n_mask = FAST ? kFastMask : p.n_mask;
     const bool want_skip = FAST ? true : (p.recon_residual != 0);

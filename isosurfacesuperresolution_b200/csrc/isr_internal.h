@@ -7,6 +7,33 @@ namespace isr {
 
 void count_launch();
 
+// Programmatic dependent launch for the small kernels between the convolutions (packing, band kernels, output conv,
+// shading, composition): launched with programmatic stream serialization, they start while the previous kernel drains and
+// call pdl_prologue() first -- griddepcontrol.launch_dependents (let the NEXT kernel start launching) and
+// griddepcontrol.wait (block until everything before this kernel has completed and is visible).  Without it every such
+// boundary of the 36-launch frame pays ~3.6 us of launch latency (tools/launch_floor.py: 10.2 vs 6.6 us per launch).
+extern int g_pdl_small;   // process-wide switch (tunable "pdl_small"): 1 = the small kernels are launched programmatically
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl_small ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 cudaError_t launch_flatten_high(const float *in, float *out, int B, int C, int H, int W, int r, cudaStream_t s);
 cudaError_t launch_warp_upscale(const float *prev, const float *flow, float *out, int B, int C, int h, int w, int r,
                                 int special_mask, int align_corners, cudaStream_t s);

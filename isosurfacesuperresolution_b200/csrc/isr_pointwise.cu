@@ -216,6 +216,7 @@ __global__ void __launch_bounds__(256)
 pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ prev, const float *__restrict__ flow,
                       uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int B, int c_low, int c_prev_rt, int h,
                       int w, int special_mask, int align_corners, int nparts, int is_bf16) {
+  pdl_prologue();
   __shared__ float tile[kPackLow][129];
   const int c_prev = CP > 0 ? CP : c_prev_rt;
   const int xb = blockIdx.x * kPackLow;
@@ -329,6 +330,7 @@ pack_recurrent_v2_kernel(const float *__restrict__ low, const float *__restrict_
                          uint16_t *__restrict__ out_g0, uint16_t *__restrict__ out_g1, int c_low, int h, int w,
                          int special_mask, int align_corners) {
   constexpr int nparts = NPARTS, is_bf16 = BF16;
+  pdl_prologue();
   __shared__ __align__(16) float tile[kPack2Low * kPack2Pitch];
   const int xb = blockIdx.x * kPack2Low;
   const int y = blockIdx.y;
@@ -639,6 +641,7 @@ __device__ __forceinline__ void shade_pixel(const ShadeParams &s, float m, float
 template <int VEC>
 __global__ void __launch_bounds__(256)
 shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams s, float sf, int B, int C, size_t plane) {
+  pdl_prologue();
   const unsigned nvec = static_cast<unsigned>(plane / VEC);
   const size_t b = blockIdx.y;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {
@@ -679,6 +682,7 @@ shade_kernel(const float *__restrict__ in, float *__restrict__ out, ShadeParams 
 __global__ void __launch_bounds__(256)
 shade_rgb8_kernel(const float *__restrict__ in, unsigned char *__restrict__ out, ShadeParams s, float sf, int B, int C,
                   size_t plane) {
+  pdl_prologue();
   const unsigned nvec = static_cast<unsigned>(plane / 4);
   const size_t b = blockIdx.y;
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {
@@ -717,6 +721,7 @@ shade_rgb8_kernel(const float *__restrict__ in, unsigned char *__restrict__ out,
 __global__ void __launch_bounds__(256)
 compose_kernel(const float *__restrict__ low, const float *__restrict__ pred, float *__restrict__ out, ShadeParams sp,
                float sf, int B, int c_low, int c_pred, int h, int w, int unshaded, int masking, float bg0) {
+  pdl_prologue();
   const int H = 4 * h, W = 4 * w;
   const size_t plane = static_cast<size_t>(H) * W, lplane = static_cast<size_t>(h) * w;
   const int y = blockIdx.x % H, b = blockIdx.x / H;
@@ -760,6 +765,7 @@ template <int UNSHADED, int MASKING, int AO6>
 __global__ void __launch_bounds__(128)
 compose_v4_kernel(const float *__restrict__ low, const float *__restrict__ pred, float *__restrict__ out, ShadeParams sp,
                   float sf, int B, int h, int w, float bg0) {
+  pdl_prologue();
   constexpr int c_low = 12, c_pred = UNSHADED ? (AO6 ? 6 : 5) : 3;
   const int H = 4 * h, W = 4 * w;
   const size_t plane = static_cast<size_t>(H) * W, lplane = static_cast<size_t>(h) * w;
@@ -1093,10 +1099,10 @@ cudaError_t launch_shade(const float *in, const float *params22, float *out, int
   const bool vec = (plane % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
   if (vec) {
     dim3 grid(grid_for(plane / 4, 256), B);
-    shade_kernel<4><<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+    launch_pdl(shade_kernel<4>, grid, dim3(256), 0, s, in, out, sp, sf, B, C, plane);
   } else {
     dim3 grid(grid_for(plane, 256), B);
-    shade_kernel<1><<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+    launch_pdl(shade_kernel<1>, grid, dim3(256), 0, s, in, out, sp, sf, B, C, plane);
   }
   count_launch();
   return cudaGetLastError();
@@ -1109,10 +1115,15 @@ cudaError_t launch_shade_rgb8(const float *in, const float *params22, unsigned c
   const float sf = static_cast<float>((static_cast<double>(expo) + 2.0) / (2.0 * 3.14159265358979323846));
   const size_t plane = static_cast<size_t>(H) * W;
   dim3 grid(grid_for(plane / 4, 256), B);
-  shade_rgb8_kernel<<<grid, 256, 0, s>>>(in, out, sp, sf, B, C, plane);
+  launch_pdl(shade_rgb8_kernel, grid, dim3(256), 0, s, in, out, sp, sf, B, C, plane);
   count_launch();
   return cudaGetLastError();
 }
+// Measured (tools/pdl_experiments.py, in-process A/B): launching the small kernels programmatically makes the configs[4]
+// chunk step 8 % SLOWER (9.9 vs 9.1 ms) and leaves the 1080p graph unchanged: their blocks become resident next to the
+// persistent conv CTA that is still running (it called launch_dependents at its start) and wait there, taking issue slots
+// from an epilogue that is latency-bound.  Off by default; the convolutions keep their own PDL chain.
+int g_pdl_small = 0;
 static int g_compose_variant = 2;   // 1 = scalar kernel, 2 = compose_v4_kernel (4 pixels per thread; 12-channel renders)
 int set_compose_variant(int v) {
   const int old = g_compose_variant;
@@ -1129,7 +1140,7 @@ cudaError_t launch_compose(const float *low, const float *pred, const float *par
   if (g_compose_variant == 2 && c_low == 12 && aligned && (unshaded ? (c_pred == 5 || c_pred == 6) : c_pred == 3)) {
     const size_t threads = static_cast<size_t>(B) * 4 * h * w;
     const unsigned blocks = static_cast<unsigned>((threads + 127) / 128);
-#define ISR_COMPOSE(U, M, A) compose_v4_kernel<U, M, A><<<blocks, 128, 0, s>>>(low, pred, out, sp, sf, B, h, w, bg0)
+#define ISR_COMPOSE(U, M, A) launch_pdl(compose_v4_kernel<U, M, A>, dim3(blocks), dim3(128), 0, s, low, pred, out, sp, sf, B, h, w, bg0)
     if (unshaded && c_pred == 6) { if (masking) ISR_COMPOSE(1, 1, 1); else ISR_COMPOSE(1, 0, 1); }
     else if (unshaded) { if (masking) ISR_COMPOSE(1, 1, 0); else ISR_COMPOSE(1, 0, 0); }
     else { if (masking) ISR_COMPOSE(0, 1, 0); else ISR_COMPOSE(0, 0, 0); }
@@ -1137,7 +1148,8 @@ cudaError_t launch_compose(const float *low, const float *pred, const float *par
     count_launch();
     return cudaGetLastError();
   }
-  compose_kernel<<<B * 4 * h, 256, 0, s>>>(low, pred, out, sp, sf, B, c_low, c_pred, h, w, unshaded, masking, bg0);
+  launch_pdl(compose_kernel, dim3(B * 4 * h), dim3(256), 0, s, low, pred, out, sp, sf, B, c_low, c_pred, h, w, unshaded, masking,
+             bg0);
   count_launch();
   return cudaGetLastError();
 }
@@ -1162,11 +1174,11 @@ cudaError_t launch_pack_recurrent(const float *low, const float *prev, const flo
 #define ISR_PACK2(CPV, NP, BF)                                                                                          \
   do {                                                                                                                  \
     if (vec4)                                                                                                           \
-      pack_recurrent_v2_kernel<CPV, NP, BF, 1><<<grid2, 128, 0, s>>>(low, prev, flow, g0, g1, c_low, h, w, special_mask, \
-                                                                    align_corners);                                     \
+      launch_pdl(pack_recurrent_v2_kernel<CPV, NP, BF, 1>, grid2, dim3(128), 0, s, low, prev, flow, g0, g1, c_low, h, w,   \
+                 special_mask, align_corners);                                                                          \
     else                                                                                                                \
-      pack_recurrent_v2_kernel<CPV, NP, BF, 0><<<grid2, 128, 0, s>>>(low, prev, flow, g0, g1, c_low, h, w, special_mask, \
-                                                                    align_corners);                                     \
+      launch_pdl(pack_recurrent_v2_kernel<CPV, NP, BF, 0>, grid2, dim3(128), 0, s, low, prev, flow, g0, g1, c_low, h, w,   \
+                 special_mask, align_corners);                                                                          \
   } while (0)
     const int sel = (c_prev == 6 ? 4 : 0) + (nparts == 2 ? 2 : 0) + (is_bf16 ? 1 : 0);
     switch (sel) {
@@ -1185,14 +1197,14 @@ cudaError_t launch_pack_recurrent(const float *low, const float *prev, const flo
   }
   dim3 grid((w + kPackLow - 1) / kPackLow, h, B);
   if (c_prev == 6 && small_plane)
-    pack_recurrent_kernel<6><<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
-                                                 align_corners, nparts, is_bf16);
+    launch_pdl(pack_recurrent_kernel<6>, grid, dim3(256), 0, s, low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
+               align_corners, nparts, is_bf16);
   else if (c_prev == 3 && small_plane)
-    pack_recurrent_kernel<3><<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
-                                                 align_corners, nparts, is_bf16);
+    launch_pdl(pack_recurrent_kernel<3>, grid, dim3(256), 0, s, low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
+               align_corners, nparts, is_bf16);
   else
-    pack_recurrent_kernel<0><<<grid, 256, 0, s>>>(low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
-                                                 align_corners, nparts, is_bf16);
+    launch_pdl(pack_recurrent_kernel<0>, grid, dim3(256), 0, s, low, prev, flow, g0, g1, B, c_low, c_prev, h, w, special_mask,
+               align_corners, nparts, is_bf16);
   count_launch();
   return cudaGetLastError();
 }

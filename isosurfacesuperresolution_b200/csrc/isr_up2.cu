@@ -70,6 +70,7 @@ __device__ __forceinline__ void up_src(int dst, int n_in, int &i0, int &i1, floa
 // in: [B][hl][wl][64 * in_parts] 16-bit (first plane used)
 __global__ void band_upsample_kernel(const uint16_t *__restrict__ in, uint16_t *__restrict__ rows, uint16_t *__restrict__ cols,
                                      int B, int hl, int wl, int in_parts, int is_bf16) {
+  pdl_prologue();
   const int H2 = 2 * hl, W2 = 2 * wl;
   const size_t n_row = static_cast<size_t>(B) * 2 * 3 * W2, n_col = static_cast<size_t>(B) * 2 * H2 * 3;
   const size_t total = (n_row + n_col) * 8;   // one thread = 8 channels of one band pixel
@@ -114,6 +115,7 @@ __global__ void band_upsample_kernel(const uint16_t *__restrict__ in, uint16_t *
 // copies the two valid rows / columns of each convolved band over the fused result out[B][H2][W2][64 * out_parts]
 __global__ void band_scatter_kernel(const uint16_t *__restrict__ rows, const uint16_t *__restrict__ cols,
                                     uint16_t *__restrict__ out, int B, int H2, int W2, int parts) {
+  pdl_prologue();
   const size_t cs = static_cast<size_t>(64) * parts;     // 16-bit elements per pixel, same in bands and output
   const size_t n_row = static_cast<size_t>(B) * 2 * 2 * W2, n_col = static_cast<size_t>(B) * 2 * H2 * 2;
   const size_t chunks = cs / 8;
@@ -160,14 +162,14 @@ cudaError_t launch_pack_weights_up2(const float *w, uint16_t *out, cudaStream_t 
 cudaError_t launch_band_upsample(const uint16_t *in, uint16_t *rows, uint16_t *cols, int B, int hl, int wl, int in_parts,
                                  int is_bf16, cudaStream_t s) {
   const size_t total = (static_cast<size_t>(B) * 6 * 2 * wl + static_cast<size_t>(B) * 6 * 2 * hl) * 8;
-  band_upsample_kernel<<<grid_up(total), 256, 0, s>>>(in, rows, cols, B, hl, wl, in_parts, is_bf16);
+  launch_pdl(band_upsample_kernel, dim3(grid_up(total)), dim3(256), 0, s, in, rows, cols, B, hl, wl, in_parts, is_bf16);
   count_launch();
   return cudaGetLastError();
 }
 cudaError_t launch_band_scatter(const uint16_t *rows, const uint16_t *cols, uint16_t *out, int B, int H2, int W2, int parts,
                                 cudaStream_t s) {
   const size_t total = (static_cast<size_t>(B) * 4 * W2 + static_cast<size_t>(B) * 4 * H2) * (8 * parts);
-  band_scatter_kernel<<<grid_up(total), 256, 0, s>>>(rows, cols, out, B, H2, W2, parts);
+  launch_pdl(band_scatter_kernel, dim3(grid_up(total)), dim3(256), 0, s, rows, cols, out, B, H2, W2, parts);
   count_launch();
   return cudaGetLastError();
 }

@@ -13,13 +13,13 @@ net = net.cuda().eval()
 h = net._native()
 res = {}
 for pair in (1, 0):
-    _lib.set_tunable("cta_pair", pair)
+    h.set_tunable("cta_pair", pair)
     for scale in (4, 1):
         for dbg, name in ((0, "full"), (1, "no_stores"), (2, "no_mma"), (6, "no_mma_no_epilogue"), (4, "no_epilogue"), (14, "loads_only_decoupled"), (8, "mma_not_waiting_epilogue")):
             if dbg & 10 and not pair:
                 continue
-            _lib.set_tunable("dbg", dbg)
+            h.set_tunable("dbg", dbg)
             ms = min(h.time_conv(16, 256, 256, "mixed", scale=scale, iters=10) for _ in range(3))
             res[f"pair{pair}_scale{scale}_{name}"] = round(ms * 1e3, 1)
-_lib.set_tunable("dbg", 0); _lib.set_tunable("cta_pair", 1)
+h.set_tunable("dbg", 0); h.set_tunable("cta_pair", 1)
 print(json.dumps(res, indent=1))

@@ -17,8 +17,8 @@ for scale in (4,):
     # (bit 3, "MMA warp does not wait for the epilogue", is unsafe with two issuing warps: tmem_full phases can alias)
     for dbg, name in ((32, "full"), (36, "epilogue_handshake_only"), (48, "no_tma_after_fill"),
                       (52, "no_tma_epilogue_handshake_only"), (2, "no_mma")):
-        _lib.set_tunable("dbg", dbg)
+        h.set_tunable("dbg", dbg)
         ms = min(h.time_conv(16, 256, 256, prec, scale=scale, iters=10) for _ in range(3))
         res[f"scale{scale}_{name}"] = round(ms * 1e3, 1)
-_lib.set_tunable("dbg", 0)
+h.set_tunable("dbg", 0)
 print(json.dumps(res, indent=1))

@@ -13,10 +13,10 @@ net = net.cuda().eval()
 h = net._native()
 res = {}
 for fin in (1, 3):
-    _lib.set_tunable("final_issuers", fin)
+    h.set_tunable("final_issuers", fin)
     for dbg, name in ((0, "full"), (0, "full_again"), (64, "no_stores"), (128, "no_skip_loads"), (192, "no_stores_no_skip")):
-        _lib.set_tunable("dbg", dbg)
+        h.set_tunable("dbg", dbg)
         ms = min(h.time_conv(16, 256, 256, "hybrid", scale=5, iters=10) for _ in range(3))
         res[f"issuers{fin}_{name}"] = round(ms * 1e3, 1)
-_lib.set_tunable("dbg", 0); _lib.set_tunable("final_issuers", 3)
+h.set_tunable("dbg", 0); h.set_tunable("final_issuers", 3)
 print(json.dumps(res, indent=1))
