@@ -402,20 +402,22 @@ def run_b200(args, rank, world, local_rank):
         e2e_sync_value = chunk * H * W * 3 / (time.perf_counter() - t0) / 1e6
         del staging
 
-        # ---- the box's device-to-host ceiling: every rank streams 403 MB blocks into pinned memory AT THE SAME TIME ---
-        n_probe = 403 * 1024 * 1024 // 4
+        # ---- the box's device-to-host ceiling: every rank streams 403 MB blocks into pinned memory AT THE SAME TIME, into
+        # three rotating buffers like the pipeline does (a single reused buffer flatters the host side: 120 instead of
+        # ~100 GB/s aggregate at 8 ranks)
+        n_probe = recon_one.numel()
         src = torch.empty(n_probe, device=dev)
-        dst = recon_one.view(-1)[:n_probe] if recon_one.numel() >= n_probe else torch.empty(n_probe).pin_memory()
-        n_probe = min(n_probe, dst.numel())
-        dst[:n_probe].copy_(src[:n_probe], non_blocking=True)
+        dsts = [recon_one.view(-1)] + [torch.empty(n_probe).pin_memory() for _ in range(2)]
+        for d in dsts:
+            d.copy_(src, non_blocking=True)
         sync_all()
         t0 = time.perf_counter()
-        for _ in range(8):
-            dst[:n_probe].copy_(src[:n_probe], non_blocking=True)
+        for k in range(12):
+            dsts[k % 3].copy_(src, non_blocking=True)
         torch.cuda.synchronize()
-        my_gbs = 8 * n_probe * 4 / (time.perf_counter() - t0) / 1e9
+        my_gbs = 12 * n_probe * 4 / (time.perf_counter() - t0) / 1e9
         d2h_ceiling = sum_over_ranks(my_gbs)
-        del src
+        del src, dsts
 
         # ---- roofline of the dominant kernel (64->64 conv at 4h x 4w), CUDA events on the launching stream ---------
         conv_ms = handle.time_conv(chunk, h, w, PRECISION, scale=4, iters=10)
@@ -459,7 +461,8 @@ def run_b200(args, rank, world, local_rank):
                                      "copies of neighbouring chunks overlap the kernels)",
                     serialised_value=e2e_sync_value, serialised_api="isr_net_forward_recurrent_host (one chunk)",
                     d2h_ceiling_gbs=d2h_ceiling,
-                    d2h_ceiling_how="all ranks copy 403 MB blocks device->pinned host concurrently (sum of the ranks' GB/s)",
+                    d2h_ceiling_how="all ranks copy 403 MB blocks device->pinned host concurrently, three rotating buffers per rank "
+                                    "(sum of the ranks' GB/s)",
                     d2h_frac_of_ceiling=e2e["fp32"]["d2h_gbs_all_ranks"] / d2h_ceiling if d2h_ceiling else None,
                     affinity=affinity,
                     fp16_out=dict(e2e["fp16_out"], api="isr_pipe_submit_f16: the host result is the full prediction rounded "
