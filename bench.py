@@ -75,6 +75,18 @@ def ncu_traffic(kernel, shape_key):
         return None, None
 
 
+def ncu_tensor_activity():
+    """Time-weighted tensor-pipe activity of one recurrent step from the committed ncu pass (profiles/r02_tensor_activity.json:
+    sm__pipe_tensor_subpipe_hmma_cycles_active x gpu__time_duration per launch); a profile, not a live measurement."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_tensor_activity.json")))["configs4_chunk_4x512x512"]
+        return {"conv_stack_pct": d["tensor_pipe_active_pct_time_weighted_conv_stack"],
+                "whole_step_pct": d["tensor_pipe_active_pct_time_weighted_whole_step"],
+                "source": "profiles/r02_tensor_activity.json (ncu, one configs[4] chunk, precision hybrid K=10)"}
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def physical_cores():
     try:
         seen = set()
@@ -480,7 +492,8 @@ def run_b200(args, rank, world, local_rank):
                      "whole_conv_stack": {"algorithmic_tflops": stack_tflops, "frac_of_burst": stack_tflops / peak_tf,
                                           "frac_of_sustained": stack_tflops / peak_tf_sustained,
                                           "how": "272,232 algorithmic FLOP per output px x px per step / ms_per_step "
-                                                 "(the step also holds packing and shading)"}},
+                                                 "(the step also holds packing and shading)",
+                                          "tensor_pipe_active": ncu_tensor_activity()}},
     }
     line.update(extra)
     if latency is not None:

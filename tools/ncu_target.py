@@ -22,6 +22,7 @@ ap.add_argument("--shape", default="4x512x512")
 ap.add_argument("--frames", type=int, default=3)
 ap.add_argument("--precision", default="hybrid")
 ap.add_argument("--compose", action="store_true")
+ap.add_argument("--smooth-flow", action="store_true", help="replace the synthetic flow by its noise-free low-frequency part")
 ap.add_argument("--tunable", action="append", default=[], help="key=value, process-wide tunable set before the net is built")
 args = ap.parse_args()
 for kv in args.tunable:
@@ -40,6 +41,11 @@ shd.specular_light_color(np.array([0.2, 0.2, 0.2])); shd.specular_exponent(16)
 shd.light_direction(np.array([0.1, 0.1, 1.0])); shd.material_color(np.array([1.0, 0.3, 0.0]))
 shd.ambient_occlusion(0.5); shd.background(np.array([0.0, 0.0, 0.0]))
 low_np, flow_np, _ = synthetic.synthetic_gbuffer(1, h, w, 4322, T=2)
+if args.smooth_flow:   # the sinusoid of synthetic.synthetic_gbuffer without the per-pixel uniform noise
+    yy, xx = np.meshgrid(np.linspace(-1, 1, h, dtype=np.float32), np.linspace(-1, 1, w, dtype=np.float32), indexing="ij")
+    for t in range(flow_np.shape[1]):
+        flow_np[0, t, 0] = 0.012 * np.sin(2.1 * xx + 0.3 * t) * np.cos(1.3 * yy)
+        flow_np[0, t, 1] = 0.012 * np.cos(1.7 * xx) * np.sin(2.3 * yy + 0.2 * t)
 low = torch.from_numpy(np.tile(low_np, (B, 1, 1, 1, 1))).cuda()
 flow = torch.from_numpy(np.tile(flow_np, (B, 1, 1, 1, 1))).cuda()
 render = torch.rand(B, 12, h, w, device="cuda")
