@@ -306,6 +306,9 @@ class NetHandle:
         assert len(ts) == 50
         arr = (ctypes.c_void_p * 50)(*[t.data_ptr() for t in ts])
         with torch.cuda.device(self.device):
+            # (re)packing overwrites the buffers every plan reads: drain all streams of the device first -- a
+            # RecurrentPipeline or a forward on a side stream may still be running with the old weights
+            torch.cuda.synchronize(self.device)
             check(lib().isr_net_load_weights(self._net, arr, 50, _stream()))
 
     def workspace(self, B, h, w, precision):
