@@ -43,6 +43,9 @@ struct Tunables {
   int final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
   int final_groups = 3;    // column-stacked output conv: epilogue groups (3 | 4)
   int pdl = 1;             // CTA-pair convs are launched with programmatic stream serialization
+  int trunk_lo8 = 1;       // ISR_PREC_HYBRID: the low activation plane of the fully split trunk convs is 8-bit (e4m3 * 2^6)
+                           // and the A_lo x W correction pass runs as kind::f8f6f4 against e5m2 weights (half the MMA
+                           // time of the fp16 pass); 0 = the fp16 low plane
   int trunk_full_blocks = 10;  // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3).  10 = the whole
                                // trunk: at realistic frame sizes K = 4 does NOT keep the 1e-2 bar (1.04e-2 on frame 0 of a
                                // 2 x 256^2 crop, 7.0e-3 worst over 6 weight seeds; K = 10: 6.7e-3 / 4.6e-3 --
@@ -119,9 +122,41 @@ static int make_w_map(CUtensorMap *m, const void *ptr, int rows, int n, int is_b
   return ISR_OK;
 }
 
+// the 8-bit low plane of an activation tensor with `pitch` bytes per pixel: byte-typed, box = 64 bytes x box_w x box_h
+static int make_act8_map(CUtensorMap *m, const void *ptr, int B, int H, int W, int pitch, int box_w, int box_h) {
+  EncodeTiledFn enc = get_encode();
+  if (enc == nullptr) return fail(ISR_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[4] = {static_cast<cuuint64_t>(pitch), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H),
+                        static_cast<cuuint64_t>(B)};
+  cuuint64_t strides[3] = {static_cast<cuuint64_t>(pitch), static_cast<cuuint64_t>(W) * pitch,
+                           static_cast<cuuint64_t>(H) * W * pitch};
+  cuuint32_t box[4] = {64, static_cast<cuuint32_t>(box_w), static_cast<cuuint32_t>(box_h), 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void *>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ISR_ERR_CUDA, "cuTensorMapEncodeTiled(8-bit activations) failed: %d", (int)r);
+  return ISR_OK;
+}
+// 8-bit weight plane [rows][64] bytes; box = 64 x n rows
+static int make_w8_map(CUtensorMap *m, const void *ptr, int rows, int n) {
+  EncodeTiledFn enc = get_encode();
+  if (enc == nullptr) return fail(ISR_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {64, static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {64};
+  cuuint32_t box[2] = {64, static_cast<cuuint32_t>(n)};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ISR_ERR_CUDA, "cuTensorMapEncodeTiled(8-bit weights) failed: %d", (int)r);
+  return ISR_OK;
+}
+
 // ---- conv launch -----------------------------------------------------------------------------------------------
 struct ConvLaunch {
   CUtensorMap tmA, tmW;
+  CUtensorMap tmA8, tmW8;   // 8-bit low activation plane / 8-bit weight plane (copies of tmA / tmW when unused)
   ConvParams p;
   int n;  // 64 (EPI_STORE16) or 16 (EPI_FINAL)
   int cp = 0;  // > 0: tap-stacked output conv (conv3x3_final_kernel<cp>)
@@ -192,7 +227,9 @@ static int setup_kernel_attrs() {
 // fills geometry, smem plan and tensor maps of one conv launch; epilogue fields are set by the caller
 static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act, int B, int H, int W, int n_act_parts,
                      const void *wpacked, int w_rows_total, int w_row0, int w_row_stride, int n_w_parts, int is_bf16,
-                     int tensor_parts = 0) {
+                     int tensor_parts = 0, int in_pitch = 0, const void *w8 = nullptr) {
+  // in_pitch: bytes per input pixel when it is not 128 * tensor_parts (tensors that carry an 8-bit plane: kLo8Pitch);
+  // w8 != nullptr: the second activation part is that 8-bit plane and the correction pass runs against this 8-bit weight plane
   if (tensor_parts < n_act_parts) tensor_parts = n_act_parts;   // planes stored per pixel (>= planes the MMAs read)
   memset(&L->p, 0, sizeof L->p);
   L->n = n;
@@ -215,6 +252,7 @@ static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act,
   // weight bytes per CTA: the pair kernel keeps half of the B operand per CTA (+ its half of W_hi when stacked)
   size_t w_bytes = align_up(static_cast<size_t>(n_w_parts) * 9 * n * 128, 1024);
   if (L->pair) w_bytes = align_up(static_cast<size_t>(stack ? 3 : n_w_parts) * 9 * (n / 2) * 128, 1024);
+  if (L->pair && stack && w8 != nullptr) w_bytes = align_up(static_cast<size_t>(9) * 2 * (n / 2) * 128 + 9 * (n / 2) * 64, 1024);
   p.stage_bytes = static_cast<int>(align_up(static_cast<size_t>(kPitch) * kHaloH * 128, 1024));
   const size_t avail = kSmemLimit - kStaticSmem - 1024 - w_bytes - 256;
   int stages = static_cast<int>(avail / p.stage_bytes);
@@ -233,9 +271,19 @@ static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act,
     if (cap < 2) cap = 2;
     L->grid = want < cap ? want : cap;
   }
-  int rc = make_act_map(&L->tmA, act, B, H, W, 64 * tensor_parts, kPitch, kHaloH, is_bf16);
+  int rc = make_act_map(&L->tmA, act, B, H, W, in_pitch > 0 ? in_pitch / 2 : 64 * tensor_parts, kPitch, kHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
-  return make_w_map(&L->tmW, wpacked, w_rows_total, L->pair ? n / 2 : n, is_bf16);
+  if ((rc = make_w_map(&L->tmW, wpacked, w_rows_total, L->pair ? n / 2 : n, is_bf16)) != ISR_OK) return rc;
+  L->tmA8 = L->tmA;
+  L->tmW8 = L->tmW;
+  if (w8 != nullptr) {
+    if (!(L->pair && stack && n == 64 && n_act_parts == 2 && in_pitch == kLo8Pitch))
+      return fail(ISR_ERR_UNSUPPORTED, "the 8-bit low plane needs the stacked CTA-pair kernel");
+    p.a_lo8 = 1;
+    if ((rc = make_act8_map(&L->tmA8, act, B, H, W, in_pitch, kPitch, kHaloH)) != ISR_OK) return rc;
+    if ((rc = make_w8_map(&L->tmW8, w8, 9 * 64, 32)) != ISR_OK) return rc;
+  }
+  return ISR_OK;
 }
 
 // fused bilinear-2x-upsample + conv (64 -> 64): act = LOW-res input [B][hl][wl][64 * tensor_parts], wpacked = composite
@@ -264,7 +312,10 @@ static int init_conv_up2(const Tunables &tun, ConvLaunch *L, const void *act, in
   L->grid = want < cap ? want : cap;
   int rc = make_act_map(&L->tmA, act, B, hl, wl, 64 * tensor_parts, kPitch, kHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
-  return make_w_map(&L->tmW, wpacked, 36 * 64, 32, is_bf16);
+  if ((rc = make_w_map(&L->tmW, wpacked, 36 * 64, 32, is_bf16)) != ISR_OK) return rc;
+  L->tmA8 = L->tmA;
+  L->tmW8 = L->tmW;
+  return ISR_OK;
 }
 
 static int final_cp(int cout) { return cout <= 4 ? 4 : (cout <= 6 ? 6 : 8); }
@@ -406,11 +457,11 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = L.pdl ? 1 : 0;
-    if (L.ph == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, L.tmA, L.tmW, L.p));
-    else if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
-    else if (L.n == 16) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 16, EPI_FINAL>, L.tmA, L.tmW, L.p));
-    else if (stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16>, L.tmA, L.tmW, L.p));
-    else ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16>, L.tmA, L.tmW, L.p));
+    if (L.ph == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else if (L.n == 16) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 16, EPI_FINAL>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else if (stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     count_launch();
     return ISR_OK;
   }
@@ -461,6 +512,7 @@ struct Layer {
   float *bias = nullptr;       // npad floats, zero padded
   uint16_t *packed_fin = nullptr;  // output conv only: tap-stacked [fmt 2][part 2][nrows][64]
   uint16_t *packed_fin2 = nullptr; // output conv only: column-stacked [fmt 2][ky 3][part 2][nk][64] (isr_conv_final2.cuh)
+  uint8_t *packed_w8 = nullptr;    // 64 -> 64 trunk layers (1..20): e5m2(W * 2^-6) plane [tap 9][n 64][k 64] for the 8-bit correction pass
   uint16_t *packed_up = nullptr;   // layers 21, 22: composite weights of the fused upsample + conv [fmt 2][phase 4][tap 9][64][64]
   size_t per_fmt() const { return static_cast<size_t>(2) * 9 * G * npad * 64; }
   int rows() const { return 2 * 9 * G * npad; }
@@ -500,10 +552,17 @@ struct isr_net {
 
 namespace isr {
 
+// does this plan keep the 8-bit low plane (320-byte pixels) in its trunk tensors?
+static bool plan_lo8(const isr_net *net, int precision) {
+  return precision == ISR_PREC_HYBRID && net->tun.trunk_lo8 && net->tun.cta_pair && net->tun.stack_w &&
+         net->tun.trunk_full_blocks > 0;
+}
+
 static size_t plan_bytes(const isr_net *net, int B, int h, int w, const Scheme &trunk, const Scheme &tail,
-                         size_t *offs /* 13 offsets */) {
+                         size_t *offs /* 13 offsets */, bool lo8 = false) {
   const size_t P = static_cast<size_t>(B) * h * w;
-  const size_t lo = align_up(P * 128 * (trunk.stream_parts() > trunk.na ? trunk.stream_parts() : trunk.na), 1024);
+  size_t lo = align_up(P * 128 * (trunk.stream_parts() > trunk.na ? trunk.stream_parts() : trunk.na), 1024);
+  if (lo8) lo = align_up(P * kLo8Pitch, 1024);
   const size_t t2 = align_up(P * 4 * 128 * tail.na, 1024);
   const size_t t4 = align_up(P * 16 * 128 * tail.na, 1024);
   size_t o = 0;
@@ -539,17 +598,18 @@ static void set_store(ConvLaunch *L, const float *bias, int relu, const uint16_t
 }
 
 static int conv_for_layer(const Tunables &tun, ConvLaunch *L, const Layer &ly, int g, const uint16_t *act, int B, int H,
-                          int W, const Scheme &sc, int tensor_parts = 0) {
+                          int W, const Scheme &sc, int tensor_parts = 0, int in_pitch = 0, bool a_lo8 = false) {
   const uint16_t *wbase = ly.packed + (sc.bf16 ? 0 : ly.per_fmt());
   return init_conv(tun, L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16,
-                   tensor_parts);
+                   tensor_parts, in_pitch, a_lo8 ? ly.packed_w8 : nullptr);
 }
 
 static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
   if (!get_schemes(precision, &pl->trunk, &pl->tail, &pl->fin_nw))
     return fail(ISR_ERR_ARG, "unknown precision %d", precision);
   size_t offs[13];
-  const size_t need = plan_bytes(net, B, h, w, pl->trunk, pl->tail, offs);
+  const bool lo8 = plan_lo8(net, precision);
+  const size_t need = plan_bytes(net, B, h, w, pl->trunk, pl->tail, offs, lo8);
   if (ws == nullptr || ws_bytes < need)
     return fail(ISR_ERR_WORKSPACE, "workspace too small: %zu < %zu bytes", ws_bytes, need);
   if (reinterpret_cast<uintptr_t>(ws) % 1024 != 0) return fail(ISR_ERR_ARG, "workspace must be 1024-byte aligned");
@@ -570,17 +630,31 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->convs.clear();
   ConvLaunch L;
   int rc;
+  // Trunk tensors (partial, f0, f1, t) of the 8-bit-low-plane form: 320-byte pixels [hi | lo fp16 | lo8].  The fully
+  // split convs read hi + lo8 (the correction pass is an 8-bit MMA), the residual addend reads hi + lo fp16 (the stream
+  // itself keeps its 22 bits), the epilogues write the planes their consumers need.  The network input (in_g0 / in_g1,
+  // written by the packing kernels) keeps the 16-bit low plane: the preblock runs the fp16 correction pass.
+  const int TP = lo8 ? kLo8Pitch : 0;   // pitch of the trunk tensors (0 = 128 * planes)
+  auto pitches = [&](ConvLaunch *c, bool has_add, bool out8) {
+    if (!lo8) return;
+    c->p.out_pitch = TP;
+    if (has_add) c->p.add_pitch = TP;
+    c->p.out_lo8 = out8 ? 1 : 0;
+  };
   // preblock (enhancenet.py:93-95): one launch per 64-channel input group; the second adds the first's partial sums
   if (net->G == 1) {
     if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, nullptr, 0, f0, FS);
+    pitches(&L, false, true);
     pl->convs.push_back(L);
   } else {
     if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, nullptr, 0, nullptr, 0, partial, FS);
+    pitches(&L, false, false);
     pl->convs.push_back(L);
     if ((rc = conv_for_layer(tun, &L, net->layers[0], 1, pl->in_g[1], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, partial, FS, f0, FS);
+    pitches(&L, true, true);
     pl->convs.push_back(L);
   }
   // 10 residual blocks (enhancenet.py:108-112,140-141): f = f + conv(relu(conv(f)))
@@ -593,13 +667,20 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   uint16_t *fc = f0, *fn = f1;
   int pf = FS;   // planes stored in the current stream tensor
   for (int blk = 0; blk < 10; ++blk) {
-    const Scheme &Sb = (hybrid && blk >= K) ? cheap : T;
+    const bool full = !(hybrid && blk >= K);
+    const Scheme &Sb = full ? T : cheap;
     const int pn = hybrid ? ((blk + 1 < K) ? 2 : 1) : FS;
-    if ((rc = conv_for_layer(tun, &L, net->layers[1 + 2 * blk], 0, fc, B, h, w, Sb, pf)) != ISR_OK) return rc;
-    set_store(&L, net->layers[1 + 2 * blk].bias, 1, nullptr, 0, t, Sb.na);
+    const bool a8 = lo8 && full;              // this block's convs read the 8-bit low plane
+    const bool next8 = lo8 && blk + 1 < K;    // ... and so do the next block's: its input needs one
+    const bool last = blk == 9;               // the last output feeds the tail: compact single-plane pixels
+    if ((rc = conv_for_layer(tun, &L, net->layers[1 + 2 * blk], 0, fc, B, h, w, Sb, pf, TP, a8)) != ISR_OK) return rc;
+    set_store(&L, net->layers[1 + 2 * blk].bias, 1, nullptr, 0, t, a8 ? 1 : Sb.na);   // t: hi (+ lo8) suffices with a8
+    pitches(&L, false, a8);
     pl->convs.push_back(L);
-    if ((rc = conv_for_layer(tun, &L, net->layers[2 + 2 * blk], 0, t, B, h, w, Sb)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[2 + 2 * blk], 0, t, B, h, w, Sb, a8 ? 1 : 0, TP, a8)) != ISR_OK) return rc;
     set_store(&L, net->layers[2 + 2 * blk].bias, 0, fc, pf, fn, pn);
+    pitches(&L, true, next8);
+    if (lo8 && last) L.p.out_pitch = 0;       // = 128 * pn
     pl->convs.push_back(L);
     uint16_t *sw = fc; fc = fn; fn = sw;
     pf = pn;
@@ -765,6 +846,7 @@ static int *tunable_slot(Tunables *t, const char *key, int value) {
                                       : bad("final_stacked must be 0 (generic), 1 (tap-stacked), 2 (CTA pair) or 3 (column-stacked)");
   if (strcmp(key, "trunk_full_blocks") == 0)
     return (value >= 0 && value <= 10) ? &t->trunk_full_blocks : bad("trunk_full_blocks must be in [0, 10]");
+  if (strcmp(key, "trunk_lo8") == 0) return (value == 0 || value == 1) ? &t->trunk_lo8 : bad("trunk_lo8 must be 0 or 1");
   if (strcmp(key, "fuse_up") == 0) return (value == 0 || value == 1) ? &t->fuse_up : bad("fuse_up must be 0 or 1");
   if (strcmp(key, "final_issuers") == 0) return (value == 1 || value == 3) ? &t->final_issuers : bad("final_issuers must be 1 or 3");
   if (strcmp(key, "final_groups") == 0) return (value == 3 || value == 4) ? &t->final_groups : bad("final_groups must be 3 or 4");
@@ -1133,6 +1215,11 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
       return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
     }
   }
+  for (int i = 1; i <= 20; ++i)
+    if (cudaMalloc(&net->layers[i].packed_w8, static_cast<size_t>(9) * 64 * 64) != cudaSuccess) {
+      isr_net_destroy(net);
+      return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
+    }
   for (int i = 21; i <= 22; ++i)
     if (cudaMalloc(&net->layers[i].packed_up, static_cast<size_t>(2) * 36 * 4096 * sizeof(uint16_t)) != cudaSuccess) {
       isr_net_destroy(net);
@@ -1160,6 +1247,7 @@ void isr_net_destroy(isr_net *net) {
     if (net->layers[i].packed_fin) cudaFree(net->layers[i].packed_fin);
     if (net->layers[i].packed_fin2) cudaFree(net->layers[i].packed_fin2);
     if (net->layers[i].packed_up) cudaFree(net->layers[i].packed_up);
+    if (net->layers[i].packed_w8) cudaFree(net->layers[i].packed_w8);
   }
   delete net;
 }
@@ -1172,6 +1260,7 @@ int isr_net_load_weights(isr_net *net, const float *const *params, int n_params,
     if (params[2 * i] == nullptr || params[2 * i + 1] == nullptr) return fail(ISR_ERR_ARG, "load_weights: null tensor");
     ISR_CUDA(launch_pack_weights(params[2 * i], ly.packed, ly.cout, ly.cin, ly.npad, ly.G, S(stream)));
     if (ly.packed_up != nullptr) ISR_CUDA(launch_pack_weights_up2(params[2 * i], ly.packed_up, S(stream)));
+    if (ly.packed_w8 != nullptr) ISR_CUDA(launch_pack_weights_lo8(params[2 * i], ly.packed_w8, S(stream)));
     if (ly.packed_fin != nullptr)
       ISR_CUDA(launch_pack_weights_final(params[2 * i], ly.packed_fin, ly.cout, final_cp(ly.cout),
                                          final_rows(final_cp(ly.cout)), S(stream)));
@@ -1190,7 +1279,7 @@ int isr_net_workspace_bytes(const isr_net *net, int B, int h, int w, int precisi
   Scheme t, hs;
   if (net == nullptr || bytes == nullptr || B <= 0 || h <= 0 || w <= 0) return fail(ISR_ERR_ARG, "workspace: bad arguments");
   if (!get_schemes(precision, &t, &hs)) return fail(ISR_ERR_ARG, "unknown precision %d", precision);
-  *bytes = plan_bytes(net, B, h, w, t, hs, nullptr);
+  *bytes = plan_bytes(net, B, h, w, t, hs, nullptr, plan_lo8(net, precision));
   return ISR_OK;
 }
 

@@ -20,6 +20,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include <cuda_fp8.h>
 
 #include "isr_ptx.cuh"
 
@@ -59,7 +60,15 @@ struct ConvParams {
   const float *skip_src;  // low-res fp32 NCHW input, first n_mask channels used
   long long skip_bstride;  // floats between batches of skip_src
   int h_low, w_low;
+  // 8-bit low plane of the split-precision trunk (pair kernel, STACK; 0 everywhere = the 16-bit forms):
+  int a_lo8;              // the second activation part is e4m3(lo * 2^6), 64 B per pixel at byte 256 of the input pixel:
+                          // the A_lo x W correction pass runs as kind::f8f6f4 (K = 32 per MMA) against e5m2(W * 2^-6)
+  int out_pitch;          // bytes per output pixel (0 = 128 * out_parts)
+  int add_pitch;          // bytes per addend pixel (0 = 128 * add_parts)
+  int out_lo8;            // also write e4m3(lo * 2^6) at byte 256 of the output pixel
 };
+constexpr int kLo8ByteOffset = 256;   // pixel layout with an 8-bit plane: [hi 64 x fp16 | lo 64 x fp16 | lo8 64 x e4m3] = 320 B
+constexpr int kLo8Pitch = 320;
 
 __device__ __forceinline__ uint32_t pack2(float a, float b, int is_bf16) {
   if (is_bf16) {
@@ -109,15 +118,18 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
     // behind the tile's MMAs.  ad[pixel j = 2*half+hh][part][2 x 16 B]
     uint32_t ad[4][2][8];
     const bool has_add = p.addend != nullptr;
+    const size_t add_pitch = p.add_pitch > 0 ? p.add_pitch : 128 * p.add_parts;
+    const size_t out_pitch = p.out_pitch > 0 ? p.out_pitch : 128 * p.out_parts;
     if (has_add) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int y = ty * kTileH + 4 * q + j;
         const bool ok = tile_valid && (y < p.H) && (x < p.W);
         const size_t pix = (static_cast<size_t>(b) * p.H + (ok ? y : 0)) * p.W + (ok ? x : 0);
+        const uint8_t *ab = reinterpret_cast<const uint8_t *>(p.addend) + pix * add_pitch + 32 * m;
 #pragma unroll
         for (int ap = 0; ap < 2; ++ap) {
-          if (ap < p.add_parts) ldg_v8(p.addend + pix * (64 * p.add_parts) + ap * 64 + 16 * m, ad[j][ap]);
+          if (ap < p.add_parts) ldg_v8(ab + ap * 128, ad[j][ap]);
         }
       }
     }
@@ -169,15 +181,34 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
           uint32_t hi[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
-          st_global_v8(p.out16 + pix * (64 * p.out_parts) + 16 * m, hi);
-          if (p.out_parts == 2) {
-            uint32_t lo[8];
+          uint8_t *ob = reinterpret_cast<uint8_t *>(p.out16) + pix * out_pitch + 32 * m;
+          st_global_v8(ob, hi);
+          if (p.out_parts == 2 || p.out_lo8) {
+            float2 lf[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float2 h = unpack2(hi[j], p.is_bf16);
-              lo[j] = pack2(f[2 * j] - h.x, f[2 * j + 1] - h.y, p.is_bf16);
+              lf[j] = make_float2(f[2 * j] - h.x, f[2 * j + 1] - h.y);
             }
-            st_global_v8(p.out16 + pix * 128 + 64 + 16 * m, lo);
+            if (p.out_parts == 2) {
+              uint32_t lo[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) lo[j] = pack2(lf[j].x, lf[j].y, p.is_bf16);
+              st_global_v8(ob + 128, lo);
+            }
+            if (p.out_lo8) {   // e4m3(lo * 2^6): the operand of the 8-bit correction pass of the next conv
+              uint32_t l8[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const uint32_t a = __nv_cvt_float2_to_fp8x2(make_float2(lf[2 * j].x * 64.f, lf[2 * j].y * 64.f), __NV_SATFINITE, __NV_E4M3);
+                const uint32_t c = __nv_cvt_float2_to_fp8x2(make_float2(lf[2 * j + 1].x * 64.f, lf[2 * j + 1].y * 64.f), __NV_SATFINITE, __NV_E4M3);
+                l8[j] = a | (c << 16);
+              }
+              // channels 16 m .. 16 m + 15 = 16 bytes at kLo8ByteOffset + 16 m of the pixel (ob already holds + 32 m)
+              asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(ob - 32 * m + kLo8ByteOffset + 16 * m), "r"(l8[0]),
+                           "r"(l8[1]), "r"(l8[2]), "r"(l8[3])
+                           : "memory");
+            }
           }
         }
       }

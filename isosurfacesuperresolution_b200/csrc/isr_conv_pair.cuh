@@ -82,6 +82,18 @@ __device__ __forceinline__ void umma2_f16_k64(uint32_t tmem_d, uint64_t adesc, u
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate_first)
       : "memory");
 }
+// two M256 x N x K32 8-bit MMAs (kind::f8f6f4) covering K = 64 of one tap; always accumulating
+__device__ __forceinline__ void umma2_f8_k64(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t.reg .b64 a1, b1;\n\t"
+      "setp.eq.b32 q, %3, %3;\n\t"
+      "add.s64 a1, %1, 2;\n\t"
+      "add.s64 b1, %2, 2;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, q;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], a1, b1, %3, q;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc)
+      : "memory");
+}
 // arrive on the barrier at this offset in BOTH CTAs when all previously issued MMAs of the pair have completed
 __device__ __forceinline__ void umma2_commit_multicast(uint32_t bar) {
   asm volatile(
@@ -125,7 +137,11 @@ constexpr int kPairThreads = (4 * kPairGroups + 1 + kPairIssuers) * 32;
 template <int STACK, int N = 64, int EPI = EPI_STORE16, int PH = 1>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                    const __grid_constant__ CUtensorMap tmA8, const __grid_constant__ CUtensorMap tmW8,
                     const ConvParams p) {
+  // tmA8 / tmW8: byte-typed maps of the 8-bit low activation plane and the 8-bit weight plane (SWIZZLE_64B), used only
+  // when p.a_lo8 is set (STACK): pass 1 is then A_lo8 x W8 as kind::f8f6f4 -- two K = 32 MMAs per tap instead of four
+  // K = 16 ones, half the shared-memory operand bytes of the fp16 correction pass (profiles/r02_probe_mma4_fp8_lo.json).
   static_assert(N == 64 || N == 16, "N = 64 (hidden layers) or 16 (output conv)");
   static_assert(PH == 1 || (PH == 4 && STACK == 0 && N == 64 && EPI == EPI_STORE16), "PH = 4: single-pass 64-wide layers only");
   extern __shared__ uint8_t smem_raw[];
@@ -135,7 +151,10 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t rank = cluster_ctarank();
 
   constexpr uint32_t kHalfTap = (N / 2) * 128;   // 32 weight rows = 4 KB
-  const uint32_t w_bytes = STACK ? 9 * 3 * kHalfTap : (PH == 4 ? 36 : p.n_w_parts * 9) * kHalfTap;   // per CTA
+  constexpr uint32_t kHalfTap8 = (N / 2) * 64;   // 32 rows of 64 bytes = 2 KB
+  const bool lo8 = STACK && p.a_lo8 != 0;
+  const uint32_t w_bytes = STACK ? (lo8 ? 9 * 2 * kHalfTap + 9 * kHalfTap8 : 9 * 3 * kHalfTap)
+                                 : (PH == 4 ? 36 : p.n_w_parts * 9) * kHalfTap;   // per CTA
   const uint32_t s_w = smem_base;
   const uint32_t s_wy = s_w + 9 * 2 * kHalfTap;   // STACK: Y region after the X region
   const uint32_t s_stage0 = s_w + ((w_bytes + 1023u) & ~1023u);
@@ -189,7 +208,10 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const int row_x = p.w_row0 + (static_cast<int>(rank) * 9 + tap) * p.w_row_stride;   // part = rank
           tma2_load_2d(s_w + tap * 2 * kHalfTap, &tmW, lead_w, 0, row_x);
           tma2_load_2d(s_w + tap * 2 * kHalfTap + kHalfTap, &tmW, lead_w, 0, row_x + N / 2);
-          tma2_load_2d(s_wy + tap * kHalfTap, &tmW, lead_w, 0, p.w_row0 + tap * p.w_row_stride + static_cast<int>(rank) * (N / 2));
+          if (lo8)
+            tma2_load_2d(s_wy + tap * kHalfTap8, &tmW8, lead_w, 0, tap * N + static_cast<int>(rank) * (N / 2));
+          else
+            tma2_load_2d(s_wy + tap * kHalfTap, &tmW, lead_w, 0, p.w_row0 + tap * p.w_row_stride + static_cast<int>(rank) * (N / 2));
         }
       } else {
         const int nblk = PH == 4 ? 36 : p.n_w_parts * 9;   // (part | phase, tap) blocks of N rows
@@ -222,6 +244,9 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t lead_full = mapa_shared(b_full + 8 * s, 0);
           if ((p.dbg & 16) && it >= static_cast<uint32_t>(p.num_stages)) {   // bench experiment: stages are filled once
             mbar_arrive_cluster(lead_full);
+          } else if (lo8 && ap == 1) {   // the 8-bit plane: 64-byte rows at byte 256 of every pixel
+            mbar_arrive_expect_tx_cluster(lead_full, kPitch * kHaloH * 64);
+            tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA8, lead_full, kLo8ByteOffset, tx * kTileW - 1, ty * kTileH - 1, b);
           } else {
             mbar_arrive_expect_tx_cluster(lead_full, kPitch * kHaloH * 128);
             tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA, lead_full, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
@@ -244,6 +269,8 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t idesc2 = make_idesc_f16(256, 2 * N, p.is_bf16);
       const uint64_t b_desc_base = make_smem_desc_sw128(s_w, 1024, 0);
       const uint64_t by_desc_base = make_smem_desc_sw128(s_wy, 1024, 0);
+      const uint64_t by8_desc_base = make_smem_desc_sw64(s_wy, 512);
+      const uint32_t idesc8 = make_idesc_f8(256, N, 0, 1);   // A e4m3, B e5m2
       mbar_wait(b_w, 0);
       const long long c_start = clock64();
       for (int v = mw; v < my_iters * PH; v += kPairIssuers) {   // virtual tile v = PH * i + phase
@@ -264,6 +291,15 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint64_t a_desc0 = make_smem_desc_sw128(a_base, kPitch * 128, 0);
           if (elect_one()) {
             if (p.dbg & 2) {
+            } else if (STACK && lo8 && ap == 1) {
+              // correction pass on the 8-bit planes: the same nine tap windows, 64-byte rows (SWIZZLE_64B)
+              const uint64_t a8_desc0 = make_smem_desc_sw64(a_base, kPitch * 64);
+#pragma unroll
+              for (int tap = 0; tap < 9; ++tap) {
+                const uint64_t adesc = a8_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 64) >> 4);
+                const uint64_t bdesc = by8_desc_base + static_cast<uint64_t>((tap * kHalfTap8) >> 4);
+                umma2_f8_k64(d_tmem, adesc, bdesc, idesc8);
+              }
             } else if constexpr (STACK) {
 #pragma unroll
               for (int tap = 0; tap < 9; ++tap) {

@@ -6,6 +6,7 @@
 // Reference paths are relative to /root/reference/SuperresolutionNetwork.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include <cuda_fp8.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -1003,6 +1004,19 @@ __global__ void pack_weights_kernel(const float *__restrict__ w, uint16_t *__res
   }
 }
 
+// 8-bit weight plane of a 64 -> 64 layer for the A_lo x W correction pass (kind::f8f6f4): e5m2(w * 2^-6), same GEMM-column
+// permutation as pack_weights_kernel, [tap 9][n 64][k 64] bytes.  The activation's low plane is stored as e4m3(lo * 2^6),
+// so the product carries no scale.  e5m2 keeps 2 mantissa bits: the correction term lo x w (2^-11 of the main product) is
+// reproduced to ~10 %, i.e. the pair (hi, lo8) acts like a ~14-bit activation where the fp16 pair gave 22 bits.
+__global__ void pack_weights_lo8_kernel(const float *__restrict__ w, uint8_t *__restrict__ out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 9 * 64 * 64; i += gridDim.x * blockDim.x) {
+    const int k = i & 63, n = (i >> 6) & 63, tap = i >> 12;
+    const int co = 16 * ((n & 7) >> 1) + 2 * (n >> 3) + (n & 1);
+    const float v = w[(static_cast<size_t>(co) * 64 + k) * 9 + tap] * 0.015625f;
+    out[i] = static_cast<uint8_t>(__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E5M2));
+  }
+}
+
 // tap-stacked weights of the output conv (isr_conv_final.cuh): fp32 OIHW [cout][64][3][3] ->
 // [fmt 2][part 2][n = tap*cp + co, padded to nrows][64] 16-bit
 __global__ void pack_weights_final_kernel(const float *__restrict__ w, uint16_t *__restrict__ out, int cout, int cp,
@@ -1248,6 +1262,11 @@ cudaError_t launch_upsample2x(const uint16_t *in, uint16_t *out, int B, int h, i
 }
 cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s) {
   pack_weights_final_kernel<<<(nrows * 64 + 255) / 256, 256, 0, s>>>(w, out, cout, cp, nrows);
+  count_launch();
+  return cudaGetLastError();
+}
+cudaError_t launch_pack_weights_lo8(const float *w, uint8_t *out, cudaStream_t s) {
+  pack_weights_lo8_kernel<<<(9 * 64 * 64 + 255) / 256, 256, 0, s>>>(w, out);
   count_launch();
   return cudaGetLastError();
 }

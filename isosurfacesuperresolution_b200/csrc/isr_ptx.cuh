@@ -215,6 +215,23 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t addr, uint32_t
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+// The same for 64-byte rows (8-bit operands of 64 channels): SWIZZLE_64B (layout type 4), 8-row groups `sbo_bytes` apart.
+// Validated on hardware with tap-shifted start addresses (tools/probe_mma4.cu, profiles/r02_probe_mma4_fp8_lo.json).
+__device__ __forceinline__ uint64_t make_smem_desc_sw64(uint32_t addr, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(4) << 61;
+  return d;
+}
+// Instruction descriptor for kind::f8f6f4 with 8-bit operands: c_format F32 (bit 4), a / b format at bits 7 / 10
+// (0 = E4M3, 1 = E5M2), K-major A and B, N>>3 at bit 17, M>>4 at bit 24.  K = 32 per instruction.
+__host__ __device__ constexpr uint32_t make_idesc_f8(int m, int n, int a_e5m2, int b_e5m2) {
+  return (1u << 4) | (static_cast<uint32_t>(a_e5m2) << 7) | (static_cast<uint32_t>(b_e5m2) << 10) |
+         (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
 // Instruction descriptor for kind::f16 (cute::UMMA::InstrDescriptor): c_format F32 (bit 4), a/b format at bits 7/10
 // (0 = F16, 1 = BF16), K-major A and B (bits 15,16 = 0), N>>3 at bit 17, M>>4 at bit 24.
 __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, int is_bf16) {

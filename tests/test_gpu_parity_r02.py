@@ -455,3 +455,35 @@ def test_output_conv_column_stacked_equals_tap_stacked(isr, weights, shape, vari
     for a, b in zip(outs[3], outs[1]):
         assert torch.isfinite(a).all()
         assert maxabs(a, b) <= 5e-5
+
+
+@pytest.mark.parametrize("seed", [1234, 7, 2024])
+def test_trunk_8bit_low_plane(isr, golden, weights, seed):
+    """The default `hybrid` trunk stores the LOW activation plane as e4m3(lo * 2^6) and runs the A_lo x W correction pass as
+    an 8-bit MMA (kind::f8f6f4 against e5m2(W * 2^-6), tunable trunk_lo8): half the cost of the fp16 pass.  The correction
+    term only needs ~3 bits, so against the fp32 oracle the result must (1) be as good as the fp16-low-plane form, in
+    max-abs and in rms, and (2) recover most of what separates that form from the scheme without any correction pass
+    (K = 0) -- a wrong byte order or scale in the 8-bit path would leave it at the K = 0 level or worse.  (The two forms
+    are NOT compared with each other directly: any trunk difference, however small, re-rolls the fp16 roundings of the
+    tail, which puts a floor of ~5e-4 rms under such a comparison.)"""
+    sd = weights if seed == 1234 else _seeded_reference_weights(101, 6, seed)
+    rng = np.random.RandomState(seed)
+    x = rng.uniform(-1, 1, (1, 101, 96, 128)).astype(np.float32)
+    ref, _ = orc.enhancenet_forward(sd, x, "bilinear", "residual", 5, backend="torch")
+    outs = {}
+    try:
+        for name, lo8, K in (("lo8", 1, 10), ("lo16", 0, 10), ("cheap", 0, 0)):
+            isr._lib.set_tunable("trunk_lo8", lo8)
+            isr._lib.set_tunable("trunk_full_blocks", K)
+            net = _net(isr, sd)
+            with torch.no_grad():
+                outs[name] = net(cu(x))[0].cpu().numpy()
+    finally:
+        isr._lib.set_tunable("trunk_lo8", 1)
+        isr._lib.set_tunable("trunk_full_blocks", 10)
+    e8, e16, ec = (float(np.max(np.abs(outs[k] - ref))) for k in ("lo8", "lo16", "cheap"))
+    r8, r16, rc = (float(np.sqrt(np.mean((outs[k] - ref) ** 2))) for k in ("lo8", "lo16", "cheap"))
+    assert e8 <= 1e-2 and e8 <= 1.15 * e16 + 2e-4, (e8, e16, ec)
+    assert r8 <= 1.1 * r16, (r8, r16, rc)
+    assert rc >= 1.2 * r16 and (rc - r8) >= 0.7 * (rc - r16), (r8, r16, rc)
+    _check_net(torch.from_numpy(outs["lo8"]), ref)
