@@ -227,9 +227,9 @@ static int setup_kernel_attrs() {
 // fills geometry, smem plan and tensor maps of one conv launch; epilogue fields are set by the caller
 static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act, int B, int H, int W, int n_act_parts,
                      const void *wpacked, int w_rows_total, int w_row0, int w_row_stride, int n_w_parts, int is_bf16,
-                     int tensor_parts = 0, int in_pitch = 0, const void *w8 = nullptr) {
-  // in_pitch: bytes per input pixel when it is not 128 * tensor_parts (tensors that carry an 8-bit plane: kLo8Pitch);
-  // w8 != nullptr: the second activation part is that 8-bit plane and the correction pass runs against this 8-bit weight plane
+                     int tensor_parts = 0, const void *act8 = nullptr, const void *w8 = nullptr) {
+  // act8 / w8 != nullptr: the second activation part is the planar 8-bit plane act8 (64 B per pixel) and the correction pass
+  // runs against the 8-bit weight plane w8; `act` is then the planar hi plane (tensor_parts = 1)
   if (tensor_parts < n_act_parts) tensor_parts = n_act_parts;   // planes stored per pixel (>= planes the MMAs read)
   memset(&L->p, 0, sizeof L->p);
   L->n = n;
@@ -271,16 +271,16 @@ static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act,
     if (cap < 2) cap = 2;
     L->grid = want < cap ? want : cap;
   }
-  int rc = make_act_map(&L->tmA, act, B, H, W, in_pitch > 0 ? in_pitch / 2 : 64 * tensor_parts, kPitch, kHaloH, is_bf16);
+  int rc = make_act_map(&L->tmA, act, B, H, W, w8 != nullptr ? 64 : 64 * tensor_parts, kPitch, kHaloH, is_bf16);
   if (rc != ISR_OK) return rc;
   if ((rc = make_w_map(&L->tmW, wpacked, w_rows_total, L->pair ? n / 2 : n, is_bf16)) != ISR_OK) return rc;
   L->tmA8 = L->tmA;
   L->tmW8 = L->tmW;
   if (w8 != nullptr) {
-    if (!(L->pair && stack && n == 64 && n_act_parts == 2 && in_pitch == kLo8Pitch))
+    if (!(L->pair && stack && n == 64 && n_act_parts == 2 && act8 != nullptr))
       return fail(ISR_ERR_UNSUPPORTED, "the 8-bit low plane needs the stacked CTA-pair kernel");
     p.a_lo8 = 1;
-    if ((rc = make_act8_map(&L->tmA8, act, B, H, W, in_pitch, kPitch, kHaloH)) != ISR_OK) return rc;
+    if ((rc = make_act8_map(&L->tmA8, act8, B, H, W, 64, kPitch, kHaloH)) != ISR_OK) return rc;
     if ((rc = make_w8_map(&L->tmW8, w8, 9 * 64, 32)) != ISR_OK) return rc;
   }
   return ISR_OK;
@@ -562,7 +562,7 @@ static size_t plan_bytes(const isr_net *net, int B, int h, int w, const Scheme &
                          size_t *offs /* 13 offsets */, bool lo8 = false) {
   const size_t P = static_cast<size_t>(B) * h * w;
   size_t lo = align_up(P * 128 * (trunk.stream_parts() > trunk.na ? trunk.stream_parts() : trunk.na), 1024);
-  if (lo8) lo = align_up(P * kLo8Pitch, 1024);
+  if (lo8) lo = align_up(P * kLo8Bytes, 1024);   // planar: hi (P x 128 B), lo fp16 (P x 128 B), lo8 (P x 64 B)
   const size_t t2 = align_up(P * 4 * 128 * tail.na, 1024);
   const size_t t4 = align_up(P * 16 * 128 * tail.na, 1024);
   size_t o = 0;
@@ -598,10 +598,10 @@ static void set_store(ConvLaunch *L, const float *bias, int relu, const uint16_t
 }
 
 static int conv_for_layer(const Tunables &tun, ConvLaunch *L, const Layer &ly, int g, const uint16_t *act, int B, int H,
-                          int W, const Scheme &sc, int tensor_parts = 0, int in_pitch = 0, bool a_lo8 = false) {
+                          int W, const Scheme &sc, int tensor_parts = 0, const void *act8 = nullptr) {
   const uint16_t *wbase = ly.packed + (sc.bf16 ? 0 : ly.per_fmt());
   return init_conv(tun, L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16,
-                   tensor_parts, in_pitch, a_lo8 ? ly.packed_w8 : nullptr);
+                   tensor_parts, act8, act8 != nullptr ? ly.packed_w8 : nullptr);
 }
 
 static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
@@ -630,31 +630,39 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   pl->convs.clear();
   ConvLaunch L;
   int rc;
-  // Trunk tensors (partial, f0, f1, t) of the 8-bit-low-plane form: 320-byte pixels [hi | lo fp16 | lo8].  The fully
-  // split convs read hi + lo8 (the correction pass is an 8-bit MMA), the residual addend reads hi + lo fp16 (the stream
-  // itself keeps its 22 bits), the epilogues write the planes their consumers need.  The network input (in_g0 / in_g1,
-  // written by the packing kernels) keeps the 16-bit low plane: the preblock runs the fp16 correction pass.
-  const int TP = lo8 ? kLo8Pitch : 0;   // pitch of the trunk tensors (0 = 128 * planes)
-  auto pitches = [&](ConvLaunch *c, bool has_add, bool out8) {
+  // Trunk tensors (partial, f0, f1, t) of the 8-bit-low-plane form are PLANAR inside their workspace block: hi plane
+  // (P x 128 B), lo fp16 plane (P x 128 B), lo8 plane (P x 64 B).  The fully split convs read hi + lo8 (the correction pass
+  // is an 8-bit MMA), the residual addend reads hi + lo fp16 (the stream itself keeps its 22 bits), the epilogues write the
+  // planes their consumers need.  The network input (in_g0 / in_g1, written by the packing kernels) keeps the interleaved
+  // 16-bit low plane: the preblock runs the fp16 correction pass.
+  const size_t PX = static_cast<size_t>(B) * h * w;
+  auto lo16_of = [&](uint16_t *x) { return reinterpret_cast<uint16_t *>(reinterpret_cast<uint8_t *>(x) + PX * 128); };
+  auto lo8_of = [&](uint16_t *x) { return reinterpret_cast<uint8_t *>(x) + PX * 256; };
+  // planar output: hi always, lo fp16 when `parts` == 2, lo8 when `out8`; planar addend
+  auto planar = [&](ConvLaunch *c, uint16_t *out, int parts, bool out8, const uint16_t *add, int aparts) {
     if (!lo8) return;
-    c->p.out_pitch = TP;
-    if (has_add) c->p.add_pitch = TP;
-    c->p.out_lo8 = out8 ? 1 : 0;
+    c->p.out_pitch = 128;
+    c->p.out_lo16 = parts == 2 ? lo16_of(out) : nullptr;
+    c->p.out_lo8 = out8 ? lo8_of(out) : nullptr;
+    if (add != nullptr) {
+      c->p.add_pitch = 128;
+      c->p.addend_lo = aparts == 2 ? lo16_of(const_cast<uint16_t *>(add)) : nullptr;
+    }
   };
   // preblock (enhancenet.py:93-95): one launch per 64-channel input group; the second adds the first's partial sums
   if (net->G == 1) {
     if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, nullptr, 0, f0, FS);
-    pitches(&L, false, true);
+    planar(&L, f0, FS, true, nullptr, 0);
     pl->convs.push_back(L);
   } else {
     if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, nullptr, 0, nullptr, 0, partial, FS);
-    pitches(&L, false, false);
+    planar(&L, partial, FS, false, nullptr, 0);
     pl->convs.push_back(L);
     if ((rc = conv_for_layer(tun, &L, net->layers[0], 1, pl->in_g[1], B, h, w, T)) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, partial, FS, f0, FS);
-    pitches(&L, true, true);
+    planar(&L, f0, FS, true, partial, FS);
     pl->convs.push_back(L);
   }
   // 10 residual blocks (enhancenet.py:108-112,140-141): f = f + conv(relu(conv(f)))
@@ -672,15 +680,14 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
     const int pn = hybrid ? ((blk + 1 < K) ? 2 : 1) : FS;
     const bool a8 = lo8 && full;              // this block's convs read the 8-bit low plane
     const bool next8 = lo8 && blk + 1 < K;    // ... and so do the next block's: its input needs one
-    const bool last = blk == 9;               // the last output feeds the tail: compact single-plane pixels
-    if ((rc = conv_for_layer(tun, &L, net->layers[1 + 2 * blk], 0, fc, B, h, w, Sb, pf, TP, a8)) != ISR_OK) return rc;
+    // planar tensors are read through their hi plane (tensor_parts 1); interleaved ones carry pf planes per pixel
+    if ((rc = conv_for_layer(tun, &L, net->layers[1 + 2 * blk], 0, fc, B, h, w, Sb, lo8 ? 1 : pf, a8 ? lo8_of(fc) : nullptr)) != ISR_OK) return rc;
     set_store(&L, net->layers[1 + 2 * blk].bias, 1, nullptr, 0, t, a8 ? 1 : Sb.na);   // t: hi (+ lo8) suffices with a8
-    pitches(&L, false, a8);
+    planar(&L, t, a8 ? 1 : Sb.na, a8, nullptr, 0);
     pl->convs.push_back(L);
-    if ((rc = conv_for_layer(tun, &L, net->layers[2 + 2 * blk], 0, t, B, h, w, Sb, a8 ? 1 : 0, TP, a8)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[2 + 2 * blk], 0, t, B, h, w, Sb, lo8 ? 1 : 0, a8 ? lo8_of(t) : nullptr)) != ISR_OK) return rc;
     set_store(&L, net->layers[2 + 2 * blk].bias, 0, fc, pf, fn, pn);
-    pitches(&L, true, next8);
-    if (lo8 && last) L.p.out_pitch = 0;       // = 128 * pn
+    planar(&L, fn, pn, next8, fc, pf);
     pl->convs.push_back(L);
     uint16_t *sw = fc; fc = fn; fn = sw;
     pf = pn;

@@ -61,14 +61,18 @@ struct ConvParams {
   long long skip_bstride;  // floats between batches of skip_src
   int h_low, w_low;
   // 8-bit low plane of the split-precision trunk (pair kernel, STACK; 0 everywhere = the 16-bit forms):
-  int a_lo8;              // the second activation part is e4m3(lo * 2^6), 64 B per pixel at byte 256 of the input pixel:
-                          // the A_lo x W correction pass runs as kind::f8f6f4 (K = 32 per MMA) against e5m2(W * 2^-6)
-  int out_pitch;          // bytes per output pixel (0 = 128 * out_parts)
+  // Tensors of that form are PLANAR: a hi plane (128 B per pixel), a lo fp16 plane (128 B) and a lo8 plane (64 B), each
+  // contiguous (interleaving them in 320-byte pixels made the TMA / L2 fetch the unused plane too: 604 MB of DRAM reads
+  // where 280 MB were needed, and a DRAM-bound 190 us launch).
+  int a_lo8;              // the second activation part is the e4m3(lo * 2^6) plane (tmA8): the A_lo x W correction pass runs
+                          // as kind::f8f6f4 (K = 32 per MMA) against e5m2(W * 2^-6) (tmW8)
+  int out_pitch;          // bytes per output pixel of the hi (+ interleaved lo) plane (0 = 128 * out_parts)
   int add_pitch;          // bytes per addend pixel (0 = 128 * add_parts)
-  int out_lo8;            // also write e4m3(lo * 2^6) at byte 256 of the output pixel
+  uint16_t *out_lo16;     // planar lo fp16 output plane (nullptr: interleaved at +128 B of the output pixel when out_parts == 2)
+  uint8_t *out_lo8;       // planar e4m3(lo * 2^6) output plane, 64 B per pixel (nullptr: none)
+  const uint16_t *addend_lo;   // planar lo fp16 plane of the addend (nullptr: interleaved at +128 B when add_parts == 2)
 };
-constexpr int kLo8ByteOffset = 256;   // pixel layout with an 8-bit plane: [hi 64 x fp16 | lo 64 x fp16 | lo8 64 x e4m3] = 320 B
-constexpr int kLo8Pitch = 320;
+constexpr int kLo8Bytes = 320;   // bytes per pixel of a tensor with all three planes (128 + 128 + 64)
 
 __device__ __forceinline__ uint32_t pack2(float a, float b, int is_bf16) {
   if (is_bf16) {
@@ -127,10 +131,9 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
         const bool ok = tile_valid && (y < p.H) && (x < p.W);
         const size_t pix = (static_cast<size_t>(b) * p.H + (ok ? y : 0)) * p.W + (ok ? x : 0);
         const uint8_t *ab = reinterpret_cast<const uint8_t *>(p.addend) + pix * add_pitch + 32 * m;
-#pragma unroll
-        for (int ap = 0; ap < 2; ++ap) {
-          if (ap < p.add_parts) ldg_v8(ab + ap * 128, ad[j][ap]);
-        }
+        ldg_v8(ab, ad[j][0]);
+        if (p.add_parts == 2)
+          ldg_v8(p.addend_lo != nullptr ? reinterpret_cast<const uint8_t *>(p.addend_lo) + pix * 128 + 32 * m : ab + 128, ad[j][1]);
       }
     }
     mbar_wait_parked(b_tfull + 8 * acc, acc_ph);
@@ -183,7 +186,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
           for (int j = 0; j < 8; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
           uint8_t *ob = reinterpret_cast<uint8_t *>(p.out16) + pix * out_pitch + 32 * m;
           st_global_v8(ob, hi);
-          if (p.out_parts == 2 || p.out_lo8) {
+          if (p.out_parts == 2 || p.out_lo8 != nullptr) {
             float2 lf[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -194,9 +197,9 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
               uint32_t lo[8];
 #pragma unroll
               for (int j = 0; j < 8; ++j) lo[j] = pack2(lf[j].x, lf[j].y, p.is_bf16);
-              st_global_v8(ob + 128, lo);
+              st_global_v8(p.out_lo16 != nullptr ? reinterpret_cast<uint8_t *>(p.out_lo16) + pix * 128 + 32 * m : ob + 128, lo);
             }
-            if (p.out_lo8) {   // e4m3(lo * 2^6): the operand of the 8-bit correction pass of the next conv
+            if (p.out_lo8 != nullptr) {   // e4m3(lo * 2^6): the operand of the 8-bit correction pass of the next conv
               uint32_t l8[4];
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
@@ -204,8 +207,8 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
                 const uint32_t c = __nv_cvt_float2_to_fp8x2(make_float2(lf[2 * j + 1].x * 64.f, lf[2 * j + 1].y * 64.f), __NV_SATFINITE, __NV_E4M3);
                 l8[j] = a | (c << 16);
               }
-              // channels 16 m .. 16 m + 15 = 16 bytes at kLo8ByteOffset + 16 m of the pixel (ob already holds + 32 m)
-              asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(ob - 32 * m + kLo8ByteOffset + 16 * m), "r"(l8[0]),
+              // channels 16 m .. 16 m + 15 = 16 bytes of the pixel's 64-byte row in the lo8 plane
+              asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p.out_lo8 + pix * 64 + 16 * m), "r"(l8[0]),
                            "r"(l8[1]), "r"(l8[2]), "r"(l8[3])
                            : "memory");
             }

@@ -244,9 +244,9 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t lead_full = mapa_shared(b_full + 8 * s, 0);
           if ((p.dbg & 16) && it >= static_cast<uint32_t>(p.num_stages)) {   // bench experiment: stages are filled once
             mbar_arrive_cluster(lead_full);
-          } else if (lo8 && ap == 1) {   // the 8-bit plane: 64-byte rows at byte 256 of every pixel
+          } else if (lo8 && ap == 1) {   // the 8-bit plane: 64-byte rows
             mbar_arrive_expect_tx_cluster(lead_full, kPitch * kHaloH * 64);
-            tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA8, lead_full, kLo8ByteOffset, tx * kTileW - 1, ty * kTileH - 1, b);
+            tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA8, lead_full, 0, tx * kTileW - 1, ty * kTileH - 1, b);
           } else {
             mbar_arrive_expect_tx_cluster(lead_full, kPitch * kHaloH * 128);
             tma2_load_4d(s_stage0 + s * p.stage_bytes, &tmA, lead_full, ap * 64, tx * kTileW - 1, ty * kTileH - 1, b);
