@@ -48,8 +48,8 @@ FLOP_PER_OUT_PX_NET = 272232                        # algorithmic 
 PRECISION = os.environ.get("ISR_PRECISION", "hybrid")
 DTYPE_NAMES = {"mixed": "bf16x3(trunk)+fp16(tail), fp32 accumulate", "bf16x3": "bf16x3", "bf16": "bf16", "fp16": "fp16",
                "fp16x3": "fp16x3", "mixed2": "bf16x3(trunk)+fp16x2(tail)",
-               "hybrid": "fp16 (x3 split operands in the preblock + residual trunk, single-pass 4x tail, hi+lo weights in the "
-                         "output conv), fp32 accumulate"}
+               "hybrid": "fp16 (x3 split operands in the preblock + residual trunk with an 8-bit e4m3 x e5m2 correction pass, "
+                         "single-pass 4x tail, hi+lo weights in the output conv), fp32 accumulate"}
 
 
 def load_weights():

@@ -54,8 +54,9 @@ extern "C" {
 #define ISR_PREC_MIXED4 7      /* fp16 trunk with split weights stacked along N (one N=128 MMA per k-step), fp16 tail */
 #define ISR_PREC_MIXED5 8      /* MIXED4 + the residual stream stored as hi + lo planes (MMAs read hi, the addend is exact) */
 #define ISR_PREC_HYBRID 10     /* fp16: preblock + first K residual blocks fully split (x3), remaining blocks hi activations x split
-                                * weights (one N=128 MMA per k-step), single-pass fp16 tail; K = tunable trunk_full_blocks (4).  DEFAULT of the
-                                * Python front end and of bench.py */
+                                * weights (one N=128 MMA per k-step), single-pass fp16 tail; K = tunable trunk_full_blocks (10 = the
+                                * whole trunk).  In the fully split residual convs the A_lo x W correction pass runs on 8-bit planes
+                                * (e4m3 x e5m2, kind::f8f6f4; tunable trunk_lo8).  DEFAULT of the Python front end and of bench.py */
 #define ISR_PREC_MIXED6 9      /* single-pass fp16 everywhere + hi/lo residual stream */
 
 int isr_version(void);
@@ -294,6 +295,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "stack_w" (0 | [1])              hi/lo weight planes as one N=128 B operand
  *   "pdl" (0 | [1])                  programmatic dependent launch between consecutive convs
  *   "fuse_up" (0 | [1])              bilinear 2x upsample fused into the following conv (four phase convolutions)
+ *   "trunk_lo8" (0 | [1])            ISR_PREC_HYBRID: 8-bit low activation plane + 8-bit (kind::f8f6f4) correction pass in the
+ *                                    fully split trunk convs (0 = fp16 low plane, 25 % more trunk time, same parity)
  *   "trunk_full_blocks" (0..10, [10]) residual blocks of ISR_PREC_HYBRID that run fully split (4 is 11 % faster per
  *                                    step and misses the 1e-2 bar at full frame sizes: profiles/r02_parity_margin.json)
  *   "final_stacked" (0 | 1 | 2 | [3]) output conv: generic / tap-stacked (shared-memory gather) / CTA-pair N=16 /
