@@ -295,6 +295,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "stack_w" (0 | [1])              hi/lo weight planes as one N=128 B operand
  *   "pdl" (0 | [1])                  programmatic dependent launch between consecutive convs
  *   "fuse_up" (0 | [1])              bilinear 2x upsample fused into the following conv (four phase convolutions)
+ *   "up2_wide" (0 | [1])             ... with the two x-phases of an output row stacked as one N = 128 MMA operand
+ *                                    (tensor floor: 64 cycles per two phases instead of 2 x 43); 0 = four N = 64 phases
  *   "trunk_lo8" (0 | [1])            ISR_PREC_HYBRID: 8-bit low activation plane + 8-bit (kind::f8f6f4) correction pass in the
  *                                    fully split trunk convs (0 = fp16 low plane, 25 % more trunk time, same parity)
  *   "trunk_full_blocks" (0..10, [10]) residual blocks of ISR_PREC_HYBRID that run fully split (4 is 11 % faster per

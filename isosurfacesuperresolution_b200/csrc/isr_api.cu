@@ -39,6 +39,7 @@ struct Tunables {
                            // kernel (measured slower: 1.24 vs 0.92 ms), 0 = generic single-CTA N=16 kernel
   int stack_w = 1;         // split-precision 64-wide convs: [W_hi ; W_lo] as one N=128 MMA operand
   int fuse_up = 1;         // bilinear nets: upsample + conv run as one phase-decomposed kernel (isr_up2.cu)
+  int up2_wide = 1;        // ... with the two x-phases of an output row as one N = 128 MMA operand (0: four N = 64 phases)
   int final_w_parts = 0;   // output conv weight planes: 0 = the scheme's choice, 1 = single, 2 = hi + lo
   int final_issuers = 3;   // MMA-issuing warps of the tap-stacked output conv (1 | 3)
   int final_groups = 3;    // column-stacked output conv: epilogue groups (3 | 4)
@@ -163,7 +164,7 @@ struct ConvLaunch {
   int final2 = 0;  // 1: column-stacked output conv (conv3x3_final2_kernel<cp>)
   int groups = 3;  // conv3x3_final2_kernel: epilogue groups (= accumulator buffers = MMA-issuing warps), 3 | 4
   int pair = 0;  // 1: CTA-pair kernel (conv3x3_pair_kernel)
-  int ph = 1;    // 4: fused upsample + conv (four output phases per low-res tile)
+  int ph = 1;    // fused upsample + conv: 4 = four N=64 output phases per low-res tile, 2 = two N=128 phase pairs
   int stack = 0; // split weights stacked as one N=128 operand
   int pdl = 1;   // programmatic dependent launch
   size_t smem;
@@ -206,8 +207,11 @@ static int setup_kernel_attrs() {
   ISR_CUDA(set_max_smem(conv3x3_umma_kernel<16, EPI_FINAL, 0>));
   ISR_CUDA(set_max_smem(conv3x3_umma_kernel<16, EPI_FINAL, 1>));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0>));
+  ISR_CUDA(set_max_smem((conv3x3_pair_kernel<0, 64, EPI_STORE16, 1, false>)));
+  ISR_CUDA(set_max_smem((conv3x3_pair_kernel<1, 64, EPI_STORE16, 1, false>)));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<1>));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>));
+  ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 64, EPI_STORE16, 2>));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 16, EPI_FINAL>));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<1, 16, EPI_FINAL>));
   ISR_CUDA(set_max_smem(conv3x3_final_kernel<4>));
@@ -291,7 +295,7 @@ static int init_conv(const Tunables &tun, ConvLaunch *L, int n, const void *act,
 static int init_conv_up2(const Tunables &tun, ConvLaunch *L, const void *act, int B, int hl, int wl, int tensor_parts,
                          const void *wpacked, int is_bf16) {
   memset(&L->p, 0, sizeof L->p);
-  L->n = 64; L->cp = 0; L->final2 = 0; L->pair = 1; L->ph = 4; L->stack = 0; L->pdl = tun.pdl;
+  L->n = 64; L->cp = 0; L->final2 = 0; L->pair = 1; L->ph = tun.up2_wide ? 2 : 4; L->stack = 0; L->pdl = tun.pdl;
   ConvParams &p = L->p;
   p.B = B; p.H = hl; p.W = wl;
   p.tiles_x = (wl + kTileW - 1) / kTileW;
@@ -457,10 +461,13 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = L.pdl ? 1 : 0;
-    if (L.ph == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    if (L.ph == 2) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 2>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else if (L.ph == 4) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else if (L.n == 16) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 16, EPI_FINAL>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else if (stack && L.p.addend == nullptr && !(L.p.dbg & 2048)) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16, 1, false>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else if (stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else if (L.p.addend == nullptr && !(L.p.dbg & 2048)) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 1, false>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     count_launch();
     return ISR_OK;
@@ -855,6 +862,7 @@ static int *tunable_slot(Tunables *t, const char *key, int value) {
     return (value >= 0 && value <= 10) ? &t->trunk_full_blocks : bad("trunk_full_blocks must be in [0, 10]");
   if (strcmp(key, "trunk_lo8") == 0) return (value == 0 || value == 1) ? &t->trunk_lo8 : bad("trunk_lo8 must be 0 or 1");
   if (strcmp(key, "fuse_up") == 0) return (value == 0 || value == 1) ? &t->fuse_up : bad("fuse_up must be 0 or 1");
+  if (strcmp(key, "up2_wide") == 0) return (value == 0 || value == 1) ? &t->up2_wide : bad("up2_wide must be 0 or 1");
   if (strcmp(key, "final_issuers") == 0) return (value == 1 || value == 3) ? &t->final_issuers : bad("final_issuers must be 1 or 3");
   if (strcmp(key, "final_groups") == 0) return (value == 3 || value == 4) ? &t->final_groups : bad("final_groups must be 3 or 4");
   if (strcmp(key, "final_w_parts") == 0)
@@ -1538,13 +1546,15 @@ void isr_pipe_destroy(isr_pipe *p) {
 
 int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scale, void *workspace,
                       size_t workspace_bytes, int iters, float *ms, void *stream) {
-  if (ms == nullptr || iters <= 0 || (scale != 1 && scale != 4 && scale != 5)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");
+  if (ms == nullptr || iters <= 0 || (scale != 1 && scale != 3 && scale != 4 && scale != 5)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");
   Plan *pl = nullptr;
   int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
   if (rc != ISR_OK) return rc;
   // scale 4: postblock.4 (64->64 at 4h x 4w, the dominant kernel); scale 1: first residual-block conv (h x w)
   // scale 5: the output conv, writing into scratch (c4) with the packed-input buffer standing in for the skip source
-  ConvLaunch L = pl->convs[scale == 5 ? pl->idx_final : (scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1))];
+  // scale 3: the fused upsample + conv launch that produces the 4h x 4w tensor (needs a bilinear net)
+  if (scale == 3 && !pl->fuse4.on) return fail(ISR_ERR_UNSUPPORTED, "time_conv: this plan has no fused upsample + conv");
+  ConvLaunch L = scale == 3 ? pl->fuse4.up : pl->convs[scale == 5 ? pl->idx_final : (scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1))];
   if (scale == 5) {
     const size_t n_out = static_cast<size_t>(B) * net->cout * 16 * h * w;
     L.p.out_recon = reinterpret_cast<float *>(pl->c4);

@@ -104,7 +104,7 @@ __device__ __forceinline__ void bil_src(int dst, int n_in, float inv_scale, int 
 // Epilogue of a 64-wide layer for one 8x16 tile (one warp = TMEM lanes 32q..32q+31): waits for the accumulator, then
 // bias (+ residual addend) (+ ReLU) -> 16-bit NHWC hi (and lo) planes.  Shared by the single-CTA and the CTA-pair kernel.
 // thread (m = lane%4, rr = lane/4): pixel column rr of image rows 4q..4q+3 of the tile, channels 16m..16m+15
-template <int N, int STACK>
+template <int N, int STACK, bool ADD = true>   // ADD = false: the layer never has a residual addend (frees its 64 registers)
 __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const float *s_bias, uint32_t taddr, int q, int lane,
                                                  int b, int ty, int tx, bool tile_valid, uint32_t bar_tfull,
                                                  uint32_t acc_ph, int omul = 1, int oyadd = 0, int oxadd = 0) {
@@ -121,7 +121,7 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
     // residual addend (the block's skip): fetched BEFORE waiting for the accumulator, so its HBM latency hides
     // behind the tile's MMAs.  ad[pixel j = 2*half+hh][part][2 x 16 B]
     uint32_t ad[4][2][8];
-    const bool has_add = p.addend != nullptr;
+    const bool has_add = ADD && p.addend != nullptr;
     const size_t add_pitch = p.add_pitch > 0 ? p.add_pitch : 128 * p.add_parts;
     const size_t out_pitch = p.out_pitch > 0 ? p.out_pitch : 128 * p.out_parts;
     if (has_add) {

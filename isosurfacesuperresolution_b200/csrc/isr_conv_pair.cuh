@@ -134,7 +134,14 @@ constexpr int kPairThreads = (4 * kPairGroups + 1 + kPairIssuers) * 32;
 // PH = 4: fused bilinear-2x-upsample + conv (isr_up2.cu): every low-res tile is convolved four times, once per output
 // phase (py, px), with that phase's composite weights; the four results are four "virtual tiles" v = 4*i + phase that
 // share the tile's halo stage, each with its own accumulator buffer (8 buffers) and its own strided output pixels.
-template <int STACK, int N = 64, int EPI = EPI_STORE16, int PH = 1>
+// PH = 2 (the default form of that layer): the same, with the two x-phases of an output row stacked along N -- the A
+// window of a tap is the same for all four phases, so [W'(py,0) ; W'(py,1)] is ONE N = 128 operand (leader holds the
+// px = 0 rows, the peer the px = 1 rows, as the split-precision stack does): 64 cycles per k16-step for two phases, the
+// tensor floor, instead of 2 x 43 (an N = 64 pair-MMA is bound by its shared-memory operand reads).  Two virtual tiles
+// v = 2*i + py per low-res tile, four 128-column accumulator buffers; the epilogue drains columns 0..63 to output pixel
+// (2y+py, 2x) and 64..127 to (2y+py, 2x+1).
+// ADD = false: an instance for layers without a residual addend (its prefetch registers are not allocated).
+template <int STACK, int N = 64, int EPI = EPI_STORE16, int PH = 1, bool ADD = true>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const __grid_constant__ CUtensorMap tmA8, const __grid_constant__ CUtensorMap tmW8,
@@ -143,7 +150,9 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // when p.a_lo8 is set (STACK): pass 1 is then A_lo8 x W8 as kind::f8f6f4 -- two K = 32 MMAs per tap instead of four
   // K = 16 ones, half the shared-memory operand bytes of the fp16 correction pass (profiles/r02_probe_mma4_fp8_lo.json).
   static_assert(N == 64 || N == 16, "N = 64 (hidden layers) or 16 (output conv)");
-  static_assert(PH == 1 || (PH == 4 && STACK == 0 && N == 64 && EPI == EPI_STORE16), "PH = 4: single-pass 64-wide layers only");
+  static_assert(PH == 1 || ((PH == 4 || PH == 2) && STACK == 0 && N == 64 && EPI == EPI_STORE16), "PH = 4 / 2: single-pass 64-wide layers only");
+  constexpr bool kUp = PH != 1;     // fused upsample + conv
+  constexpr bool kWide = PH == 2;   // ... with two phases per MMA (N = 128)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5;
@@ -154,7 +163,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr uint32_t kHalfTap8 = (N / 2) * 64;   // 32 rows of 64 bytes = 2 KB
   const bool lo8 = STACK && p.a_lo8 != 0;
   const uint32_t w_bytes = STACK ? (lo8 ? 9 * 2 * kHalfTap + 9 * kHalfTap8 : 9 * 3 * kHalfTap)
-                                 : (PH == 4 ? 36 : p.n_w_parts * 9) * kHalfTap;   // per CTA
+                                 : (kUp ? 36 : p.n_w_parts * 9) * kHalfTap;   // per CTA
   const uint32_t s_w = smem_base;
   const uint32_t s_wy = s_w + 9 * 2 * kHalfTap;   // STACK: Y region after the X region
   const uint32_t s_stage0 = s_w + ((w_bytes + 1023u) & ~1023u);
@@ -171,7 +180,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmW);
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(b_full + 8 * s, 2);    // used in the leader: one arrive.expect_tx per CTA
-      mbar_init(b_empty + 8 * s, PH == 4 ? 2 : 1);   // per CTA: multicast commit (PH = 4: one per issuing warp)
+      mbar_init(b_empty + 8 * s, kUp ? 2 : 1);   // per CTA: multicast commit (fused upsample: one per issuing warp)
     }
     mbar_init(b_w, 2);
     for (int a = 0; a < NB; ++a) {
@@ -180,7 +189,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     fence_barrier_init();
   }
-  constexpr uint32_t kAccCols = STACK ? 2 * N : N;
+  constexpr uint32_t kAccCols = (STACK || kWide) ? 2 * N : N;
   constexpr uint32_t kTmemCols = (NB * kAccCols <= 64) ? 64 : (NB * kAccCols <= 128) ? 128 : ((NB * kAccCols <= 256) ? 256 : 512);
   static_assert(NB * kAccCols <= 512 && NB % G == 0, "accumulator buffers exceed TMEM");
   if (warp == kMmaWarp) tmem_alloc2(s_tptr, kTmemCols);
@@ -212,6 +221,16 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             tma2_load_2d(s_wy + tap * kHalfTap8, &tmW8, lead_w, 0, tap * N + static_cast<int>(rank) * (N / 2));
           else
             tma2_load_2d(s_wy + tap * kHalfTap, &tmW, lead_w, 0, p.w_row0 + tap * p.w_row_stride + static_cast<int>(rank) * (N / 2));
+        }
+      } else if constexpr (kWide) {
+        // this CTA keeps all 64 rows of the phases with px = rank: block (py, tap) = 8 KB at (py * 9 + tap) * 8 KB
+        for (int j = 0; j < 36; ++j) {
+          const int phase = j / 9, tap = j - 9 * phase;
+          if ((phase & 1) != static_cast<int>(rank)) continue;
+          const uint32_t dst = s_w + static_cast<uint32_t>(((phase >> 1) * 9 + tap) * 2) * kHalfTap;
+          const int row = p.w_row0 + j * p.w_row_stride;
+          tma2_load_2d(dst, &tmW, lead_w, 0, row);
+          tma2_load_2d(dst + kHalfTap, &tmW, lead_w, 0, row + N / 2);
         }
       } else {
         const int nblk = PH == 4 ? 36 : p.n_w_parts * 9;   // (part | phase, tap) blocks of N rows
@@ -314,8 +333,8 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                 for (int tap = 0; tap < 9; ++tap) {
                   const uint64_t adesc = a_desc0 + static_cast<uint64_t>((((tap / 3) * kPitch + (tap % 3)) * 128) >> 4);
-                  const uint64_t bdesc = b_desc_base + static_cast<uint64_t>((((PH == 4 ? phase : wp) * 9 + tap) * kHalfTap) >> 4);
-                  umma2_f16_k64(d_tmem, adesc, bdesc, idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
+                  const uint64_t bdesc = b_desc_base + static_cast<uint64_t>((((kUp ? phase : wp) * 9 + tap) * (kWide ? 2 : 1) * kHalfTap) >> 4);
+                  umma2_f16_k64(d_tmem, adesc, bdesc, kWide ? idesc2 : idesc, (tap == 0) ? (first ? 0u : 1u) : 1u);
                 }
                 first = 0;
               }
@@ -360,8 +379,12 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t acc = v % NB;
       const uint32_t acc_ph = (v / NB) & 1;
       const uint32_t taddr = tmem_base + acc * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
-      if constexpr (EPI == EPI_STORE16)
-        epilogue_store16<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph,
+      if constexpr (kWide) {
+#pragma unroll 1   // one copy of the epilogue body (two inlined copies push its arrays into local memory)
+        for (int u = 0; u < 2; ++u)
+          epilogue_store16<N, 0, false>(p, s_bias, taddr + u * N, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph, 2, phase, u);
+      } else if constexpr (EPI == EPI_STORE16)
+        epilogue_store16<N, STACK, ADD>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph,
                                    PH == 4 ? 2 : 1, PH == 4 ? (phase >> 1) : 0, PH == 4 ? (phase & 1) : 0);
       else
         epilogue_final<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);

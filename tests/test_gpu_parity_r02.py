@@ -487,3 +487,26 @@ def test_trunk_8bit_low_plane(isr, golden, weights, seed):
     assert r8 <= 1.1 * r16, (r8, r16, rc)
     assert rc >= 1.2 * r16 and (rc - r8) >= 0.7 * (rc - r16), (r8, r16, rc)
     _check_net(torch.from_numpy(outs["lo8"]), ref)
+
+
+@pytest.mark.parametrize("shape", [(1, 16, 20), (2, 19, 27), (1, 33, 130), (1, 270, 480)])
+def test_fused_upsample_wide_equals_four_phase(isr, weights, shape):
+    """The fused upsample + conv layers issue the two x-phases of an output row as ONE N = 128 MMA operand (tunable
+    up2_wide = 1, the default: conv3x3_pair_kernel<0, 64, 0, 2>) instead of four N = 64 phase convolutions (up2_wide = 0):
+    the same products accumulated in the same order, so the network output is bit-identical -- on ragged tiles, on a
+    frame with an odd number of tile pairs and at 1080p / 4."""
+    from isosurfacesuperresolution_b200 import _lib
+    B, h, w = shape
+    g = torch.Generator(device="cuda").manual_seed(17)
+    x = torch.rand(B, 101, h, w, device="cuda", generator=g) * 2 - 1
+    outs = {}
+    try:
+        for wide in (1, 0):
+            _lib.set_tunable("up2_wide", wide)
+            net = _net(isr, weights)
+            with torch.no_grad():
+                outs[wide] = net(x)[0].clone()
+    finally:
+        _lib.set_tunable("up2_wide", 1)
+    assert torch.isfinite(outs[1]).all()
+    assert torch.equal(outs[1], outs[0])
