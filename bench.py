@@ -284,14 +284,16 @@ def run_b200(args, rank, world, local_rank):
     # ---- one workload: device-resident value + end-to-end through the host pipeline --------------------------------
     def measure(wl, steps, warmup, e2e_variants, sample_clocks):
         B, chunk, h, w = wl["B"], wl["chunk"], wl["h"], wl["w"]
+        if os.environ.get("ISR_BENCH_CHUNK"):      # experiment: another chunking of the same workload
+            chunk = int(os.environ["ISR_BENCH_CHUNK"])
         n_chunks = B // chunk
         H, W = 4 * h, 4 * w
         out_px_per_step = B * H * W
         # 2 distinct sequences generated on the host and tiled to one chunk (generation cost only), per-rank seed; every
         # chunk of the rank reads the same low / flow tensors and owns its own recurrent state
         low_np, flow_np, _ = synthetic.synthetic_gbuffer(2, h, w, sharding.rank_seed(4321 + 1, rank), T=T)
-        low = torch.from_numpy(np.tile(low_np, (chunk // 2, 1, 1, 1, 1))).to(dev)
-        flow = torch.from_numpy(np.tile(flow_np, (chunk // 2, 1, 1, 1, 1))).to(dev)
+        low = torch.from_numpy(np.tile(low_np, ((chunk + 1) // 2, 1, 1, 1, 1))[:chunk]).to(dev)
+        flow = torch.from_numpy(np.tile(flow_np, ((chunk + 1) // 2, 1, 1, 1, 1))[:chunk]).to(dev)
         res = {}
         with torch.no_grad():
             inp0 = low[:, 0].contiguous()

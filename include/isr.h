@@ -299,6 +299,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *                                    (tensor floor: 64 cycles per two phases instead of 2 x 43); 0 = four N = 64 phases
  *   "trunk_lo8" (0 | [1])            ISR_PREC_HYBRID: 8-bit low activation plane + 8-bit (kind::f8f6f4) correction pass in the
  *                                    fully split trunk convs (0 = fp16 low plane, 25 % more trunk time, same parity)
+ *   "stream_lo8" (0 | [1])           with trunk_lo8: the residual stream is stored as hi + that 8-bit low plane only (0 = it
+ *                                    also carries an fp16 low plane for the residual addend: +67 % stream traffic)
  *   "trunk_full_blocks" (0..10, [10]) residual blocks of ISR_PREC_HYBRID that run fully split (4 is 11 % faster per
  *                                    step and misses the 1e-2 bar at full frame sizes: profiles/r02_parity_margin.json)
  *   "final_stacked" (0 | 1 | 2 | [3]) output conv: generic / tap-stacked (shared-memory gather) / CTA-pair N=16 /

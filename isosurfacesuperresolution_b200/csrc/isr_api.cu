@@ -47,6 +47,9 @@ struct Tunables {
   int trunk_lo8 = 1;       // ISR_PREC_HYBRID: the low activation plane of the fully split trunk convs is 8-bit (e4m3 * 2^6)
                            // and the A_lo x W correction pass runs as kind::f8f6f4 against e5m2 weights (half the MMA
                            // time of the fp16 pass); 0 = the fp16 low plane
+  int stream_lo8 = 1;      // with trunk_lo8: the residual stream itself is kept as hi + the 8-bit low plane (the planes the convs
+                           // read anyway); 0 = it also carries an fp16 low plane for the residual addend (320 instead of
+                           // 192 B per pixel and tensor: the convs with an addend were HBM-bound, 156 vs 119 us)
   int trunk_full_blocks = 10;  // ISR_PREC_HYBRID: residual blocks (and the preblock) that run fully split (x3).  10 = the whole
                                // trunk: at realistic frame sizes K = 4 does NOT keep the 1e-2 bar (1.04e-2 on frame 0 of a
                                // 2 x 256^2 crop, 7.0e-3 worst over 6 weight seeds; K = 10: 6.7e-3 / 4.6e-3 --
@@ -646,14 +649,27 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   auto lo16_of = [&](uint16_t *x) { return reinterpret_cast<uint16_t *>(reinterpret_cast<uint8_t *>(x) + PX * 128); };
   auto lo8_of = [&](uint16_t *x) { return reinterpret_cast<uint8_t *>(x) + PX * 256; };
   // planar output: hi always, lo fp16 when `parts` == 2, lo8 when `out8`; planar addend
+  const bool s8 = lo8 && tun.stream_lo8;   // two-plane stream tensors are hi + lo8 (no fp16 low plane)
   auto planar = [&](ConvLaunch *c, uint16_t *out, int parts, bool out8, const uint16_t *add, int aparts) {
     if (!lo8) return;
     c->p.out_pitch = 128;
-    c->p.out_lo16 = parts == 2 ? lo16_of(out) : nullptr;
-    c->p.out_lo8 = out8 ? lo8_of(out) : nullptr;
+    if (s8 && parts == 2) {
+      c->p.out_parts = 1;
+      c->p.out_lo16 = nullptr;
+      c->p.out_lo8 = lo8_of(out);
+    } else {
+      c->p.out_lo16 = parts == 2 ? lo16_of(out) : nullptr;
+      c->p.out_lo8 = out8 ? lo8_of(out) : nullptr;
+    }
     if (add != nullptr) {
       c->p.add_pitch = 128;
-      c->p.addend_lo = aparts == 2 ? lo16_of(const_cast<uint16_t *>(add)) : nullptr;
+      if (s8 && aparts == 2) {
+        c->p.add_parts = 1;
+        c->p.addend_lo = nullptr;
+        c->p.addend_lo8 = lo8_of(const_cast<uint16_t *>(add));
+      } else {
+        c->p.addend_lo = aparts == 2 ? lo16_of(const_cast<uint16_t *>(add)) : nullptr;
+      }
     }
   };
   // preblock (enhancenet.py:93-95): one launch per 64-channel input group; the second adds the first's partial sums
@@ -862,6 +878,7 @@ static int *tunable_slot(Tunables *t, const char *key, int value) {
     return (value >= 0 && value <= 10) ? &t->trunk_full_blocks : bad("trunk_full_blocks must be in [0, 10]");
   if (strcmp(key, "trunk_lo8") == 0) return (value == 0 || value == 1) ? &t->trunk_lo8 : bad("trunk_lo8 must be 0 or 1");
   if (strcmp(key, "fuse_up") == 0) return (value == 0 || value == 1) ? &t->fuse_up : bad("fuse_up must be 0 or 1");
+  if (strcmp(key, "stream_lo8") == 0) return (value == 0 || value == 1) ? &t->stream_lo8 : bad("stream_lo8 must be 0 or 1");
   if (strcmp(key, "up2_wide") == 0) return (value == 0 || value == 1) ? &t->up2_wide : bad("up2_wide must be 0 or 1");
   if (strcmp(key, "final_issuers") == 0) return (value == 1 || value == 3) ? &t->final_issuers : bad("final_issuers must be 1 or 3");
   if (strcmp(key, "final_groups") == 0) return (value == 3 || value == 4) ? &t->final_groups : bad("final_groups must be 3 or 4");
@@ -1546,7 +1563,7 @@ void isr_pipe_destroy(isr_pipe *p) {
 
 int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scale, void *workspace,
                       size_t workspace_bytes, int iters, float *ms, void *stream) {
-  if (ms == nullptr || iters <= 0 || (scale != 1 && scale != 3 && scale != 4 && scale != 5)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");
+  if (ms == nullptr || iters <= 0 || (scale < 1 || scale > 5)) return fail(ISR_ERR_ARG, "time_conv: bad arguments");
   Plan *pl = nullptr;
   int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
   if (rc != ISR_OK) return rc;
@@ -1554,7 +1571,8 @@ int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scal
   // scale 5: the output conv, writing into scratch (c4) with the packed-input buffer standing in for the skip source
   // scale 3: the fused upsample + conv launch that produces the 4h x 4w tensor (needs a bilinear net)
   if (scale == 3 && !pl->fuse4.on) return fail(ISR_ERR_UNSUPPORTED, "time_conv: this plan has no fused upsample + conv");
-  ConvLaunch L = scale == 3 ? pl->fuse4.up : pl->convs[scale == 5 ? pl->idx_final : (scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1))];
+  // scale 2: the second conv of the first residual block (h x w, with the residual addend)
+  ConvLaunch L = scale == 3 ? pl->fuse4.up : pl->convs[scale == 5 ? pl->idx_final : (scale == 4 ? pl->idx_post4 : (net->G == 2 ? 2 : 1) + (scale == 2 ? 1 : 0))];
   if (scale == 5) {
     const size_t n_out = static_cast<size_t>(B) * net->cout * 16 * h * w;
     L.p.out_recon = reinterpret_cast<float *>(pl->c4);

@@ -71,6 +71,8 @@ struct ConvParams {
   uint16_t *out_lo16;     // planar lo fp16 output plane (nullptr: interleaved at +128 B of the output pixel when out_parts == 2)
   uint8_t *out_lo8;       // planar e4m3(lo * 2^6) output plane, 64 B per pixel (nullptr: none)
   const uint16_t *addend_lo;   // planar lo fp16 plane of the addend (nullptr: interleaved at +128 B when add_parts == 2)
+  const uint8_t *addend_lo8;   // planar e4m3(lo * 2^6) plane of the addend (add_parts == 1): the residual stream kept as
+                               // hi + 8-bit lo, the very planes the convs read (192 instead of 320 B per pixel and tensor)
 };
 constexpr int kLo8Bytes = 320;   // bytes per pixel of a tensor with all three planes (128 + 128 + 64)
 
@@ -134,6 +136,10 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
         ldg_v8(ab, ad[j][0]);
         if (p.add_parts == 2)
           ldg_v8(p.addend_lo != nullptr ? reinterpret_cast<const uint8_t *>(p.addend_lo) + pix * 128 + 32 * m : ab + 128, ad[j][1]);
+        else if (p.addend_lo8 != nullptr)
+          asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(ad[j][1][0]), "=r"(ad[j][1][1]), "=r"(ad[j][1][2]), "=r"(ad[j][1][3])
+                       : "l"(p.addend_lo8 + pix * 64 + 16 * m));
       }
     }
     mbar_wait_parked(b_tfull + 8 * acc, acc_ph);
@@ -175,6 +181,20 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
                   f[2 * j + 1] += a.y;
                 }
               }
+            }
+          }
+          if (has_add && p.add_parts == 1 && p.addend_lo8 != nullptr) {
+            const uint32_t *w = ad[2 * half + hh][1];   // 16 e4m3 bytes = lo * 2^6 of channels 16 m .. 16 m + 15
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const __half2_raw h01 = __nv_cvt_fp8x2_to_halfraw2(static_cast<__nv_fp8x2_storage_t>(w[j] & 0xffffu), __NV_E4M3);
+              const __half2_raw h23 = __nv_cvt_fp8x2_to_halfraw2(static_cast<__nv_fp8x2_storage_t>(w[j] >> 16), __NV_E4M3);
+              const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&h01));
+              const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&h23));
+              f[4 * j] += a.x * 0.015625f;
+              f[4 * j + 1] += a.y * 0.015625f;
+              f[4 * j + 2] += c.x * 0.015625f;
+              f[4 * j + 3] += c.y * 0.015625f;
             }
           }
           if (p.relu) {

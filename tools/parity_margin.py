@@ -43,9 +43,10 @@ for seed in (int(s) for s in args.seeds.split(",")):
     sd = _seeded_reference_weights(101, 6, seed)
     refs = {k: orc.enhancenet_forward(sd, x, "bilinear", "residual", 5, backend="torch")[0] for k, x in inputs.items()}
     schemes = [("hybrid_K%d" % k, "hybrid", k) for k in (int(v) for v in args.ks.split(","))]
-    schemes += [("hybrid_K10_lo16", "hybrid", 10), ("mixed", "mixed", None), ("bf16x3", "bf16x3", None)]
+    schemes += [("hybrid_K10_lo16", "hybrid", 10), ("hybrid_K10_stream16", "hybrid", 10), ("mixed", "mixed", None), ("bf16x3", "bf16x3", None)]
     for name, prec, k in schemes:
         old8 = isr._lib.set_tunable("trunk_lo8", 0 if name.endswith("lo16") else 1)
+        olds = isr._lib.set_tunable("stream_lo8", 0 if name.endswith("stream16") else 1)
         if k is not None:
             old = isr._lib.set_tunable("trunk_full_blocks", k)
         net = isr.createNetwork("EnhanceNet", 4, 101, [0, 1, 2, 3, 4], 6,
@@ -62,6 +63,7 @@ for seed in (int(s) for s in args.seeds.split(",")):
         if k is not None:
             isr._lib.set_tunable("trunk_full_blocks", old)
         isr._lib.set_tunable("trunk_lo8", old8)
+        isr._lib.set_tunable("stream_lo8", olds)
         del net
     sys.stderr.write("seed %d done\n" % seed)
 for name, d in out["schemes"].items():
