@@ -47,6 +47,8 @@ struct Tunables {
   int trunk_lo8 = 1;       // ISR_PREC_HYBRID: the low activation plane of the fully split trunk convs is 8-bit (e4m3 * 2^6)
                            // and the A_lo x W correction pass runs as kind::f8f6f4 against e5m2 weights (half the MMA
                            // time of the fp16 pass); 0 = the fp16 low plane
+  int input_lo8 = 1;       // with trunk_lo8: the packed network input is hi + 8-bit low plane too (the preblock runs the 8-bit
+                           // correction pass like the residual blocks); 0 = interleaved fp16 hi | lo, fp16 correction pass
   int stream_lo8 = 1;      // with trunk_lo8: the residual stream itself is kept as hi + the 8-bit low plane (the planes the convs
                            // read anyway); 0 = it also carries an fp16 low plane for the residual addend (320 instead of
                            // 192 B per pixel and tensor: the convs with an addend were HBM-bound, 156 vs 119 us)
@@ -530,6 +532,7 @@ struct Layer {
 
 struct Plan {
   int B = 0, h = 0, w = 0, precision = -1, f_last_parts = 1;
+  int in_parts = 1;     // what the packing kernels write: 1 | 2 interleaved 16-bit planes, 3 = planar fp16 hi + e4m3 lo8
   void *ws = nullptr;
   size_t ws_need = 0;   // bytes of workspace this plan uses (checked on every call, also on a cache hit)
   Scheme trunk, tail;
@@ -611,7 +614,7 @@ static int conv_for_layer(const Tunables &tun, ConvLaunch *L, const Layer &ly, i
                           int W, const Scheme &sc, int tensor_parts = 0, const void *act8 = nullptr) {
   const uint16_t *wbase = ly.packed + (sc.bf16 ? 0 : ly.per_fmt());
   return init_conv(tun, L, ly.npad, act, B, H, W, sc.na, wbase, ly.rows(), g * ly.npad, ly.G * ly.npad, sc.nw, sc.bf16,
-                   tensor_parts, act8, act8 != nullptr ? ly.packed_w8 : nullptr);
+                   tensor_parts, act8, act8 != nullptr ? ly.packed_w8 + static_cast<size_t>(g) * 9 * 64 * 64 : nullptr);
 }
 
 static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision, void *ws, size_t ws_bytes) {
@@ -673,17 +676,20 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
     }
   };
   // preblock (enhancenet.py:93-95): one launch per 64-channel input group; the second adds the first's partial sums
+  const bool i8 = lo8 && tun.input_lo8 && net->layers[0].packed_w8 != nullptr;   // packed input = planar hi + lo8
+  pl->in_parts = i8 ? 3 : T.na;
+  auto in8 = [&](int g) -> const void * { return i8 ? lo8_of(pl->in_g[g]) : nullptr; };
   if (net->G == 1) {
-    if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T, i8 ? 1 : 0, in8(0))) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, nullptr, 0, f0, FS);
     planar(&L, f0, FS, true, nullptr, 0);
     pl->convs.push_back(L);
   } else {
-    if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[0], 0, pl->in_g[0], B, h, w, T, i8 ? 1 : 0, in8(0))) != ISR_OK) return rc;
     set_store(&L, nullptr, 0, nullptr, 0, partial, FS);
     planar(&L, partial, FS, false, nullptr, 0);
     pl->convs.push_back(L);
-    if ((rc = conv_for_layer(tun, &L, net->layers[0], 1, pl->in_g[1], B, h, w, T)) != ISR_OK) return rc;
+    if ((rc = conv_for_layer(tun, &L, net->layers[0], 1, pl->in_g[1], B, h, w, T, i8 ? 1 : 0, in8(1))) != ISR_OK) return rc;
     set_store(&L, net->layers[0].bias, 1, partial, FS, f0, FS);
     planar(&L, f0, FS, true, partial, FS);
     pl->convs.push_back(L);
@@ -878,6 +884,7 @@ static int *tunable_slot(Tunables *t, const char *key, int value) {
     return (value >= 0 && value <= 10) ? &t->trunk_full_blocks : bad("trunk_full_blocks must be in [0, 10]");
   if (strcmp(key, "trunk_lo8") == 0) return (value == 0 || value == 1) ? &t->trunk_lo8 : bad("trunk_lo8 must be 0 or 1");
   if (strcmp(key, "fuse_up") == 0) return (value == 0 || value == 1) ? &t->fuse_up : bad("fuse_up must be 0 or 1");
+  if (strcmp(key, "input_lo8") == 0) return (value == 0 || value == 1) ? &t->input_lo8 : bad("input_lo8 must be 0 or 1");
   if (strcmp(key, "stream_lo8") == 0) return (value == 0 || value == 1) ? &t->stream_lo8 : bad("stream_lo8 must be 0 or 1");
   if (strcmp(key, "up2_wide") == 0) return (value == 0 || value == 1) ? &t->up2_wide : bad("up2_wide must be 0 or 1");
   if (strcmp(key, "final_issuers") == 0) return (value == 1 || value == 3) ? &t->final_issuers : bad("final_issuers must be 1 or 3");
@@ -1247,8 +1254,8 @@ int isr_net_create(isr_net **out, int input_channels, int output_channels, int n
       return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
     }
   }
-  for (int i = 1; i <= 20; ++i)
-    if (cudaMalloc(&net->layers[i].packed_w8, static_cast<size_t>(9) * 64 * 64) != cudaSuccess) {
+  for (int i = 0; i <= 20; ++i)
+    if (cudaMalloc(&net->layers[i].packed_w8, static_cast<size_t>(net->layers[i].G) * 9 * 64 * 64) != cudaSuccess) {
       isr_net_destroy(net);
       return fail(ISR_ERR_CUDA, "net_create: cudaMalloc failed");
     }
@@ -1292,7 +1299,7 @@ int isr_net_load_weights(isr_net *net, const float *const *params, int n_params,
     if (params[2 * i] == nullptr || params[2 * i + 1] == nullptr) return fail(ISR_ERR_ARG, "load_weights: null tensor");
     ISR_CUDA(launch_pack_weights(params[2 * i], ly.packed, ly.cout, ly.cin, ly.npad, ly.G, S(stream)));
     if (ly.packed_up != nullptr) ISR_CUDA(launch_pack_weights_up2(params[2 * i], ly.packed_up, S(stream)));
-    if (ly.packed_w8 != nullptr) ISR_CUDA(launch_pack_weights_lo8(params[2 * i], ly.packed_w8, S(stream)));
+    if (ly.packed_w8 != nullptr) ISR_CUDA(launch_pack_weights_lo8(params[2 * i], ly.packed_w8, ly.cin, ly.G, S(stream)));
     if (ly.packed_fin != nullptr)
       ISR_CUDA(launch_pack_weights_final(params[2 * i], ly.packed_fin, ly.cout, final_cp(ly.cout),
                                          final_rows(final_cp(ly.cout)), S(stream)));
@@ -1330,7 +1337,7 @@ int isr_net_forward(isr_net *net, const float *inputs, float *out_recon, float *
   Plan *pl = nullptr;
   int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
   if (rc != ISR_OK) return rc;
-  ISR_CUDA(launch_pack_nchw(inputs, pl->in_g[0], pl->in_g[1], B, net->cin, h, w, pl->trunk.na, pl->trunk.bf16, S(stream)));
+  ISR_CUDA(launch_pack_nchw(inputs, pl->in_g[0], pl->in_g[1], B, net->cin, h, w, pl->in_parts, pl->trunk.bf16, S(stream)));
   return run_plan(net, pl, inputs, static_cast<long long>(net->cin) * h * w, out_recon, out_raw, out_state,
                   state_unshaded, S(stream));
 }
@@ -1348,7 +1355,7 @@ int isr_net_forward_recurrent(isr_net *net, const float *low, const float *prev,
   int rc = forward_common(net, B, h, w, precision, workspace, workspace_bytes, &pl);
   if (rc != ISR_OK) return rc;
   ISR_CUDA(launch_pack_recurrent(low, prev, flow, pl->in_g[0], pl->in_g[1], B, c_low, c_prev, h, w, special_mask,
-                                 align_corners, pl->trunk.na, pl->trunk.bf16, S(stream)));
+                                 align_corners, pl->in_parts, pl->trunk.bf16, S(stream)));
   return run_plan(net, pl, low, static_cast<long long>(c_low) * h * w, out_recon, out_raw, out_state, state_unshaded,
                   S(stream));
 }

@@ -64,7 +64,7 @@ cudaError_t launch_pack_weights(const float *w, uint16_t *out, int cout, int cin
 cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, int cp, int nrows, cudaStream_t s);
 
 // 8-bit (e5m2, scaled 2^-6) weight plane of a 64 -> 64 layer: [tap 9][n 64 (permuted like pack_weights)][k 64] bytes
-cudaError_t launch_pack_weights_lo8(const float *w, uint8_t *out, cudaStream_t s);
+cudaError_t launch_pack_weights_lo8(const float *w, uint8_t *out, int cin, int G, cudaStream_t s);
 // column-stacked output-conv weights (isr_conv_final2.cuh): [fmt 2][ky 3][part 2][nk (n = kx*cp + co)][64]
 cudaError_t launch_pack_weights_final2(const float *w, uint16_t *out, int cout, int cp, int nk, cudaStream_t s);
 

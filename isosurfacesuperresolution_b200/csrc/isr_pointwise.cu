@@ -135,6 +135,34 @@ __device__ __forceinline__ void store_chunk8(uint16_t *dst_pix, int chunk, int n
   if (nparts == 2) *reinterpret_cast<uint4 *>(dst_pix + 64 + chunk * 8) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
+// nparts == 3 of the packing kernels: PLANAR fp16 hi plane (128 B per pixel) + e4m3(lo * 2^6) plane (64 B per pixel) at
+// byte offset npix * 256 of the group's block -- the operand planes of the 8-bit correction pass (isr_conv_pair.cuh)
+__device__ __forceinline__ void store_chunk8_planar(uint16_t *g, size_t pix, size_t npix, int chunk, const float *f) {
+  uint32_t hi[4];
+  float lf[8];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    hi[j] = pack2_pw(f[2 * j], f[2 * j + 1], 0);
+    const float2 hf = unpack2_pw(hi[j], 0);
+    lf[2 * j] = (f[2 * j] - hf.x) * 64.f;
+    lf[2 * j + 1] = (f[2 * j + 1] - hf.y) * 64.f;
+  }
+  *reinterpret_cast<uint4 *>(g + pix * 64 + chunk * 8) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  uint32_t l8[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const uint32_t a = __nv_cvt_float2_to_fp8x2(make_float2(lf[4 * j], lf[4 * j + 1]), __NV_SATFINITE, __NV_E4M3);
+    const uint32_t c = __nv_cvt_float2_to_fp8x2(make_float2(lf[4 * j + 2], lf[4 * j + 3]), __NV_SATFINITE, __NV_E4M3);
+    l8[j] = a | (c << 16);
+  }
+  *reinterpret_cast<uint2 *>(reinterpret_cast<uint8_t *>(g) + npix * 256 + pix * 64 + chunk * 8) = make_uint2(l8[0], l8[1]);
+}
+__device__ __forceinline__ void store_chunk8_any(uint16_t *g, size_t pix, size_t npix, int chunk, int nparts, const float *f,
+                                                 int is_bf16) {
+  if (nparts == 3) store_chunk8_planar(g, pix, npix, chunk, f);
+  else store_chunk8(g + pix * (64 * nparts), chunk, nparts, f, is_bf16);
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // VideoTools.flatten_high (models/videotools.py:8-25)
 __global__ void flatten_high_kernel(const float *__restrict__ in, float *__restrict__ out, int B, int C, int H, int W,
@@ -305,8 +333,8 @@ pack_recurrent_kernel(const float *__restrict__ low, const float *__restrict__ p
     float f[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = tile[lp][g * 64 + chunk * 8 + j];
-    uint16_t *dst = (g == 0 ? out_g0 : out_g1) + ((static_cast<size_t>(b) * h + y) * w + xb + lp) * (64 * nparts);
-    store_chunk8(dst, chunk, nparts, f, is_bf16);
+    store_chunk8_any(g == 0 ? out_g0 : out_g1, (static_cast<size_t>(b) * h + y) * w + xb + lp,
+                     static_cast<size_t>(gridDim.z) * h * w, chunk, nparts, f, is_bf16);
   }
 }
 
@@ -499,8 +527,8 @@ pack_recurrent_v2_kernel(const float *__restrict__ low, const float *__restrict_
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] = (ch0 + j < cin) ? tile[lp * kPack2Pitch + ch0 + j] : 0.f;
     }
-    uint16_t *dst = (g == 0 ? out_g0 : out_g1) + ((static_cast<size_t>(b) * h + y) * w + xb + lp) * (64 * nparts);
-    store_chunk8(dst, chunk, nparts, f, is_bf16);
+    store_chunk8_any(g == 0 ? out_g0 : out_g1, (static_cast<size_t>(b) * h + y) * w + xb + lp,
+                     static_cast<size_t>(gridDim.z) * h * w, chunk, nparts, f, is_bf16);
   }
 }
 
@@ -524,8 +552,8 @@ pack_nchw_kernel(const float *__restrict__ in, uint16_t *__restrict__ out_g0, ui
     float f[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = tile[lp][g * 64 + chunk * 8 + j];
-    uint16_t *dst = (g == 0 ? out_g0 : out_g1) + ((static_cast<size_t>(b) * h + y) * w + xb + lp) * (64 * nparts);
-    store_chunk8(dst, chunk, nparts, f, is_bf16);
+    store_chunk8_any(g == 0 ? out_g0 : out_g1, (static_cast<size_t>(b) * h + y) * w + xb + lp,
+                     static_cast<size_t>(gridDim.z) * h * w, chunk, nparts, f, is_bf16);
   }
 }
 
@@ -1008,11 +1036,13 @@ __global__ void pack_weights_kernel(const float *__restrict__ w, uint16_t *__res
 // permutation as pack_weights_kernel, [tap 9][n 64][k 64] bytes.  The activation's low plane is stored as e4m3(lo * 2^6),
 // so the product carries no scale.  e5m2 keeps 2 mantissa bits: the correction term lo x w (2^-11 of the main product) is
 // reproduced to ~10 %, i.e. the pair (hi, lo8) acts like a ~14-bit activation where the fp16 pair gave 22 bits.
-__global__ void pack_weights_lo8_kernel(const float *__restrict__ w, uint8_t *__restrict__ out) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 9 * 64 * 64; i += gridDim.x * blockDim.x) {
-    const int k = i & 63, n = (i >> 6) & 63, tap = i >> 12;
+// out: [group G][tap 9][n 64][k 64]; input channel of (group g, k) = 64 g + k (zero beyond cin)
+__global__ void pack_weights_lo8_kernel(const float *__restrict__ w, uint8_t *__restrict__ out, int cin, int G) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < G * 9 * 64 * 64; i += gridDim.x * blockDim.x) {
+    const int k = i & 63, n = (i >> 6) & 63, tap = (i >> 12) % 9, g = i / (9 * 4096);
     const int co = 16 * ((n & 7) >> 1) + 2 * (n >> 3) + (n & 1);
-    const float v = w[(static_cast<size_t>(co) * 64 + k) * 9 + tap] * 0.015625f;
+    const int ci = 64 * g + k;
+    const float v = ci < cin ? w[(static_cast<size_t>(co) * cin + ci) * 9 + tap] * 0.015625f : 0.f;
     out[i] = static_cast<uint8_t>(__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E5M2));
   }
 }
@@ -1194,8 +1224,10 @@ cudaError_t launch_pack_recurrent(const float *low, const float *prev, const flo
       launch_pdl(pack_recurrent_v2_kernel<CPV, NP, BF, 0>, grid2, dim3(128), 0, s, low, prev, flow, g0, g1, c_low, h, w,   \
                  special_mask, align_corners);                                                                          \
   } while (0)
-    const int sel = (c_prev == 6 ? 4 : 0) + (nparts == 2 ? 2 : 0) + (is_bf16 ? 1 : 0);
+    const int sel = nparts == 3 ? (c_prev == 6 ? 9 : 8) : (c_prev == 6 ? 4 : 0) + (nparts == 2 ? 2 : 0) + (is_bf16 ? 1 : 0);
     switch (sel) {
+      case 8: ISR_PACK2(3, 3, 0); break;
+      case 9: ISR_PACK2(6, 3, 0); break;
       case 0: ISR_PACK2(3, 1, 0); break;
       case 1: ISR_PACK2(3, 1, 1); break;
       case 2: ISR_PACK2(3, 2, 0); break;
@@ -1265,8 +1297,8 @@ cudaError_t launch_pack_weights_final(const float *w, uint16_t *out, int cout, i
   count_launch();
   return cudaGetLastError();
 }
-cudaError_t launch_pack_weights_lo8(const float *w, uint8_t *out, cudaStream_t s) {
-  pack_weights_lo8_kernel<<<(9 * 64 * 64 + 255) / 256, 256, 0, s>>>(w, out);
+cudaError_t launch_pack_weights_lo8(const float *w, uint8_t *out, int cin, int G, cudaStream_t s) {
+  pack_weights_lo8_kernel<<<(G * 9 * 64 * 64 + 255) / 256, 256, 0, s>>>(w, out, cin, G);
   count_launch();
   return cudaGetLastError();
 }

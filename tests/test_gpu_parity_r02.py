@@ -472,21 +472,31 @@ def test_trunk_8bit_low_plane(isr, golden, weights, seed):
     ref, _ = orc.enhancenet_forward(sd, x, "bilinear", "residual", 5, backend="torch")
     outs = {}
     try:
-        for name, lo8, K in (("lo8", 1, 10), ("lo16", 0, 10), ("cheap", 0, 0)):
+        # lo8: the default (8-bit low plane in the packed input, the residual stream and the conv operands);
+        # lo8_convs_only: the residual stream and the packed input keep an fp16 low plane (stream_lo8 = input_lo8 = 0)
+        for name, lo8, wide8, K in (("lo8", 1, 1, 10), ("lo8_convs_only", 1, 0, 10), ("lo16", 0, 0, 10), ("cheap", 0, 0, 0)):
             isr._lib.set_tunable("trunk_lo8", lo8)
+            isr._lib.set_tunable("stream_lo8", wide8)
+            isr._lib.set_tunable("input_lo8", wide8)
             isr._lib.set_tunable("trunk_full_blocks", K)
             net = _net(isr, sd)
             with torch.no_grad():
                 outs[name] = net(cu(x))[0].cpu().numpy()
     finally:
         isr._lib.set_tunable("trunk_lo8", 1)
+        isr._lib.set_tunable("stream_lo8", 1)
+        isr._lib.set_tunable("input_lo8", 1)
         isr._lib.set_tunable("trunk_full_blocks", 10)
-    e8, e16, ec = (float(np.max(np.abs(outs[k] - ref))) for k in ("lo8", "lo16", "cheap"))
-    r8, r16, rc = (float(np.sqrt(np.mean((outs[k] - ref) ** 2))) for k in ("lo8", "lo16", "cheap"))
-    assert e8 <= 1e-2 and e8 <= 1.15 * e16 + 2e-4, (e8, e16, ec)
-    assert r8 <= 1.1 * r16, (r8, r16, rc)
-    assert rc >= 1.2 * r16 and (rc - r8) >= 0.7 * (rc - r16), (r8, r16, rc)
-    _check_net(torch.from_numpy(outs["lo8"]), ref)
+    e16, ec = (float(np.max(np.abs(outs[k] - ref))) for k in ("lo16", "cheap"))
+    r16, rc = (float(np.sqrt(np.mean((outs[k] - ref) ** 2))) for k in ("lo16", "cheap"))
+    assert rc >= 1.2 * r16, (r16, rc)
+    for k in ("lo8", "lo8_convs_only"):
+        e8 = float(np.max(np.abs(outs[k] - ref)))
+        r8 = float(np.sqrt(np.mean((outs[k] - ref) ** 2)))
+        assert e8 <= 1e-2 and e8 <= 1.15 * e16 + 2e-4, (k, e8, e16, ec)
+        assert r8 <= 1.1 * r16, (k, r8, r16, rc)
+        assert (rc - r8) >= 0.7 * (rc - r16), (k, r8, r16, rc)
+        _check_net(torch.from_numpy(outs[k]), ref)
 
 
 @pytest.mark.parametrize("shape", [(1, 16, 20), (2, 19, 27), (1, 33, 130), (1, 270, 480)])

@@ -47,6 +47,7 @@ for seed in (int(s) for s in args.seeds.split(",")):
     for name, prec, k in schemes:
         old8 = isr._lib.set_tunable("trunk_lo8", 0 if name.endswith("lo16") else 1)
         olds = isr._lib.set_tunable("stream_lo8", 0 if name.endswith("stream16") else 1)
+        oldi = isr._lib.set_tunable("input_lo8", 0 if name.endswith("stream16") else 1)
         if k is not None:
             old = isr._lib.set_tunable("trunk_full_blocks", k)
         net = isr.createNetwork("EnhanceNet", 4, 101, [0, 1, 2, 3, 4], 6,
@@ -64,6 +65,7 @@ for seed in (int(s) for s in args.seeds.split(",")):
             isr._lib.set_tunable("trunk_full_blocks", old)
         isr._lib.set_tunable("trunk_lo8", old8)
         isr._lib.set_tunable("stream_lo8", olds)
+        isr._lib.set_tunable("input_lo8", oldi)
         del net
     sys.stderr.write("seed %d done\n" % seed)
 for name, d in out["schemes"].items():
