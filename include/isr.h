@@ -299,6 +299,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *                                    (tensor floor: 64 cycles per two phases instead of 2 x 43); 0 = four N = 64 phases
  *   "trunk_lo8" (0 | [1])            ISR_PREC_HYBRID: 8-bit low activation plane + 8-bit (kind::f8f6f4) correction pass in the
  *                                    fully split trunk convs (0 = fp16 low plane, 25 % more trunk time, same parity)
+ *   "alt_order" (0 | [1])            consecutive convs walk their tiles in alternating directions, so that each starts on the
+ *                                    part of its input that the previous launch left in L2
  *   "input_lo8" (0 | [1])            with trunk_lo8: the packed network input is planar fp16 hi + 8-bit low plane as well (the
  *                                    preblock runs the 8-bit correction pass); 0 = interleaved fp16 hi | lo
  *   "stream_lo8" (0 | [1])           with trunk_lo8: the residual stream is stored as hi + that 8-bit low plane only (0 = it

@@ -47,6 +47,8 @@ struct Tunables {
   int trunk_lo8 = 1;       // ISR_PREC_HYBRID: the low activation plane of the fully split trunk convs is 8-bit (e4m3 * 2^6)
                            // and the A_lo x W correction pass runs as kind::f8f6f4 against e5m2 weights (half the MMA
                            // time of the fp16 pass); 0 = the fp16 low plane
+  int alt_order = 1;       // consecutive convs walk their tiles in alternating directions (ConvParams::reverse): each starts on
+                           // the part of its input that is still in L2
   int input_lo8 = 1;       // with trunk_lo8: the packed network input is hi + 8-bit low plane too (the preblock runs the 8-bit
                            // correction pass like the residual blocks); 0 = interleaved fp16 hi | lo, fp16 correction pass
   int stream_lo8 = 1;      // with trunk_lo8: the residual stream itself is kept as hi + the 8-bit low plane (the planes the convs
@@ -780,6 +782,16 @@ static int build_plan(isr_net *net, Plan *pl, int B, int h, int w, int precision
   L.p.h_low = h;
   L.p.w_low = w;
   pl->convs.push_back(L);
+  if (tun.alt_order) {
+    // the packing kernels finish at the end of their tensors, so the first conv walks down, the next one up, ...
+    int k = 1;
+    for (size_t i = 0; i < pl->convs.size(); ++i, ++k) {
+      ConvLaunch *c = &pl->convs[i];
+      if (static_cast<int>(i) == pl->idx_post1 && pl->fuse2.on) c = &pl->fuse2.up;
+      if (static_cast<int>(i) == pl->idx_post4 && pl->fuse4.on) c = &pl->fuse4.up;
+      c->p.reverse = k & 1;
+    }
+  }
   return ISR_OK;
 }
 
@@ -884,6 +896,7 @@ static int *tunable_slot(Tunables *t, const char *key, int value) {
     return (value >= 0 && value <= 10) ? &t->trunk_full_blocks : bad("trunk_full_blocks must be in [0, 10]");
   if (strcmp(key, "trunk_lo8") == 0) return (value == 0 || value == 1) ? &t->trunk_lo8 : bad("trunk_lo8 must be 0 or 1");
   if (strcmp(key, "fuse_up") == 0) return (value == 0 || value == 1) ? &t->fuse_up : bad("fuse_up must be 0 or 1");
+  if (strcmp(key, "alt_order") == 0) return (value == 0 || value == 1) ? &t->alt_order : bad("alt_order must be 0 or 1");
   if (strcmp(key, "input_lo8") == 0) return (value == 0 || value == 1) ? &t->input_lo8 : bad("input_lo8 must be 0 or 1");
   if (strcmp(key, "stream_lo8") == 0) return (value == 0 || value == 1) ? &t->stream_lo8 : bad("stream_lo8 must be 0 or 1");
   if (strcmp(key, "up2_wide") == 0) return (value == 0 || value == 1) ? &t->up2_wide : bad("up2_wide must be 0 or 1");

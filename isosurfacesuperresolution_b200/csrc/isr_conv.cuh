@@ -71,6 +71,9 @@ struct ConvParams {
   uint16_t *out_lo16;     // planar lo fp16 output plane (nullptr: interleaved at +128 B of the output pixel when out_parts == 2)
   uint8_t *out_lo8;       // planar e4m3(lo * 2^6) output plane, 64 B per pixel (nullptr: none)
   const uint16_t *addend_lo;   // planar lo fp16 plane of the addend (nullptr: interleaved at +128 B when add_parts == 2)
+  int reverse;            // 1: the persistent CTAs walk the tiles from the last to the first.  Consecutive launches alternate,
+                          // so that a launch starts on the part of its input the previous launch wrote (or read) last --
+                          // the part that is still in the 126 MB L2 (the tensors of a chunk are 100 MB .. 2 GB each)
   const uint8_t *addend_lo8;   // planar e4m3(lo * 2^6) plane of the addend (add_parts == 1): the residual stream kept as
                                // hi + 8-bit lo, the very planes the convs read (192 instead of 320 B per pixel and tensor)
 };

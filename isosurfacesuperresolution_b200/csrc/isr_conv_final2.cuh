@@ -101,16 +101,24 @@ conv3x3_final2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   // pixels per tile (1000 tiles per SM at configs[1] sizes) three integer divisions per tile were a measurable part of
   // the launch (tools/final_experiments2.py).
   struct TileCursor {
-    int tx, ty, b, dx, dy, db, tiles_x, tiles_y;
-    __device__ __forceinline__ void init(int t, int step, int txs, int tys) {
-      tiles_x = txs; tiles_y = tys;
+    int tx, ty, b, dx, dy, db, tiles_x, tiles_y, rev;
+    // rev (ConvParams::reverse): walk order index t -> tile num_tiles - 1 - t, steps go down
+    __device__ __forceinline__ void init(int t, int step, int txs, int tys, int reverse, int num_tiles) {
+      tiles_x = txs; tiles_y = tys; rev = reverse;
+      if (rev) t = num_tiles - 1 - t;
       tx = t % txs; ty = (t / txs) % tys; b = t / (txs * tys);
       dx = step % txs; dy = (step / txs) % tys; db = step / (txs * tys);
     }
     __device__ __forceinline__ void advance() {
-      tx += dx; ty += dy; b += db;
-      if (tx >= tiles_x) { tx -= tiles_x; ++ty; }
-      if (ty >= tiles_y) { ty -= tiles_y; ++b; }
+      if (rev) {
+        tx -= dx; ty -= dy; b -= db;
+        if (tx < 0) { tx += tiles_x; --ty; }
+        if (ty < 0) { ty += tiles_y; --b; }
+      } else {
+        tx += dx; ty += dy; b += db;
+        if (tx >= tiles_x) { tx -= tiles_x; ++ty; }
+        if (ty >= tiles_y) { ty -= tiles_y; ++b; }
+      }
     }
   };
 
@@ -126,7 +134,7 @@ conv3x3_final2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     pdl_wait();   // the activations are the previous kernel's output
     uint32_t it = 0;
     TileCursor cur;
-    cur.init(blockIdx.x, gridDim.x, p.tiles_x, p.tiles_y);
+    cur.init(blockIdx.x, gridDim.x, p.tiles_x, p.tiles_y, p.reverse, p.num_tiles);
     for (int i = 0; i < my_tiles; ++i, cur.advance()) {
       const int tx = cur.tx, ty = cur.ty, b = cur.b;
       for (int ap = 0; ap < p.n_act_parts; ++ap, ++it) {
@@ -198,7 +206,7 @@ conv3x3_final2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       e_c[k] = e / 24; e_r[k] = (e % 24) / 6; e_cc[k] = (e % 24) % 6;
     }
     TileCursor cur;
-    cur.init(blockIdx.x + grp * gridDim.x, G * gridDim.x, p.tiles_x, p.tiles_y);
+    cur.init(blockIdx.x + grp * gridDim.x, G * gridDim.x, p.tiles_x, p.tiles_y, p.reverse, p.num_tiles);
     for (int i = grp; i < my_tiles; i += G, ++n_local, cur.advance()) {
       const int tx = cur.tx, ty = cur.ty, b = cur.b;
       const uint32_t acc = grp;

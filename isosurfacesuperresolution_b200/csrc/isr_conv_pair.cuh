@@ -104,16 +104,23 @@ __device__ __forceinline__ void umma2_commit_multicast(uint32_t bar) {
 
 // (tx, ty, b) of tile t, advanced by a constant step without divisions (one division set per role and launch)
 struct PairTileCursor {
-  int tx, ty, b, dx, dy, db, tiles_x, tiles_y;
-  __device__ __forceinline__ void init(int t, int step, int txs, int tys) {
-    tiles_x = txs; tiles_y = tys;
+  int tx, ty, b, dx, dy, db, tiles_x, tiles_y, rev;
+  // rev: the cursor starts at tile t and walks DOWN by `step` (ConvParams::reverse)
+  __device__ __forceinline__ void init(int t, int step, int txs, int tys, int reverse = 0) {
+    tiles_x = txs; tiles_y = tys; rev = reverse;
     tx = t % txs; ty = (t / txs) % tys; b = t / (txs * tys);
     dx = step % txs; dy = (step / txs) % tys; db = step / (txs * tys);
   }
   __device__ __forceinline__ void advance() {
-    tx += dx; ty += dy; b += db;
-    if (tx >= tiles_x) { tx -= tiles_x; ++ty; }
-    if (ty >= tiles_y) { ty -= tiles_y; ++b; }
+    if (rev) {
+      tx -= dx; ty -= dy; b -= db;
+      if (tx < 0) { tx += tiles_x; --ty; }
+      if (ty < 0) { ty += tiles_y; --b; }
+    } else {
+      tx += dx; ty += dy; b += db;
+      if (tx >= tiles_x) { tx -= tiles_x; ++ty; }
+      if (ty >= tiles_y) { ty -= tiles_y; ++b; }
+    }
   }
 };
 
@@ -245,7 +252,8 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // tools/final_experiments2.py): the tile coordinates and the stage ring are counters advanced by constant steps.
     uint32_t it = 0, s = 0, ph = 0;
     PairTileCursor cur;
-    cur.init(2 * pair_id + static_cast<int>(rank), 2 * num_pairs, p.tiles_x, p.tiles_y);
+    cur.init(2 * (p.reverse ? pair_tiles - 1 - pair_id : pair_id) + static_cast<int>(rank), 2 * num_pairs, p.tiles_x,
+             p.tiles_y, p.reverse);
     for (int i = 0; i < my_iters; ++i, cur.advance()) {
       bool valid = cur.b < p.B;
       int tx = cur.tx, ty = cur.ty;
@@ -364,7 +372,9 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int v = grp; v < my_iters * PH; v += G) {
       const int i = v / PH, phase = v % PH;
       if (cur_i < 0) {
-        cur.init(2 * (pair_id + i * num_pairs) + static_cast<int>(rank), 2 * num_pairs, p.tiles_x, p.tiles_y);
+        const int j0 = pair_id + i * num_pairs;   // pair index in walking order
+        cur.init(2 * (p.reverse ? pair_tiles - 1 - j0 : j0) + static_cast<int>(rank), 2 * num_pairs, p.tiles_x, p.tiles_y,
+                 p.reverse);
         cur_i = i;
       }
       for (; cur_i < i; ++cur_i) cur.advance();   // G / PH tiles (PH = 1) or none (the next phase of the same tile)

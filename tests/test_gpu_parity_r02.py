@@ -520,3 +520,26 @@ def test_fused_upsample_wide_equals_four_phase(isr, weights, shape):
         _lib.set_tunable("up2_wide", 1)
     assert torch.isfinite(outs[1]).all()
     assert torch.equal(outs[1], outs[0])
+
+
+@pytest.mark.parametrize("shape", [(1, 16, 20), (2, 19, 27), (3, 33, 130), (1, 270, 480)])
+def test_alternating_tile_order_is_bit_identical(isr, weights, shape):
+    """Consecutive convs walk their tiles in alternating directions (tunable alt_order = 1, the default; ConvParams::reverse)
+    so that each launch starts on the part of its input that is still in L2.  The order in which persistent CTAs visit the
+    tiles cannot change a result: bit-identical to alt_order = 0 on ragged tiles, odd tile counts (the unpaired last tile
+    is the FIRST one a reversed pair kernel visits) and several images."""
+    from isosurfacesuperresolution_b200 import _lib
+    B, h, w = shape
+    g = torch.Generator(device="cuda").manual_seed(23)
+    x = torch.rand(B, 101, h, w, device="cuda", generator=g) * 2 - 1
+    outs = {}
+    try:
+        for alt in (1, 0):
+            _lib.set_tunable("alt_order", alt)
+            net = _net(isr, weights)
+            with torch.no_grad():
+                outs[alt] = net(x)[0].clone()
+    finally:
+        _lib.set_tunable("alt_order", 1)
+    assert torch.isfinite(outs[1]).all()
+    assert torch.equal(outs[1], outs[0])
