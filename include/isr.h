@@ -310,6 +310,8 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
  *   "final_stacked" (0 | 1 | 2 | [3]) output conv: generic / tap-stacked (shared-memory gather) / CTA-pair N=16 /
  *                                    column-stacked with a register gather (isr_conv_final2.cuh)
  *   "final_issuers" (1 | [3])        MMA-issuing warps of the tap-stacked output conv
+ *   "final_groups" ([3] | 4)         epilogue groups (= accumulator buffers = issuing warps) of the column-stacked output conv
+ *                                    (4 spills in the epilogue: 0.65 against 0.61 ms)
  *   "final_w_parts" ([0] = scheme | 1 | 2)   weight planes of the output conv
  *   "raycast_two_pass" (0 | [1] = from 8 AO rays on | 2)   ambient occlusion of the ray-caster as a second pass
  *   "pdl_small" ([0] | 1)            process-wide: packing / band / shading / composition kernels launched programmatically
@@ -321,8 +323,11 @@ int isr_debug_conv_workspace_bytes(int B, int H, int W, size_t *bytes);
 int isr_set_tunable(const char *key, int value);
 int isr_net_set_tunable(isr_net *net, const char *key, int value);
 
-/* Times `iters` back-to-back launches of the network's dominant kernel (the 64->64 conv at 4h x 4w) with CUDA events
- * on `stream`; returns the average milliseconds per launch in *ms (bench.py's roofline leg). */
+/* Times `iters` back-to-back launches of ONE conv of the network's plan with CUDA events on `stream`; returns the average
+ * milliseconds per launch in *ms.  scale 4: the dominant kernel, the 64->64 conv at 4h x 4w (bench.py's roofline leg);
+ * 1 / 2: first / second conv of the first residual block (h x w; the second carries the residual addend); 3: the fused
+ * upsample + conv that produces the 4h x 4w tensor (bilinear nets); 5: the output conv (writes into scratch).  The handle's
+ * "dbg" tunable is applied to the timed launches only. */
 int isr_net_time_conv(isr_net *net, int B, int h, int w, int precision, int scale, void *workspace,
                       size_t workspace_bytes, int iters, float *ms, void *stream);
 

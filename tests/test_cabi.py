@@ -97,3 +97,27 @@ def test_python_api_refuses_cpu_tensors():
         net(torch.zeros(1, 101, 4, 4))
     with pytest.raises(ValueError):
         isr.createNetwork("nope", 4, 101, [0], 6, Namespace(upsample="bilinear", reconType="residual", useBN=False))
+
+
+def test_every_tunable_is_documented_and_accepted(lib):
+    """The tunables list of include/isr.h and the keys isr_api.cu understands are the same set, and every documented key is
+    accepted by isr_set_tunable (no GPU needed: it only changes the defaults new handles snapshot); unknown keys and
+    out-of-range values come back as a negative status, and the previous value is restored."""
+    doc = open(HEADER).read()
+    doc = doc[doc.index("Tunables for tests, experiments and bench ablations"):doc.index("int isr_set_tunable")]
+    documented = set(re.findall(r'"([a-z_0-9]+)"', doc))
+    code = open(os.path.join(ROOT, "isosurfacesuperresolution_b200", "csrc", "isr_api.cu")).read()
+    understood = set(re.findall(r'strcmp\(key, "([a-z_0-9]+)"\)', code))
+    assert documented == understood, (sorted(documented - understood), sorted(understood - documented))
+    for key in sorted(documented):
+        old = None
+        for v in (1, 0, 2, 3, 10, 16):
+            rc = lib.lib().isr_set_tunable(key.encode(), v)
+            if rc >= 0:
+                old = rc
+                break
+        assert old is not None, key
+        assert lib.lib().isr_set_tunable(key.encode(), old) >= 0          # restore the default
+        assert lib.lib().isr_set_tunable(key.encode(), old) == old
+    assert lib.lib().isr_set_tunable(b"no_such_tunable", 1) < 0
+    assert lib.lib().isr_set_tunable(b"trunk_full_blocks", 11) < 0
