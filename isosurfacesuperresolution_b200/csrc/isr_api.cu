@@ -217,6 +217,7 @@ static int setup_kernel_attrs() {
   ISR_CUDA(set_max_smem((conv3x3_pair_kernel<0, 64, EPI_STORE16, 1, false>)));
   ISR_CUDA(set_max_smem((conv3x3_pair_kernel<1, 64, EPI_STORE16, 1, false>)));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<1>));
+  ISR_CUDA(set_max_smem((conv3x3_pair_kernel<1, 64, EPI_STORE16, 1, true, 8>)));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 64, EPI_STORE16, 4>));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 64, EPI_STORE16, 2>));
   ISR_CUDA(set_max_smem(conv3x3_pair_kernel<0, 16, EPI_FINAL>));
@@ -473,6 +474,11 @@ static int run_conv(const ConvLaunch &L, cudaStream_t s) {
     else if (L.n == 16 && stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 16, EPI_FINAL>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else if (L.n == 16) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 16, EPI_FINAL>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else if (stack && L.p.addend == nullptr && !(L.p.dbg & 2048)) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16, 1, false>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    else if (stack && L.p.addend != nullptr && !(L.p.dbg & 2048)) {
+      // with a residual addend: eight warps per epilogue group (isr_conv_pair.cuh)
+      cfg.blockDim = dim3(pair_threads(8));
+      ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16, 1, true, 8>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
+    }
     else if (stack) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<1, 64, EPI_STORE16>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else if (L.p.addend == nullptr && !(L.p.dbg & 2048)) ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16, 1, false>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));
     else ISR_CUDA(cudaLaunchKernelEx(&cfg, conv3x3_pair_kernel<0, 64, EPI_STORE16>, L.tmA, L.tmW, L.tmA8, L.tmW8, L.p));

@@ -241,6 +241,134 @@ __device__ __forceinline__ void epilogue_store16(const ConvParams &p, const floa
     }
 }
 
+// The same epilogue for HALF of the channels: the CTA-pair kernel runs EIGHT warps per epilogue group -- warps q and q + 4
+// both own TMEM lanes 32q..32q+31 and split the accumulator columns (`chalf` = 0: GEMM columns 0..31, 1: columns 32..63;
+// with the column permutation of pack_weights_kernel a thread then holds channels 16 m + 8 chalf .. + 7 of its four pixels).
+// Why: one warp executes the whole chain of a tile serially (addend loads -> accumulator -> ~1000 dependent instructions
+// -> stores); with an addend that chain took ~9000 cycles per tile and group against a budget of two tiles' MMAs (6200), so
+// the convs with a residual addend were epilogue-bound (151 us against 119 without addend).  Half the work per warp, twice
+// the warps; 16-byte instead of 32-byte accesses (two lanes per sector).
+template <int N, int STACK, bool ADD = true>
+__device__ __forceinline__ void epilogue_store16_half(const ConvParams &p, const float *s_bias, uint32_t taddr, int q, int chalf,
+                                                      int lane, int b, int ty, int tx, bool tile_valid, uint32_t bar_tfull,
+                                                      uint32_t acc_ph, int omul = 1, int oyadd = 0, int oxadd = 0) {
+  const int m = lane & 3, rr = lane >> 2;
+  const int x = tx * kTileW + rr;
+  const int ch0 = 16 * m + 8 * chalf;   // first of this thread's 8 channels
+  float bias_r[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bias_r[j] = s_bias[ch0 + j];
+  uint32_t ad[4][2][4];   // [pixel][hi | lo][16 B]  (lo8: 8 B in [1][0..1])
+  const bool has_add = ADD && p.addend != nullptr;
+  const size_t add_pitch = p.add_pitch > 0 ? p.add_pitch : 128 * p.add_parts;
+  const size_t out_pitch = p.out_pitch > 0 ? p.out_pitch : 128 * p.out_parts;
+  if (has_add) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int y = ty * kTileH + 4 * q + j;
+      const bool ok = tile_valid && (y < p.H) && (x < p.W);
+      const size_t pix = (static_cast<size_t>(b) * p.H + (ok ? y : 0)) * p.W + (ok ? x : 0);
+      const uint8_t *ab = reinterpret_cast<const uint8_t *>(p.addend) + pix * add_pitch + 2 * ch0;
+      ldg_v4(ab, ad[j][0]);
+      if (p.add_parts == 2)
+        ldg_v4(p.addend_lo != nullptr ? reinterpret_cast<const uint8_t *>(p.addend_lo) + pix * 128 + 2 * ch0 : ab + 128, ad[j][1]);
+      else if (p.addend_lo8 != nullptr)
+        ldg_v2(p.addend_lo8 + pix * 64 + ch0, ad[j][1]);
+    }
+  }
+  mbar_wait_parked(bar_tfull, acc_ph);
+  tc_fence_after();
+  if (p.dbg & 4) return;   // bench experiment: barrier handshake only
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    uint32_t v[16];
+    tmem_ld_16x256b_x4(taddr + 32 * chalf + (static_cast<uint32_t>(half * 16) << 16), v);
+    if constexpr (STACK) {
+      uint32_t v2[16];
+      tmem_ld_16x256b_x4(taddr + N + 32 * chalf + (static_cast<uint32_t>(half * 16) << 16), v2);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(v2[j]));
+    } else {
+      tmem_ld_wait();
+    }
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int y = ty * kTileH + 4 * q + 2 * half + hh;
+      if (tile_valid && y < p.H && x < p.W) {
+        const size_t pix = (static_cast<size_t>(b) * (p.H * omul) + (y * omul + oyadd)) * (p.W * omul) + (x * omul + oxadd);
+        float f[8];
+#pragma unroll
+        for (int rep = 0; rep < 4; ++rep) {
+          f[2 * rep] = __uint_as_float(v[4 * rep + 2 * hh]) + bias_r[2 * rep];
+          f[2 * rep + 1] = __uint_as_float(v[4 * rep + 2 * hh + 1]) + bias_r[2 * rep + 1];
+        }
+        if (has_add) {
+#pragma unroll
+          for (int ap = 0; ap < 2; ++ap) {
+            if (ap < p.add_parts) {
+              const uint32_t *w = ad[2 * half + hh][ap];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 a = unpack2(w[j], p.is_bf16);
+                f[2 * j] += a.x;
+                f[2 * j + 1] += a.y;
+              }
+            }
+          }
+          if (p.add_parts == 1 && p.addend_lo8 != nullptr) {
+            const uint32_t *w = ad[2 * half + hh][1];   // 8 e4m3 bytes = lo * 2^6 of channels ch0 .. ch0 + 7
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const __half2_raw h01 = __nv_cvt_fp8x2_to_halfraw2(static_cast<__nv_fp8x2_storage_t>(w[j] & 0xffffu), __NV_E4M3);
+              const __half2_raw h23 = __nv_cvt_fp8x2_to_halfraw2(static_cast<__nv_fp8x2_storage_t>(w[j] >> 16), __NV_E4M3);
+              const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&h01));
+              const float2 c = __half22float2(*reinterpret_cast<const __half2 *>(&h23));
+              f[4 * j] += a.x * 0.015625f;
+              f[4 * j + 1] += a.y * 0.015625f;
+              f[4 * j + 2] += c.x * 0.015625f;
+              f[4 * j + 3] += c.y * 0.015625f;
+            }
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        uint32_t hi[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) hi[j] = pack2(f[2 * j], f[2 * j + 1], p.is_bf16);
+        uint8_t *ob = reinterpret_cast<uint8_t *>(p.out16) + pix * out_pitch + 2 * ch0;
+        st_global_v4(ob, hi);
+        if (p.out_parts == 2 || p.out_lo8 != nullptr) {
+          float2 lf[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 h = unpack2(hi[j], p.is_bf16);
+            lf[j] = make_float2(f[2 * j] - h.x, f[2 * j + 1] - h.y);
+          }
+          if (p.out_parts == 2) {
+            uint32_t lo[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) lo[j] = pack2(lf[j].x, lf[j].y, p.is_bf16);
+            st_global_v4(p.out_lo16 != nullptr ? reinterpret_cast<uint8_t *>(p.out_lo16) + pix * 128 + 2 * ch0 : ob + 128, lo);
+          }
+          if (p.out_lo8 != nullptr) {
+            uint32_t l8[2];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const uint32_t a = __nv_cvt_float2_to_fp8x2(make_float2(lf[2 * j].x * 64.f, lf[2 * j].y * 64.f), __NV_SATFINITE, __NV_E4M3);
+              const uint32_t c = __nv_cvt_float2_to_fp8x2(make_float2(lf[2 * j + 1].x * 64.f, lf[2 * j + 1].y * 64.f), __NV_SATFINITE, __NV_E4M3);
+              l8[j] = a | (c << 16);
+            }
+            st_global_v2(p.out_lo8 + pix * 64 + ch0, l8[0], l8[1]);
+          }
+        }
+      }
+    }
+  }
+}
+
 // Epilogue of the output conv (Cout <= 16) for one 8x16 tile: raw = acc + bias; recon = raw + upsampled skip
 // (enhancenet.py:51-90); optional recurrent state (mainVideoUnshaded.py:460-465).  thread = GEMM row (32x32b load):
 // pixel (py, px) = (row/8, row%8); NCHW fp32 planes, 8 px = one 32 B sector.  Shared by the single-CTA and the CTA-pair

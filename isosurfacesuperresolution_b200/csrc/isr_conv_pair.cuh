@@ -132,7 +132,14 @@ struct PairTileCursor {
 constexpr int kPairGroups = 2;
 constexpr int kPairBufs = 4;
 constexpr int kPairIssuers = 2;   // MMA-issuing warps (leader CTA), see the issuer section of the kernel
-constexpr int kPairThreads = (4 * kPairGroups + 1 + kPairIssuers) * 32;
+// Warps per epilogue group: 4 (a warp owns TMEM lanes 32q..32q+31 and all 64 columns: 32-byte stores) or 8 (EPW = 8: warps q
+// and q + 4 of a group own the same lanes and split the accumulator columns, epilogue_store16_half in isr_conv.cuh).  The
+// 8-warp form is used for the split-precision convs WITH a residual addend, whose per-tile chain in one warp (addend loads ->
+// accumulator -> ~1000 dependent instructions -> stores, ~9000 cycles) exceeded the two tiles of MMAs a group has per tile
+// (6200 cycles): 151-164 -> 134-141 us.  The store-heavy 4x layers lose with it (16-byte instead of 32-byte stores: fused
+// upsample + conv 743 -> 942 us, 64->64 at 4x 1040 -> 1110 us) and keep four warps.
+constexpr int pair_threads(int epw) { return (epw * kPairGroups + 1 + kPairIssuers) * 32; }
+constexpr int kPairThreads = pair_threads(4);
 
 // N = 64 output channels.  Weight rows of one CTA per tap: STACK: 64 (X region: W_hi for the leader, W_lo for the peer)
 // + 32 (Y region: its half of W_hi); otherwise 32 per weight part.
@@ -148,8 +155,8 @@ constexpr int kPairThreads = (4 * kPairGroups + 1 + kPairIssuers) * 32;
 // v = 2*i + py per low-res tile, four 128-column accumulator buffers; the epilogue drains columns 0..63 to output pixel
 // (2y+py, 2x) and 64..127 to (2y+py, 2x+1).
 // ADD = false: an instance for layers without a residual addend (its prefetch registers are not allocated).
-template <int STACK, int N = 64, int EPI = EPI_STORE16, int PH = 1, bool ADD = true>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
+template <int STACK, int N = 64, int EPI = EPI_STORE16, int PH = 1, bool ADD = true, int EPW = 4>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(pair_threads(EPW), 1)
 conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                     const __grid_constant__ CUtensorMap tmA8, const __grid_constant__ CUtensorMap tmW8,
                     const ConvParams p) {
@@ -157,6 +164,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // when p.a_lo8 is set (STACK): pass 1 is then A_lo8 x W8 as kind::f8f6f4 -- two K = 32 MMAs per tap instead of four
   // K = 16 ones, half the shared-memory operand bytes of the fp16 correction pass (profiles/r02_probe_mma4_fp8_lo.json).
   static_assert(N == 64 || N == 16, "N = 64 (hidden layers) or 16 (output conv)");
+  static_assert(EPW == 4 || (EPW == 8 && N == 64 && EPI == EPI_STORE16 && PH == 1), "EPW = 8: plain 64-wide layers only");
   static_assert(PH == 1 || ((PH == 4 || PH == 2) && STACK == 0 && N == 64 && EPI == EPI_STORE16), "PH = 4 / 2: single-pass 64-wide layers only");
   constexpr bool kUp = PH != 1;     // fused upsample + conv
   constexpr bool kWide = PH == 2;   // ... with two phases per MMA (N = 128)
@@ -175,7 +183,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t s_wy = s_w + 9 * 2 * kHalfTap;   // STACK: Y region after the X region
   const uint32_t s_stage0 = s_w + ((w_bytes + 1023u) & ~1023u);
   const uint32_t s_bar = s_stage0 + p.num_stages * p.stage_bytes;
-  constexpr int G = kPairGroups, NB = (PH == 4 ? 8 : kPairBufs), kTmaWarp = 4 * G, kMmaWarp = 4 * G + 1;
+  constexpr int G = kPairGroups, NB = (PH == 4 ? 8 : kPairBufs), kTmaWarp = EPW * G, kMmaWarp = EPW * G + 1;
   const uint32_t b_full = s_bar, b_empty = s_bar + 64, b_w = s_bar + 128, b_tfull = s_bar + 136,
                  b_tempty = b_tfull + 8 * NB, s_tptr = b_tempty + 8 * NB;
   static_assert(136 + 16 * NB + 4 <= (PH == 4 ? 512 : 256), "barrier block overflows its reservation (256 B; 512 B for PH = 4)");
@@ -192,7 +200,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     mbar_init(b_w, 2);
     for (int a = 0; a < NB; ++a) {
       mbar_init(b_tfull + 8 * a, 1);   // per CTA: multicast commit
-      mbar_init(b_tempty + 8 * a, 8);  // leader: 4 epilogue warps x 2 CTAs
+      mbar_init(b_tempty + 8 * a, 2 * EPW);  // leader: the epilogue warps of one group x 2 CTAs
     }
     fence_barrier_init();
   }
@@ -365,7 +373,7 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else {
     // ===================== epilogue warps: group g = warp/4 drains tiles g, g+G, ... =====================
-    const int grp = warp >> 2, q = warp & 3;
+    const int grp = warp / EPW, q = warp & 3, chalf = (warp >> 2) & 1;   // warp % 4 = its TMEM lane quarter
     pdl_wait();   // addend reads / output writes must not overtake the previous kernel
     PairTileCursor cur;
     int cur_i = -1;
@@ -393,9 +401,11 @@ conv3x3_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll 1   // one copy of the epilogue body (two inlined copies push its arrays into local memory)
         for (int u = 0; u < 2; ++u)
           epilogue_store16<N, 0, false>(p, s_bias, taddr + u * N, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph, 2, phase, u);
-      } else if constexpr (EPI == EPI_STORE16)
+      } else if constexpr (EPI == EPI_STORE16 && EPW == 8)
+        epilogue_store16_half<N, STACK, ADD>(p, s_bias, taddr, q, chalf, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
+      else if constexpr (EPI == EPI_STORE16)
         epilogue_store16<N, STACK, ADD>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph,
-                                   PH == 4 ? 2 : 1, PH == 4 ? (phase >> 1) : 0, PH == 4 ? (phase & 1) : 0);
+                                        PH == 4 ? 2 : 1, PH == 4 ? (phase >> 1) : 0, PH == 4 ? (phase & 1) : 0);
       else
         epilogue_final<N, STACK>(p, s_bias, taddr, q, lane, b, ty, tx, valid, b_tfull + 8 * acc, acc_ph);
       tc_fence_before();
