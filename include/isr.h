@@ -138,6 +138,18 @@ int isr_inpaint_workspace_bytes(int B, int h, int w, size_t *bytes);
 int isr_inpaint_flow(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, void *workspace,
                      size_t workspace_bytes, void *stream);
 
+/* isr_inpaint_flow without a workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  Same arguments, kernels and results as isr_inpaint_flow; the pyramid scratch is a
+ * static device array inside libisr.so of ISR_INPAINT_STATIC_MAX_BYTES (8 MiB, which every GPU that loads the library
+ * holds until the process exits): enough for B * h * w up to about one million low-res pixels (4 x 512 x 512,
+ * 1 x 1080 x 960; need = isr_inpaint_workspace_bytes).  Larger problems are refused with ISR_ERR_WORKSPACE.  The call
+ * itself calls no cudaMalloc / cudaFree or other allocating routine.  ALL calls share the one array (per device): calls
+ * that overlap on the GPU -- different streams, different threads -- race; serialise them or use isr_inpaint_flow.
+ * Nothing in the scratch needs clearing between calls (every element is written before it is read within a call). */
+#define ISR_INPAINT_STATIC_MAX_BYTES (8u << 20)
+int isr_inpaint_flow_static(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, void *stream);
+
 /* Screen-space ambient occlusion of the renderer's post-pass on the device:
  * ShadowFX::screenSpaceAmbientOcclusion, GPURenderer/ShadowFX.cpp:23-134, same argument list and meaning (strided
  * addressing: value(channel, x, y) = buf[channel + entry_stride * (x + row_stride * y)]; the reference calls it in place

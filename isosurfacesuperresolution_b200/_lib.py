@@ -48,6 +48,7 @@ SIGNATURES = {
     "isr_ingest_low_channels": (_i, [_i]),
     "isr_inpaint_workspace_bytes": (_i, [_i, _i, _i, _c.POINTER(_sz)]),
     "isr_inpaint_flow": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
+    "isr_inpaint_flow_static": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "isr_ssao": (_i, [_i, _i, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _i, _i, _i, _c.c_float, _c.c_float, _i, _vp]),
     "isr_ssao_tables": (_i, [_i, _i, _vp, _vp]),
     "isr_raycast_iso": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),

@@ -879,6 +879,35 @@ static int check_device() {
   return ISR_OK;
 }
 
+// ---- allocation-free flow in-painting (isr_inpaint_flow_static) -----------------------------------------------------
+// The pyramid scratch of the in-painting kernels in a file-scope device array instead of a caller workspace: for callers
+// that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every device that loads the
+// library holds these ISR_INPAINT_STATIC_MAX_BYTES until the process exits.  In host code the array's NAME is only a
+// host-side stand-in; the device address comes from cudaGetSymbolAddress, asked once per device with that device current.
+// Nothing in the scratch has to start at zero: inpaint_init_kernel writes the whole level-0 weight plane and every pull
+// step writes every value / weight element of its level before any kernel of the same call reads it, so the contents the
+// previous call left behind are never observed.  All calls share the one array: calls that overlap on the GPU (two
+// streams, two threads) race.
+static_assert(ISR_INPAINT_STATIC_MAX_BYTES % 256 == 0, "scratch size");
+static __device__ __align__(256) float g_inpaint_static_scratch[ISR_INPAINT_STATIC_MAX_BYTES / sizeof(float)];
+
+static int inpaint_static_scratch(float **out) {
+  static std::mutex mu;
+  static float *ptr[kMaxDevices] = {nullptr};
+  int dev = 0;
+  ISR_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(ISR_ERR_UNSUPPORTED, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr[dev] == nullptr) {
+    void *p = nullptr;
+    ISR_CUDA(cudaGetSymbolAddress(&p, g_inpaint_static_scratch));   // the address on the CURRENT device
+    if (p == nullptr) return fail(ISR_ERR_CUDA, "inpaint_flow_static: cudaGetSymbolAddress returned a null address");
+    ptr[dev] = static_cast<float *>(p);
+  }
+  *out = ptr[dev];
+  return ISR_OK;
+}
+
 extern "C" {
 
 int isr_version(void) { return 100; }
@@ -1232,6 +1261,23 @@ int isr_inpaint_flow(const float *flow, const unsigned char *hole, float *out, i
   int rc = check_device();
   if (rc != ISR_OK) return rc;
   ISR_CUDA(launch_inpaint_flow(flow, hole, out, B, h, w, static_cast<float *>(workspace), S(stream)));
+  return ISR_OK;
+}
+
+int isr_inpaint_flow_static(const float *flow, const unsigned char *hole, float *out, int B, int h, int w, void *stream) {
+  if (flow == nullptr || hole == nullptr || out == nullptr || B <= 0 || h <= 0 || w <= 0)
+    return fail(ISR_ERR_ARG, "inpaint_flow_static: bad arguments");
+  const size_t need = inpaint_workspace_floats(B, h, w) * sizeof(float);
+  if (need > static_cast<size_t>(ISR_INPAINT_STATIC_MAX_BYTES))
+    return fail(ISR_ERR_WORKSPACE,
+                "inpaint_flow_static: %d x %d x %d needs %zu bytes of scratch, the built-in array holds %zu "
+                "(ISR_INPAINT_STATIC_MAX_BYTES); use isr_inpaint_flow with a caller workspace",
+                B, h, w, need, static_cast<size_t>(ISR_INPAINT_STATIC_MAX_BYTES));
+  int rc = check_device();
+  if (rc != ISR_OK) return rc;
+  float *scratch = nullptr;
+  if ((rc = inpaint_static_scratch(&scratch)) != ISR_OK) return rc;
+  ISR_CUDA(launch_inpaint_flow(flow, hole, out, B, h, w, scratch, S(stream)));
   return ISR_OK;
 }
 
